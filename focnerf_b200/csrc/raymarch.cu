@@ -1,0 +1,360 @@
+// raymarch.cu -- occupancy-bitfield ray marching for sm_100a.
+//
+// Replaces the reference kernels K1-K6, K9 (raymarching/src/raymarching.cu:92-490, 701-815) behind the C ABI of
+// include/foc_b200.h.  Integer results (sample counts, cell indices, offsets) are bit-exact with the reference
+// given the same bitfield: every float operation below states its rounding (foc::fmul/fadd/ffma), placed to match
+// the FMA contractions nvcc makes for the reference source (verified against the SASS of oracle/_ref).
+//
+// Training march = three launches, no spin-waits, no atomics:
+//   count  : 1 thread / ray walks the bitfield and counts occupied steps          -> scratch counts[N]
+//   scan   : 1 CTA, warp-shuffle exclusive prefix scan over counts                 -> rays[N,3], counter[2]
+//   write  : 1 thread / ray re-walks and writes its slice (slots are ray-ordered and deterministic; the
+//            reference hands them out in atomic arrival order, raymarching.cu:405-406)
+#include "common.cuh"
+
+namespace foc {
+
+struct MarchParams {
+    const uint8_t* grid;
+    float bound, dt_gamma, dt_min, dt_max, rH, H3, Hf, Hm1, halfH;
+    int C;
+    uint32_t H;
+};
+
+__host__ inline MarchParams make_march_params(const uint8_t* grid, float bound, float dt_gamma, uint32_t max_steps, uint32_t C, uint32_t H) {
+    MarchParams p;
+    p.grid = grid; p.bound = bound; p.dt_gamma = dt_gamma; p.C = (int)C; p.H = H;
+    const float two_sqrt3 = 2.0f * 1.7320508075688772f;                 // raymarching.cu:345-346
+    p.dt_min = two_sqrt3 / (float)max_steps;                            // IEEE division on the host == device __fdiv_rn
+    p.dt_max = (two_sqrt3 * (float)(1 << (C - 1))) / (float)H;
+    p.rH = 1.0f / (float)H; p.Hf = (float)H; p.Hm1 = (float)(H - 1); p.H3 = (float)(H * H * H); p.halfH = 0.5f * (float)H;
+    return p;
+}
+
+struct Ray {
+    float ox, oy, oz, dx, dy, dz, rdx, rdy, rdz, sx, sy, sz, far;
+};
+
+__device__ __forceinline__ Ray load_ray(const float* __restrict__ rays_o, const float* __restrict__ rays_d, uint32_t id, float far) {
+    Ray r;
+    r.ox = __ldg(rays_o + 3 * (size_t)id); r.oy = __ldg(rays_o + 3 * (size_t)id + 1); r.oz = __ldg(rays_o + 3 * (size_t)id + 2);
+    r.dx = __ldg(rays_d + 3 * (size_t)id); r.dy = __ldg(rays_d + 3 * (size_t)id + 1); r.dz = __ldg(rays_d + 3 * (size_t)id + 2);
+    r.rdx = __frcp_rn(r.dx); r.rdy = __frcp_rn(r.dy); r.rdz = __frcp_rn(r.dz);       // 1/d, correctly rounded (l.337)
+    // 0.5 * sign(d) folded once: (n + 0.5) + 0.5*sign(d) is exact in fp32 for n < 2^22
+    r.sx = copysignf(0.5f, r.dx); r.sy = copysignf(0.5f, r.dy); r.sz = copysignf(0.5f, r.dz);
+    r.far = far;
+    return r;
+}
+
+__device__ __forceinline__ float step_dt(const MarchParams& p, float t) { return clampf(fmul(t, p.dt_gamma), p.dt_min, p.dt_max); }
+
+// frexp exponent of a non-negative finite float, clamped to [0, C-1] (raymarching.cu:42-54)
+__device__ __forceinline__ int mip_level(float mx, int C) {
+    int e = (int)((__float_as_uint(mx) >> 23) & 0xffu) - 126;   // normal numbers; zero/denormals give e <= 0
+    return min(C - 1, max(0, e));
+}
+
+// One probe at parameter t: returns true when the cell is occupied (x,y,z,dt filled);
+// otherwise advances t past the empty cell (raymarching.cu:360-399).
+__device__ __forceinline__ bool probe(const MarchParams& p, const Ray& r, float& t, float& x, float& y, float& z, float& dt) {
+    const float tc = t;
+    x = clampf(ffma(tc, r.dx, r.ox), -p.bound, p.bound);
+    y = clampf(ffma(tc, r.dy, r.oy), -p.bound, p.bound);
+    z = clampf(ffma(tc, r.dz, r.oz), -p.bound, p.bound);
+    dt = step_dt(p, tc);
+    int level = 0;
+    float mip_bound = fminf(1.0f, p.bound), mip_rbound;
+    if (p.C > 1) {
+        const float mx = fmaxf(fabsf(x), fmaxf(fabsf(y), fabsf(z)));
+        level = max(mip_level(mx, p.C), mip_level(fmul(fmul(dt, p.Hf), 0.5f), p.C));
+        mip_bound = fminf(__uint_as_float((uint32_t)(127 + level) << 23), p.bound);   // scalbnf(1, level)
+    }
+    mip_rbound = __frcp_rn(mip_bound);
+    // 0.5 * (x * rbound + 1) * H : the reference evaluates both products in double and narrows once (l.374).
+    // (0.5*v)*H is exact in double (24-bit x <=24-bit significands), so the single narrowing is the correctly
+    // rounded fp32 product v * (H/2) -- one FMUL here, no FP64 pipe.
+    const float fx = fmul(ffma(x, mip_rbound, 1.0f), p.halfH);
+    const float fy = fmul(ffma(y, mip_rbound, 1.0f), p.halfH);
+    const float fz = fmul(ffma(z, mip_rbound, 1.0f), p.halfH);
+    const int nx = (int)clampf(fx, 0.0f, p.Hm1), ny = (int)clampf(fy, 0.0f, p.Hm1), nz = (int)clampf(fz, 0.0f, p.Hm1);
+    const uint32_t index = (uint32_t)ffma((float)level, p.H3, (float)morton3((uint32_t)nx, (uint32_t)ny, (uint32_t)nz));
+    const bool occ = (__ldg(p.grid + (index >> 3)) >> (index & 7u)) & 1u;
+    if (occ) return true;
+    const float tx = fmul(ffma(mip_bound, ffma(fmul(fadd(fadd((float)nx, 0.5f), r.sx), p.rH), 2.0f, -1.0f), -x), r.rdx);
+    const float ty = fmul(ffma(mip_bound, ffma(fmul(fadd(fadd((float)ny, 0.5f), r.sy), p.rH), 2.0f, -1.0f), -y), r.rdy);
+    const float tz = fmul(ffma(mip_bound, ffma(fmul(fadd(fadd((float)nz, 0.5f), r.sz), p.rH), 2.0f, -1.0f), -z), r.rdz);
+    const float tt = fadd(tc, fmaxf(0.0f, fminf(tx, fminf(ty, tz))));
+    float tn = tc;
+    do { tn = fadd(tn, step_dt(p, tn)); } while (tn < tt);
+    t = tn;
+    return false;
+}
+
+}  // namespace foc
+using namespace foc;
+
+// ------------------------------------------------------------------------------------------------ utility kernels
+
+// K1 (raymarching.cu:92-145): slab test; near clamped to min_near; miss -> FLT_MAX for both.
+__global__ void __launch_bounds__(256) k_near_far(const float* __restrict__ rays_o, const float* __restrict__ rays_d,
+                                                  const float* __restrict__ aabb, uint32_t N, float min_near,
+                                                  float* __restrict__ nears, float* __restrict__ fars) {
+    const uint32_t n = blockIdx.x * blockDim.x + threadIdx.x;
+    if (n >= N) return;
+    float tn = 0.f, tf = 0.f;
+    bool miss = false;
+    #pragma unroll
+    for (int a = 0; a < 3; ++a) {
+        const float o = __ldg(rays_o + 3 * (size_t)n + a), r = __frcp_rn(__ldg(rays_d + 3 * (size_t)n + a));
+        float lo = fmul(fsub(__ldg(aabb + a), o), r), hi = fmul(fsub(__ldg(aabb + a + 3), o), r);
+        if (lo > hi) { const float s = lo; lo = hi; hi = s; }
+        if (a == 0) { tn = lo; tf = hi; }
+        else if (!miss) {
+            if (tn > hi || lo > tf) miss = true;
+            else { if (lo > tn) tn = lo; if (hi < tf) tf = hi; }
+        }
+    }
+    if (miss) { tn = tf = 3.402823466e+38f; }
+    else if (tn < min_near) tn = min_near;
+    nears[n] = tn; fars[n] = tf;
+}
+
+// K2 (raymarching.cu:163-198)
+__global__ void __launch_bounds__(256) k_sph_from_ray(const float* __restrict__ rays_o, const float* __restrict__ rays_d,
+                                                      float radius, uint32_t N, float* __restrict__ coords) {
+    const uint32_t n = blockIdx.x * blockDim.x + threadIdx.x;
+    if (n >= N) return;
+    const float ox = rays_o[3 * (size_t)n], oy = rays_o[3 * (size_t)n + 1], oz = rays_o[3 * (size_t)n + 2];
+    const float dx = rays_d[3 * (size_t)n], dy = rays_d[3 * (size_t)n + 1], dz = rays_d[3 * (size_t)n + 2];
+    const float A = dx * dx + dy * dy + dz * dz;
+    const float B = ox * dx + oy * dy + oz * dz;
+    const float Cc = ox * ox + oy * oy + oz * oz - radius * radius;
+    const float t = (-B + sqrtf(B * B - A * Cc)) / A;
+    const float x = ox + t * dx, y = oy + t * dy, z = oz + t * dz;
+    const float theta = atan2f(sqrtf(x * x + z * z), y), phi = atan2f(z, x);
+    const float RPI = 0.3183098861837907f;
+    coords[2 * (size_t)n] = 2 * theta * RPI - 1;
+    coords[2 * (size_t)n + 1] = phi * RPI;
+}
+
+// K3 / K4 (raymarching.cu:214-254)
+__global__ void __launch_bounds__(256) k_morton3d(const int32_t* __restrict__ coords, uint32_t N, int32_t* __restrict__ indices) {
+    const uint32_t n = blockIdx.x * blockDim.x + threadIdx.x;
+    if (n >= N) return;
+    indices[n] = (int32_t)morton3((uint32_t)coords[3 * (size_t)n], (uint32_t)coords[3 * (size_t)n + 1], (uint32_t)coords[3 * (size_t)n + 2]);
+}
+__global__ void __launch_bounds__(256) k_morton3d_invert(const int32_t* __restrict__ indices, uint32_t N, int32_t* __restrict__ coords) {
+    const uint32_t n = blockIdx.x * blockDim.x + threadIdx.x;
+    if (n >= N) return;
+    const uint32_t v = (uint32_t)indices[n];
+    coords[3 * (size_t)n] = (int32_t)compact3(v);
+    coords[3 * (size_t)n + 1] = (int32_t)compact3(v >> 1);
+    coords[3 * (size_t)n + 2] = (int32_t)compact3(v >> 2);
+}
+
+// K5 (raymarching.cu:268-289): one thread packs 32 cells = 4 bytes: eight float4 loads, one 32-bit store.
+__global__ void __launch_bounds__(256) k_packbits(const float* __restrict__ grid, uint32_t N, float thresh, uint8_t* __restrict__ bitfield) {
+    const uint32_t w = blockIdx.x * blockDim.x + threadIdx.x;       // word index (4 bytes of bitfield)
+    const uint32_t n_words = N >> 2;
+    if (w < n_words) {
+        const float4* g = reinterpret_cast<const float4*>(grid) + (size_t)w * 8;
+        uint32_t bits = 0;
+        #pragma unroll
+        for (int i = 0; i < 8; ++i) {
+            const float4 v = __ldg(g + i);
+            bits |= (uint32_t)(v.x > thresh) << (4 * i) | (uint32_t)(v.y > thresh) << (4 * i + 1) |
+                    (uint32_t)(v.z > thresh) << (4 * i + 2) | (uint32_t)(v.w > thresh) << (4 * i + 3);
+        }
+        reinterpret_cast<uint32_t*>(bitfield)[w] = bits;
+    } else if (w == n_words) {                                       // tail bytes when N % 4 != 0
+        for (uint32_t n = n_words * 4; n < N; ++n) {
+            uint8_t b = 0;
+            for (int i = 0; i < 8; ++i) b |= (uint8_t)((grid[(size_t)n * 8 + i] > thresh) << i);
+            bitfield[n] = b;
+        }
+    }
+}
+__global__ void __launch_bounds__(256) k_packbits_bytes(const float* __restrict__ grid, uint32_t N, float thresh, uint8_t* __restrict__ bitfield) {
+    const uint32_t n = blockIdx.x * blockDim.x + threadIdx.x;
+    if (n >= N) return;
+    uint8_t b = 0;
+    #pragma unroll
+    for (int i = 0; i < 8; ++i) b |= (uint8_t)((__ldg(grid + (size_t)n * 8 + i) > thresh) << i);
+    bitfield[n] = b;
+}
+
+// ------------------------------------------------------------------------------------------------ training march
+
+// pass 1 (raymarching.cu:353-400): count occupied steps of every ray.
+__global__ void __launch_bounds__(128) k_march_count(const float* __restrict__ rays_o, const float* __restrict__ rays_d,
+                                                     const float* __restrict__ nears, const float* __restrict__ fars,
+                                                     const float* __restrict__ noises, uint32_t N, uint32_t max_steps,
+                                                     MarchParams p, uint32_t* __restrict__ counts) {
+    const uint32_t n = blockIdx.x * blockDim.x + threadIdx.x;
+    if (n >= N) return;
+    const Ray r = load_ray(rays_o, rays_d, n, __ldg(fars + n));
+    const float near = __ldg(nears + n);
+    float t = ffma(step_dt(p, near), __ldg(noises + n), near);          // t0 = near + clamp(near*gamma)*noise (one FMA, l.351)
+    uint32_t num = 0;
+    float x, y, z, dt;
+    while (t < r.far && num < max_steps) {
+        if (probe(p, r, t, x, y, z, dt)) { ++num; t = fadd(t, dt); }
+    }
+    counts[n] = num;
+}
+
+// exclusive prefix scan of counts in ray order by ONE CTA of 1024 threads (N is a few thousand in training; at
+// 640k rays this is ~600 block iterations of coalesced loads).  rays[n] = (n, base + excl, count);
+// counter[0] += total, counter[1] += N  (raymarching.cu:405-413).
+__global__ void __launch_bounds__(1024) k_march_scan(const uint32_t* __restrict__ counts, uint32_t N,
+                                                     int32_t* __restrict__ rays, int32_t* __restrict__ counter) {
+    __shared__ uint32_t warp_tot[32];
+    __shared__ uint32_t s_base;
+    const int lane = threadIdx.x & 31, wid = threadIdx.x >> 5;
+    if (threadIdx.x == 0) s_base = (uint32_t)counter[0];
+    __syncthreads();
+    for (uint32_t start = 0; start < N; start += 1024) {
+        const uint32_t n = start + threadIdx.x;
+        const uint32_t c = n < N ? counts[n] : 0u;
+        const uint32_t incl = warp_incl_sum_u32(c, lane);
+        if (lane == 31) warp_tot[wid] = incl;
+        __syncthreads();
+        const uint32_t base = s_base;
+        uint32_t wv = warp_tot[lane];                       // every warp scans the 32 warp totals
+        const uint32_t wincl = warp_incl_sum_u32(wv, lane);
+        const uint32_t woff = __shfl_sync(0xffffffffu, wincl - wv, wid);
+        const uint32_t total = __shfl_sync(0xffffffffu, wincl, 31);
+        if (n < N) {
+            rays[3 * (size_t)n] = (int32_t)n;
+            rays[3 * (size_t)n + 1] = (int32_t)(base + woff + incl - c);
+            rays[3 * (size_t)n + 2] = (int32_t)c;
+        }
+        __syncthreads();
+        if (threadIdx.x == 0) s_base = base + total;
+        __syncthreads();
+    }
+    if (threadIdx.x == 0) { counter[0] = (int32_t)s_base; counter[1] += (int32_t)N; }
+}
+
+// pass 2 (raymarching.cu:404-479): re-walk and write the ray's slice.
+__global__ void __launch_bounds__(128) k_march_write(const float* __restrict__ rays_o, const float* __restrict__ rays_d,
+                                                     const float* __restrict__ nears, const float* __restrict__ fars,
+                                                     const float* __restrict__ noises, uint32_t N, uint32_t M,
+                                                     MarchParams p, const int32_t* __restrict__ rays,
+                                                     float* __restrict__ xyzs, float* __restrict__ dirs, float* __restrict__ deltas) {
+    const uint32_t n = blockIdx.x * blockDim.x + threadIdx.x;
+    if (n >= N) return;
+    const uint32_t off = (uint32_t)rays[3 * (size_t)n + 1], num = (uint32_t)rays[3 * (size_t)n + 2];
+    if (num == 0 || off + num > M) return;
+    const Ray r = load_ray(rays_o, rays_d, n, __ldg(fars + n));
+    const float near = __ldg(nears + n);
+    float t = ffma(step_dt(p, near), __ldg(noises + n), near);
+    float last_t = t, x, y, z, dt;
+    float* px = xyzs + 3 * (size_t)off; float* pd = dirs + 3 * (size_t)off; float* pl = deltas + 2 * (size_t)off;
+    uint32_t step = 0;
+    while (t < r.far && step < num) {
+        if (!probe(p, r, t, x, y, z, dt)) continue;
+        px[0] = x; px[1] = y; px[2] = z;
+        pd[0] = r.dx; pd[1] = r.dy; pd[2] = r.dz;
+        t = fadd(t, dt);
+        pl[0] = dt; pl[1] = fsub(t, last_t);
+        last_t = t;
+        px += 3; pd += 3; pl += 2; ++step;
+    }
+}
+
+// ------------------------------------------------------------------------------------------------ inference march (K9)
+
+// raymarching.cu:701-805: each alive ray takes <= n_step occupied samples from rays_t[id]; slot n*n_step.
+__global__ void __launch_bounds__(128) k_march_rays(uint32_t n_alive, uint32_t n_step, const int32_t* __restrict__ rays_alive,
+                                                    const float* __restrict__ rays_t, const float* __restrict__ rays_o,
+                                                    const float* __restrict__ rays_d, const float* __restrict__ fars,
+                                                    const float* __restrict__ noises, MarchParams p,
+                                                    float* __restrict__ xyzs, float* __restrict__ dirs, float* __restrict__ deltas) {
+    const uint32_t n = blockIdx.x * blockDim.x + threadIdx.x;
+    if (n >= n_alive) return;
+    const uint32_t id = (uint32_t)__ldg(rays_alive + n);
+    const Ray r = load_ray(rays_o, rays_d, id, __ldg(fars + id));
+    float t = __ldg(rays_t + id);
+    t = ffma(step_dt(p, t), __ldg(noises + n), t);
+    float last_t = t, x, y, z, dt;
+    const size_t base = (size_t)n * n_step;
+    float* px = xyzs + 3 * base; float* pd = dirs + 3 * base; float* pl = deltas + 2 * base;
+    uint32_t step = 0;
+    while (t < r.far && step < n_step) {
+        if (!probe(p, r, t, x, y, z, dt)) continue;
+        px[0] = x; px[1] = y; px[2] = z;
+        pd[0] = r.dx; pd[1] = r.dy; pd[2] = r.dz;
+        t = fadd(t, dt);
+        pl[0] = dt; pl[1] = fsub(t, last_t);
+        last_t = t;
+        px += 3; pd += 3; pl += 2; ++step;
+    }
+}
+
+// ------------------------------------------------------------------------------------------------ C ABI
+static inline cudaStream_t S(void* s) { return reinterpret_cast<cudaStream_t>(s); }
+
+FOC_API int foc_near_far_from_aabb(const float* rays_o, const float* rays_d, const float* aabb, uint32_t N, float min_near,
+                                   float* nears, float* fars, void* stream) {
+    if (N == 0) return 0;
+    k_near_far<<<ceil_div(N, 256), 256, 0, S(stream)>>>(rays_o, rays_d, aabb, N, min_near, nears, fars);
+    FOC_LAUNCH_CHECK(); return 0;
+}
+FOC_API int foc_sph_from_ray(const float* rays_o, const float* rays_d, float radius, uint32_t N, float* coords, void* stream) {
+    if (N == 0) return 0;
+    k_sph_from_ray<<<ceil_div(N, 256), 256, 0, S(stream)>>>(rays_o, rays_d, radius, N, coords);
+    FOC_LAUNCH_CHECK(); return 0;
+}
+FOC_API int foc_morton3D(const int32_t* coords, uint32_t N, int32_t* indices, void* stream) {
+    if (N == 0) return 0;
+    k_morton3d<<<ceil_div(N, 256), 256, 0, S(stream)>>>(coords, N, indices);
+    FOC_LAUNCH_CHECK(); return 0;
+}
+FOC_API int foc_morton3D_invert(const int32_t* indices, uint32_t N, int32_t* coords, void* stream) {
+    if (N == 0) return 0;
+    k_morton3d_invert<<<ceil_div(N, 256), 256, 0, S(stream)>>>(indices, N, coords);
+    FOC_LAUNCH_CHECK(); return 0;
+}
+FOC_API int foc_packbits(const float* grid, uint32_t N, float density_thresh, uint8_t* bitfield, void* stream) {
+    if (N == 0) return 0;
+    const bool aligned = ((reinterpret_cast<uintptr_t>(grid) & 15u) == 0) && ((reinterpret_cast<uintptr_t>(bitfield) & 3u) == 0);
+    if (aligned) k_packbits<<<ceil_div((N >> 2) + 1, 256), 256, 0, S(stream)>>>(grid, N, density_thresh, bitfield);
+    else k_packbits_bytes<<<ceil_div(N, 256), 256, 0, S(stream)>>>(grid, N, density_thresh, bitfield);
+    FOC_LAUNCH_CHECK(); return 0;
+}
+
+FOC_API size_t foc_march_rays_train_scratch_bytes(uint32_t N) { return (size_t)N * sizeof(uint32_t); }
+
+// small N (a training batch) is latency-bound: one warp per CTA spreads the rays over all SMs
+static inline uint32_t march_block(uint32_t n) { return n <= (uint32_t)kNumSMs * 32u * 8u ? 32u : 128u; }
+
+FOC_API int foc_march_rays_train(const float* rays_o, const float* rays_d, const uint8_t* grid, float bound, float dt_gamma,
+                                 uint32_t max_steps, uint32_t N, uint32_t C, uint32_t H, uint32_t M, const float* nears,
+                                 const float* fars, float* xyzs, float* dirs, float* deltas, int32_t* rays, int32_t* counter,
+                                 const float* noises, void* scratch, void* stream) {
+    if (N == 0) return 0;
+    if (C == 0 || C > 8 || H == 0 || H > 1024 || (uint64_t)C * H * H * H > (1ull << 24)) return FOC_ERR_UNSUPPORTED;  // fp32 cell index exact (H1)
+    const MarchParams p = make_march_params(grid, bound, dt_gamma, max_steps, C, H);
+    uint32_t* counts = static_cast<uint32_t*>(scratch);
+    const uint32_t bs = march_block(N);
+    k_march_count<<<ceil_div(N, bs), bs, 0, S(stream)>>>(rays_o, rays_d, nears, fars, noises, N, max_steps, p, counts);
+    FOC_LAUNCH_CHECK();
+    k_march_scan<<<1, 1024, 0, S(stream)>>>(counts, N, rays, counter);
+    FOC_LAUNCH_CHECK();
+    k_march_write<<<ceil_div(N, bs), bs, 0, S(stream)>>>(rays_o, rays_d, nears, fars, noises, N, M, p, rays, xyzs, dirs, deltas);
+    FOC_LAUNCH_CHECK(); return 0;
+}
+
+FOC_API int foc_march_rays(uint32_t n_alive, uint32_t n_step, const int32_t* rays_alive, const float* rays_t,
+                           const float* rays_o, const float* rays_d, float bound, float dt_gamma, uint32_t max_steps,
+                           uint32_t C, uint32_t H, const uint8_t* grid, const float* nears, const float* fars, float* xyzs,
+                           float* dirs, float* deltas, const float* noises, void* stream) {
+    (void)nears;
+    if (n_alive == 0) return 0;
+    if (C == 0 || C > 8 || H == 0 || H > 1024 || (uint64_t)C * H * H * H > (1ull << 24)) return FOC_ERR_UNSUPPORTED;
+    const MarchParams p = make_march_params(grid, bound, dt_gamma, max_steps, C, H);
+    const uint32_t bs = march_block(n_alive);
+    k_march_rays<<<ceil_div(n_alive, bs), bs, 0, S(stream)>>>(n_alive, n_step, rays_alive, rays_t, rays_o, rays_d, fars, noises, p, xyzs, dirs, deltas);
+    FOC_LAUNCH_CHECK(); return 0;
+}

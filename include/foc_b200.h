@@ -1,0 +1,133 @@
+/*
+ * foc_b200.h -- C ABI of libfoc_b200.so: the B200-native (sm_100a) implementation of FOC-NeRF's
+ * per-ray rendering hot path.  Plain pointers and sizes only; no torch / ATen / pybind types.
+ *
+ * Every entry point replaces one function of the reference's pybind11 modules (paths relative to the
+ * reference checkout).  Conventions that differ from the reference, on purpose:
+ *   - all pointers are DEVICE pointers owned by the caller; nothing is allocated or cached inside;
+ *   - `stream` is a cudaStream_t passed as void* (the reference launches on the legacy default stream);
+ *   - the return value is a cudaError_t as int (0 = success; the reference never checks launches);
+ *     FOC_ERR_UNSUPPORTED (-1) is returned for shapes the kernels do not implement.
+ *   - entry points are re-entrant and thread-safe (no globals).
+ * `half` buffers are IEEE binary16 stored as uint16_t.
+ */
+#ifndef FOC_B200_H
+#define FOC_B200_H
+
+#include <stddef.h>
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define FOC_ERR_UNSUPPORTED (-1)
+#define FOC_ABI_VERSION 1
+
+int foc_abi_version(void);
+
+/* ---------------------------------------------------------------- raymarching (raymarching/src/raymarching.h:7-18) */
+
+/* replaces near_far_from_aabb, raymarching.h:7 (kernel raymarching.cu:92-145). rays_* [N,3], aabb [6], nears/fars [N] */
+int foc_near_far_from_aabb(const float *rays_o, const float *rays_d, const float *aabb, uint32_t N, float min_near,
+                           float *nears, float *fars, void *stream);
+/* replaces sph_from_ray, raymarching.h:8 (raymarching.cu:163-198). coords [N,2] */
+int foc_sph_from_ray(const float *rays_o, const float *rays_d, float radius, uint32_t N, float *coords, void *stream);
+/* replaces morton3D / morton3D_invert, raymarching.h:9-10 (raymarching.cu:214-254). coords [N,3] i32, indices [N] i32 */
+int foc_morton3D(const int32_t *coords, uint32_t N, int32_t *indices, void *stream);
+int foc_morton3D_invert(const int32_t *indices, uint32_t N, int32_t *coords, void *stream);
+/* replaces packbits, raymarching.h:11 (raymarching.cu:268-289). grid [8N] f32 -> bitfield [N] u8 */
+int foc_packbits(const float *grid, uint32_t N, float density_thresh, uint8_t *bitfield, void *stream);
+
+/* replaces march_rays_train, raymarching.h:13 (raymarching.cu:312-480).
+ * Same outputs; slots are handed out by an exclusive prefix scan in ray order instead of arrival-order
+ * atomics, so rays[n] = (n, offset, count) is deterministic.  counter[0] += total samples, counter[1] += N.
+ * scratch: foc_march_rays_train_scratch_bytes(N) bytes of device memory (contents irrelevant). */
+size_t foc_march_rays_train_scratch_bytes(uint32_t N);
+int foc_march_rays_train(const float *rays_o, const float *rays_d, const uint8_t *grid, float bound, float dt_gamma,
+                         uint32_t max_steps, uint32_t N, uint32_t C, uint32_t H, uint32_t M, const float *nears,
+                         const float *fars, float *xyzs, float *dirs, float *deltas, int32_t *rays, int32_t *counter,
+                         const float *noises, void *scratch, void *stream);
+
+/* replaces composite_rays_train_forward / _backward, raymarching.h:14-15 (raymarching.cu:501-577, 602-682) */
+int foc_composite_rays_train_forward(const float *sigmas, const float *rgbs, const float *deltas, const int32_t *rays,
+                                     uint32_t M, uint32_t N, float T_thresh, float *weights_sum, float *depth,
+                                     float *image, void *stream);
+int foc_composite_rays_train_backward(const float *grad_weights_sum, const float *grad_image, const float *sigmas,
+                                      const float *rgbs, const float *deltas, const int32_t *rays,
+                                      const float *weights_sum, const float *image, uint32_t M, uint32_t N,
+                                      float T_thresh, float *grad_sigmas, float *grad_rgbs, void *stream);
+
+/* replaces march_rays / composite_rays, raymarching.h:17-18 (raymarching.cu:701-805, 819-905) */
+int foc_march_rays(uint32_t n_alive, uint32_t n_step, const int32_t *rays_alive, const float *rays_t,
+                   const float *rays_o, const float *rays_d, float bound, float dt_gamma, uint32_t max_steps,
+                   uint32_t C, uint32_t H, const uint8_t *grid, const float *nears, const float *fars, float *xyzs,
+                   float *dirs, float *deltas, const float *noises, void *stream);
+int foc_composite_rays(uint32_t n_alive, uint32_t n_step, float T_thresh, int32_t *rays_alive, float *rays_t,
+                       const float *sigmas, const float *rgbs, const float *deltas, float *weights_sum, float *depth,
+                       float *image, void *stream);
+
+/* New (no reference counterpart; replaces `rays_alive = rays_alive[rays_alive >= 0]`,
+ * legacy/nerf/renderer.py:363): stable compaction of the non-negative ids; *n_out (device) receives the count. */
+size_t foc_compact_alive_scratch_bytes(uint32_t n);
+int foc_compact_alive(const int32_t *rays_alive, uint32_t n, int32_t *out, int32_t *n_out, void *scratch, void *stream);
+
+/* FOC-NeRF multi-object composite (COMBINED.py:141-200, 247-251; editable.py:443-471), one fused kernel:
+ * sigmas [K,N,T], rgbs [K,N,T,3] f32; per-sample argmax-sigma selection (earlier object wins ties), then a
+ * front-to-back composite over T uniform samples in [near,far].  image [N,4], depth [N], weights_sum [N]. */
+int foc_composite_multi(const float *sigmas, const float *rgbs, const float *nears, const float *fars, uint32_t K,
+                        uint32_t N, uint32_t T, float bg, float *image, float *depth, float *weights_sum, void *stream);
+
+/* ---------------------------------------------------------------- gridencoder (gridencoder/src/gridencoder.h:12-15) */
+
+/* dtype codes for table-typed buffers */
+#define FOC_F32 0
+#define FOC_F16 1
+
+/* replaces grid_encode_forward, gridencoder.h:12 (gridencoder.cu:87-245). inputs [B,D] f32 in [0,1];
+ * embeddings [n,C]; offsets [L+1] i32; outputs [L,B,C]; dy_dx [B,L*D*C] or NULL.  D in {2,3}, C in {1,2,4,8}. */
+int foc_grid_encode_forward(const float *inputs, const void *embeddings, const int32_t *offsets, void *outputs,
+                            uint32_t B, uint32_t D, uint32_t C, uint32_t L, float S, uint32_t H, void *dy_dx,
+                            uint32_t gridtype, int align_corners, uint32_t interp, int dtype, void *stream);
+/* replaces grid_encode_backward, gridencoder.h:13 (gridencoder.cu:248-369). grad [L,B,C]; grad_embeddings [n,C]
+ * (accumulated into; caller zeroes); dy_dx/grad_inputs NULL or [B,L*D*C]/[B,D] (table dtype). */
+int foc_grid_encode_backward(const void *grad, const float *inputs, const void *embeddings, const int32_t *offsets,
+                             void *grad_embeddings, uint32_t B, uint32_t D, uint32_t C, uint32_t L, float S,
+                             uint32_t H, const void *dy_dx, void *grad_inputs, uint32_t gridtype, int align_corners,
+                             uint32_t interp, int dtype, void *stream);
+/* replaces grad_total_variation, gridencoder.h:15 (gridencoder.cu:506-645). fp32 only (grid.py:164). */
+int foc_grad_total_variation(const float *inputs, const float *embeddings, float *grad, const int32_t *offsets,
+                             float weight, uint32_t B, uint32_t D, uint32_t C, uint32_t L, float S, uint32_t H,
+                             uint32_t gridtype, int align_corners, void *stream);
+
+/* ---------------------------------------------------------------- ffmlp (ffmlp/src/ffmlp.h:7-13) */
+
+/* replaces ffmlp_forward / ffmlp_inference, ffmlp.h:8-9 (ffmlp.cu:331-407, 525-709).  tcgen05/TMEM kernel.
+ * inputs [B,input_dim] f16, weights flat f16 ([hidden,in] + (num_layers-1)x[hidden,hidden] + [16,hidden]),
+ * forward_buffer [num_layers,B,hidden] f16 (NULL = inference), outputs [B,16] f16.  B % 128 == 0,
+ * hidden_dim == 64, input_dim in {32,64}, output_dim <= 16, activation relu(0)/none(6), output activation none. */
+int foc_ffmlp_forward(const uint16_t *inputs, const uint16_t *weights, uint32_t B, uint32_t input_dim,
+                      uint32_t output_dim, uint32_t hidden_dim, uint32_t num_layers, uint32_t activation,
+                      uint32_t output_activation, uint16_t *forward_buffer, uint16_t *outputs, void *stream);
+/* replaces ffmlp_backward, ffmlp.h:11 (ffmlp.cu:410-518, 749-895).  grad [B,16] f16; backward_buffer
+ * [num_layers,B,hidden] f16; grad_inputs [B,input_dim] f16 or NULL; grad_weights flat f16 (overwritten).
+ * scratch: foc_ffmlp_backward_scratch_bytes(...) bytes (fp32 partial weight gradients). */
+size_t foc_ffmlp_backward_scratch_bytes(uint32_t B, uint32_t input_dim, uint32_t hidden_dim, uint32_t num_layers);
+int foc_ffmlp_backward(const uint16_t *grad, const uint16_t *inputs, const uint16_t *weights,
+                       const uint16_t *forward_buffer, uint32_t B, uint32_t input_dim, uint32_t output_dim,
+                       uint32_t hidden_dim, uint32_t num_layers, uint32_t activation, uint32_t output_activation,
+                       int calc_grad_inputs, uint16_t *backward_buffer, uint16_t *grad_inputs, uint16_t *grad_weights,
+                       void *scratch, void *stream);
+/* kept for API compatibility with ffmlp.h:12-13; no-ops (no side streams, no workspaces) */
+int foc_allocate_splitk(size_t size);
+int foc_free_splitk(void);
+
+/* ---------------------------------------------------------------- freqencoder (freqencoder/src/freqencoder.h:7-10) */
+int foc_freq_encode_forward(const float *inputs, uint32_t B, uint32_t D, uint32_t deg, uint32_t C, float *outputs, void *stream);
+int foc_freq_encode_backward(const float *grad, const float *outputs, uint32_t B, uint32_t D, uint32_t deg, uint32_t C,
+                             float *grad_inputs, void *stream);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* FOC_B200_H */
