@@ -1,0 +1,98 @@
+"""ctypes loader for libfoc_b200.so -- the only door between Python and the CUDA kernels.
+
+There is NO fallback: if the shared library is missing or an entry point is absent this module raises, and so
+does every operator built on it (BASELINE.json north_star: "no CPU fallback").  Prototypes are not restated
+here; they are parsed out of include/foc_b200.h, so the header stays the single source of truth and a
+signature drift between header and library shows up as a load error.
+"""
+import ctypes
+import os
+import re
+
+import torch
+
+_HERE = os.path.dirname(os.path.abspath(__file__))
+LIB_PATH = os.path.join(_HERE, "libfoc_b200.so")
+HEADER_PATH = os.path.join(os.path.dirname(_HERE), "include", "foc_b200.h")
+
+_SCALARS = {
+    "int": ctypes.c_int, "uint32_t": ctypes.c_uint32, "int32_t": ctypes.c_int32, "uint64_t": ctypes.c_uint64,
+    "int64_t": ctypes.c_int64, "float": ctypes.c_float, "size_t": ctypes.c_size_t, "void": None,
+}
+
+
+def parse_header(path=HEADER_PATH):
+    """-> {name: (restype, [argtypes])} for every `foc_*` prototype in the header."""
+    src = open(path).read()
+    src = re.sub(r"/\*.*?\*/", " ", src, flags=re.S)
+    src = re.sub(r"//[^\n]*", " ", src)
+    src = re.sub(r"^\s*#.*$", " ", src, flags=re.M)
+    protos = {}
+    for m in re.finditer(r"\b(int|size_t|void)\s+(foc_\w+)\s*\(([^)]*)\)\s*;", src):
+        ret, name, args = m.group(1), m.group(2), m.group(3).strip()
+        argtypes = []
+        if args and args != "void":
+            for a in args.split(","):
+                a = a.strip()
+                if "*" in a:
+                    argtypes.append(ctypes.c_void_p)
+                    continue
+                toks = [t for t in a.replace("const", " ").split() if t]
+                ty = toks[0]
+                if ty not in _SCALARS:
+                    raise RuntimeError(f"foc_b200.h: unknown scalar type in `{a}` of {name}")
+                argtypes.append(_SCALARS[ty])
+        protos[name] = (_SCALARS[ret], argtypes)
+    return protos
+
+
+_lib = None
+_protos = None
+
+
+def lib():
+    global _lib, _protos
+    if _lib is None:
+        if not os.path.exists(LIB_PATH):
+            raise RuntimeError(
+                f"{LIB_PATH} is missing: build it with `python -m focnerf_b200.build` (or __graft_entry__.build()). "
+                "focnerf_b200 has no CPU / PyTorch fallback for its CUDA operators.")
+        l = ctypes.CDLL(LIB_PATH)
+        _protos = parse_header()
+        for name, (ret, argtypes) in _protos.items():
+            try:
+                fn = getattr(l, name)
+            except AttributeError as e:
+                raise RuntimeError(f"libfoc_b200.so does not export `{name}` declared in include/foc_b200.h") from e
+            fn.restype, fn.argtypes = ret, argtypes
+        if l.foc_abi_version() != 1:
+            raise RuntimeError("libfoc_b200.so ABI version mismatch")
+        _lib = l
+    return _lib
+
+
+def declared_symbols():
+    return sorted(parse_header().keys())
+
+
+def ptr(t):
+    """Device pointer of a tensor (None -> NULL)."""
+    return None if t is None else t.data_ptr()
+
+
+def stream():
+    return torch.cuda.current_stream().cuda_stream
+
+
+def check(err, what):
+    if err == 0:
+        return
+    if err == -1:
+        raise RuntimeError(f"{what}: unsupported configuration for the sm_100a kernels")
+    raise RuntimeError(f"{what}: CUDA error {err}")
+
+
+def require_cuda(*tensors):
+    for t in tensors:
+        if t is not None and not t.is_cuda:
+            raise RuntimeError("focnerf_b200 operators need CUDA tensors (there is no CPU path)")

@@ -1,0 +1,141 @@
+// composite.cu -- front-to-back alpha compositing for sm_100a.
+//
+// Replaces the reference kernels K7, K8, K10 (raymarching/src/raymarching.cu:501-577, 602-682, 819-905), the
+// Python boolean-mask compaction of the render loop (legacy/nerf/renderer.py:363) and FOC-NeRF's multi-object
+// composition (COMBINED.py:141-200, 247-251, 515-526; editable.py:443-471) behind the C ABI of include/foc_b200.h.
+//
+// Training compositors: ONE WARP PER RAY.  A ray's samples are a contiguous slice [offset, offset+count) of the
+// sample arrays, so the 32 lanes read sigma / rgb / delta with coalesced 128 / 384 / 256-byte requests (the
+// reference gives each ray to one thread, which walks its slice serially with 4/12/8-byte strided loads).  The
+// recurrences T_i = prod(1-alpha), t_i = sum(delta1), acc_i = sum(w c) become warp-shuffle inclusive scans over
+// 32-sample chunks with the carry kept in registers; early termination (T < T_thresh, tested AFTER the sample
+// is accumulated, raymarching.cu:566) is a ballot + find-first-set.
+// Float results agree with the reference to rounding (different association of the same products/sums), which
+// BASELINE.json bounds at 1e-3 relative; nothing here produces integers.
+#include "common.cuh"
+
+using namespace foc;
+
+namespace {
+
+__device__ __forceinline__ float excl_from_incl_prod(float incl, int lane) {
+    const float up = __shfl_up_sync(0xffffffffu, incl, 1);
+    return lane == 0 ? 1.0f : up;
+}
+__device__ __forceinline__ float bcast_last(float v) { return __shfl_sync(0xffffffffu, v, 31); }
+
+constexpr int kCompWarpsPerCta = 4;   // 128 threads, 4 rays per CTA
+
+}  // namespace
+
+// K7 (raymarching.cu:501-577): weights_sum / depth / image are indexed by the ray id stored in rays[n,0].
+__global__ void __launch_bounds__(32 * kCompWarpsPerCta)
+k_composite_train_fwd(const float* __restrict__ sigmas, const float* __restrict__ rgbs, const float* __restrict__ deltas,
+                      const int32_t* __restrict__ rays, uint32_t M, uint32_t N, float T_thresh,
+                      float* __restrict__ weights_sum, float* __restrict__ depth, float* __restrict__ image) {
+    const int lane = threadIdx.x & 31;
+    const uint32_t n = blockIdx.x * kCompWarpsPerCta + (threadIdx.x >> 5);
+    if (n >= N) return;
+    const uint32_t id = (uint32_t)__ldg(rays + 3 * (size_t)n), off = (uint32_t)__ldg(rays + 3 * (size_t)n + 1),
+                   cnt = (uint32_t)__ldg(rays + 3 * (size_t)n + 2);
+    float r = 0.f, g = 0.f, b = 0.f, d = 0.f, ws = 0.f;
+    if (cnt != 0 && (uint64_t)off + cnt <= M) {            // raymarching.cu:521-528
+        float T = 1.0f, t_base = 0.0f;
+        for (uint32_t base = 0; base < cnt; base += 32) {
+            const uint32_t s = base + lane;
+            const bool valid = s < cnt;
+            const size_t i = (size_t)off + (valid ? s : 0);
+            float alpha = 0.f, d1 = 0.f, cr = 0.f, cg = 0.f, cb = 0.f;
+            if (valid) {
+                const float2 dl = __ldg(reinterpret_cast<const float2*>(deltas) + i);
+                alpha = 1.0f - __expf(-__ldg(sigmas + i) * dl.x);
+                d1 = dl.y;
+                cr = __ldg(rgbs + 3 * i); cg = __ldg(rgbs + 3 * i + 1); cb = __ldg(rgbs + 3 * i + 2);
+            }
+            const float incl = warp_incl_prod(1.0f - alpha, lane);
+            const float w = alpha * (T * excl_from_incl_prod(incl, lane));
+            const float T_after = T * incl;
+            const float t = t_base + warp_incl_sum(d1, lane);
+            const uint32_t stop = __ballot_sync(0xffffffffu, valid && T_after < T_thresh);
+            const int last = stop ? (__ffs(stop) - 1) : 31;
+            if (valid && lane <= last) {
+                r = fmaf(w, cr, r); g = fmaf(w, cg, g); b = fmaf(w, cb, b);
+                d = fmaf(w, t, d); ws += w;
+            }
+            if (stop) break;
+            T = bcast_last(T_after); t_base = bcast_last(t);
+        }
+        r = warp_sum(r); g = warp_sum(g); b = warp_sum(b); d = warp_sum(d); ws = warp_sum(ws);
+    }
+    if (lane == 0) {
+        weights_sum[id] = ws; depth[id] = d;
+        image[3 * (size_t)id] = r; image[3 * (size_t)id + 1] = g; image[3 * (size_t)id + 2] = b;
+    }
+}
+
+// K8 (raymarching.cu:602-682).  grad_sigma_i = delta0_i * ( sum_c g_c (T_after_i c_i - (final_c - acc_c,i))
+//                                                     + g_ws (1 - ws_final) ),  acc INCLUDING sample i.
+// Samples after the early-termination sample are not written (the caller pre-zeroes, raymarching.py:280-281).
+__global__ void __launch_bounds__(32 * kCompWarpsPerCta)
+k_composite_train_bwd(const float* __restrict__ grad_weights_sum, const float* __restrict__ grad_image,
+                      const float* __restrict__ sigmas, const float* __restrict__ rgbs, const float* __restrict__ deltas,
+                      const int32_t* __restrict__ rays, const float* __restrict__ weights_sum, const float* __restrict__ image,
+                      uint32_t M, uint32_t N, float T_thresh, float* __restrict__ grad_sigmas, float* __restrict__ grad_rgbs) {
+    const int lane = threadIdx.x & 31;
+    const uint32_t n = blockIdx.x * kCompWarpsPerCta + (threadIdx.x >> 5);
+    if (n >= N) return;
+    const uint32_t id = (uint32_t)__ldg(rays + 3 * (size_t)n), off = (uint32_t)__ldg(rays + 3 * (size_t)n + 1),
+                   cnt = (uint32_t)__ldg(rays + 3 * (size_t)n + 2);
+    if (cnt == 0 || (uint64_t)off + cnt > M) return;
+    const float gw = __ldg(grad_weights_sum + id);
+    const float gr = __ldg(grad_image + 3 * (size_t)id), gg = __ldg(grad_image + 3 * (size_t)id + 1), gb = __ldg(grad_image + 3 * (size_t)id + 2);
+    const float rf = __ldg(image + 3 * (size_t)id), gf = __ldg(image + 3 * (size_t)id + 1), bf = __ldg(image + 3 * (size_t)id + 2);
+    const float ws_term = gw * (1.0f - __ldg(weights_sum + id));
+    float T = 1.0f, ar = 0.f, ag = 0.f, ab = 0.f;       // carries: transmittance and accumulated colour
+    for (uint32_t base = 0; base < cnt; base += 32) {
+        const uint32_t s = base + lane;
+        const bool valid = s < cnt;
+        const size_t i = (size_t)off + (valid ? s : 0);
+        float alpha = 0.f, d0 = 0.f, cr = 0.f, cg = 0.f, cb = 0.f;
+        if (valid) {
+            d0 = __ldg(deltas + 2 * i);
+            alpha = 1.0f - __expf(-__ldg(sigmas + i) * d0);
+            cr = __ldg(rgbs + 3 * i); cg = __ldg(rgbs + 3 * i + 1); cb = __ldg(rgbs + 3 * i + 2);
+        }
+        const float incl = warp_incl_prod(1.0f - alpha, lane);
+        const float w = alpha * (T * excl_from_incl_prod(incl, lane));
+        const float T_after = T * incl;
+        const float pr = ar + warp_incl_sum(w * cr, lane), pg = ag + warp_incl_sum(w * cg, lane), pb = ab + warp_incl_sum(w * cb, lane);
+        const uint32_t stop = __ballot_sync(0xffffffffu, valid && T_after < T_thresh);
+        const int last = stop ? (__ffs(stop) - 1) : 31;
+        if (valid && lane <= last) {
+            grad_rgbs[3 * i] = gr * w; grad_rgbs[3 * i + 1] = gg * w; grad_rgbs[3 * i + 2] = gb * w;
+            grad_sigmas[i] = d0 * (gr * (T_after * cr - (rf - pr)) + gg * (T_after * cg - (gf - pg)) +
+                                   gb * (T_after * cb - (bf - pb)) + ws_term);
+        }
+        if (stop) break;
+        T = bcast_last(T_after); ar = bcast_last(pr); ag = bcast_last(pg); ab = bcast_last(pb);
+    }
+}
+
+// ------------------------------------------------------------------------------------------------ C ABI
+static inline cudaStream_t S(void* s) { return reinterpret_cast<cudaStream_t>(s); }
+
+FOC_API int foc_composite_rays_train_forward(const float* sigmas, const float* rgbs, const float* deltas, const int32_t* rays,
+                                             uint32_t M, uint32_t N, float T_thresh, float* weights_sum, float* depth,
+                                             float* image, void* stream) {
+    if (N == 0) return 0;
+    k_composite_train_fwd<<<ceil_div(N, kCompWarpsPerCta), 32 * kCompWarpsPerCta, 0, S(stream)>>>(
+        sigmas, rgbs, deltas, rays, M, N, T_thresh, weights_sum, depth, image);
+    FOC_LAUNCH_CHECK(); return 0;
+}
+
+FOC_API int foc_composite_rays_train_backward(const float* grad_weights_sum, const float* grad_image, const float* sigmas,
+                                              const float* rgbs, const float* deltas, const int32_t* rays,
+                                              const float* weights_sum, const float* image, uint32_t M, uint32_t N,
+                                              float T_thresh, float* grad_sigmas, float* grad_rgbs, void* stream) {
+    if (N == 0) return 0;
+    k_composite_train_bwd<<<ceil_div(N, kCompWarpsPerCta), 32 * kCompWarpsPerCta, 0, S(stream)>>>(
+        grad_weights_sum, grad_image, sigmas, rgbs, deltas, rays, weights_sum, image, M, N, T_thresh, grad_sigmas, grad_rgbs);
+    FOC_LAUNCH_CHECK(); return 0;
+}

@@ -1,0 +1,187 @@
+// hashgrid_fwd.cu -- multiresolution hash-grid encoding, forward (K11: gridencoder/src/gridencoder.cu:87-245).
+//
+// One thread per (point, level).  All 2^D corner rows of a thread are fetched as ONE vector load each (half2 for the
+// C=2 fp16 table of the FOC configuration: 4 B; float2 / 8-16 B vectors otherwise) and all 2^D loads are issued
+// before the first use, so a warp keeps 256 independent gathers in flight.  On B200 the whole 23 MB fp16 table
+// is L2-resident (126 MB L2), so the reference's level-major launch order is no longer needed for locality; two
+// thread mappings are offered:
+//   layout 0  [L,B,C]  the reference's output order (grid.y = level), what `_backend.grid_encode_forward` returns;
+//   layout 1  [B,L,C]  point-major: a warp covers 32/L points x L levels and writes a contiguous 128-byte run of the
+//                      [B, L*C] tensor the network consumes -- this removes the permute+reshape copy the reference's
+//                      Python wrapper does after the kernel (grid.py:57).
+// fp16 numerics follow the reference's c10::Half rounding sequence (see hashgrid.cuh) so encodings agree bit for bit.
+#include "hashgrid.cuh"
+
+using namespace foc;
+
+namespace {
+
+template <typename T, int C> struct RowVec;     // one table row (C features) as a single aligned vector load
+template <> struct RowVec<__half, 1> { static __device__ __forceinline__ void ld(const __half* p, float (&v)[1]) { v[0] = __half2float(__ldg(p)); } };
+template <> struct RowVec<__half, 2> { static __device__ __forceinline__ void ld(const __half* p, float (&v)[2]) {
+    const __half2 h = __ldg(reinterpret_cast<const __half2*>(p)); v[0] = __low2float(h); v[1] = __high2float(h); } };
+template <> struct RowVec<__half, 4> { static __device__ __forceinline__ void ld(const __half* p, float (&v)[4]) {
+    const uint2 u = __ldg(reinterpret_cast<const uint2*>(p));
+    const __half2 a = *reinterpret_cast<const __half2*>(&u.x), b = *reinterpret_cast<const __half2*>(&u.y);
+    v[0] = __low2float(a); v[1] = __high2float(a); v[2] = __low2float(b); v[3] = __high2float(b); } };
+template <> struct RowVec<__half, 8> { static __device__ __forceinline__ void ld(const __half* p, float (&v)[8]) {
+    const uint4 u = __ldg(reinterpret_cast<const uint4*>(p));
+    const uint32_t w[4] = {u.x, u.y, u.z, u.w};
+    #pragma unroll
+    for (int i = 0; i < 4; ++i) { const __half2 h = *reinterpret_cast<const __half2*>(&w[i]); v[2 * i] = __low2float(h); v[2 * i + 1] = __high2float(h); } } };
+template <> struct RowVec<float, 1> { static __device__ __forceinline__ void ld(const float* p, float (&v)[1]) { v[0] = __ldg(p); } };
+template <> struct RowVec<float, 2> { static __device__ __forceinline__ void ld(const float* p, float (&v)[2]) {
+    const float2 f = __ldg(reinterpret_cast<const float2*>(p)); v[0] = f.x; v[1] = f.y; } };
+template <> struct RowVec<float, 4> { static __device__ __forceinline__ void ld(const float* p, float (&v)[4]) {
+    const float4 f = __ldg(reinterpret_cast<const float4*>(p)); v[0] = f.x; v[1] = f.y; v[2] = f.z; v[3] = f.w; } };
+template <> struct RowVec<float, 8> { static __device__ __forceinline__ void ld(const float* p, float (&v)[8]) {
+    const float4 a = __ldg(reinterpret_cast<const float4*>(p)), b = __ldg(reinterpret_cast<const float4*>(p) + 1);
+    v[0] = a.x; v[1] = a.y; v[2] = a.z; v[3] = a.w; v[4] = b.x; v[5] = b.y; v[6] = b.z; v[7] = b.w; } };
+
+template <typename T, int C>
+__device__ __forceinline__ void store_row(T* p, const float (&v)[C]) {
+    if constexpr (sizeof(T) == 2 && C == 2) {
+        *reinterpret_cast<__half2*>(p) = __floats2half2_rn(v[0], v[1]);
+    } else if constexpr (sizeof(T) == 4 && C == 2) {
+        *reinterpret_cast<float2*>(p) = make_float2(v[0], v[1]);
+    } else {
+        #pragma unroll
+        for (int c = 0; c < C; ++c) Elem<T>::st(p + c, v[c]);
+    }
+}
+
+template <typename T, int D, int C, int LAYOUT>
+__global__ void __launch_bounds__(256)
+k_grid_fwd(const float* __restrict__ inputs, const T* __restrict__ table, const int32_t* __restrict__ offsets,
+           T* __restrict__ outputs, uint32_t B, uint32_t L, float S, uint32_t H, T* __restrict__ dy_dx,
+           uint32_t gridtype, bool align_corners, uint32_t interp) {
+    uint32_t b, level;
+    if constexpr (LAYOUT == 0) { b = blockIdx.x * blockDim.x + threadIdx.x; level = blockIdx.y; if (b >= B) return; }
+    else {
+        const uint64_t t = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x;
+        if (t >= (uint64_t)B * L) return;
+        b = (uint32_t)(t / L); level = (uint32_t)(t % L);
+    }
+    T* out = LAYOUT == 0 ? outputs + ((size_t)level * B + b) * C : outputs + ((size_t)b * L + level) * C;
+    T* dyo = dy_dx ? dy_dx + (((size_t)b * L + level) * D) * C : nullptr;       // [B, L, D, C]
+
+    float x[D];
+    #pragma unroll
+    for (int d = 0; d < D; ++d) x[d] = __ldg(inputs + (size_t)b * D + d);
+    if (grid_oob<D>(x)) {                                                        // gridencoder.cu:110-135
+        float z[C];
+        #pragma unroll
+        for (int c = 0; c < C; ++c) z[c] = 0.f;
+        store_row<T, C>(out, z);
+        if (dyo) { for (int i = 0; i < D * C; ++i) Elem<T>::st(dyo + i, 0.f); }
+        return;
+    }
+    const GridLevel lv = grid_level(offsets, level, S, H);
+    const T* tab = table + (size_t)lv.offset * C;
+    float pos[D], pder[D];
+    uint32_t pg[D];
+    grid_locate<D>(x, lv.scale, align_corners, interp, pos, pder, pg);
+
+    // gather: all corner rows first (independent loads), then the ordered accumulation of the reference
+    float w[1 << D], rows[1 << D][C];
+    #pragma unroll
+    for (int idx = 0; idx < (1 << D); ++idx) {
+        float wt = 1.0f;
+        uint32_t pl[D];
+        #pragma unroll
+        for (int d = 0; d < D; ++d) {
+            if ((idx >> d) & 1) { wt = __fmul_rn(wt, pos[d]); pl[d] = pg[d] + 1; }
+            else { wt = __fmul_rn(wt, __fsub_rn(1.0f, pos[d])); pl[d] = pg[d]; }
+        }
+        w[idx] = wt;
+        RowVec<T, C>::ld(tab + (size_t)grid_index<D>(gridtype, align_corners, lv.hashmap_size, lv.resolution, pl) * C, rows[idx]);
+    }
+    float res[C];
+    #pragma unroll
+    for (int c = 0; c < C; ++c) res[c] = 0.f;
+    #pragma unroll
+    for (int idx = 0; idx < (1 << D); ++idx) {
+        #pragma unroll
+        for (int c = 0; c < C; ++c) res[c] = Elem<T>::acc(res[c], w[idx], rows[idx][c]);
+    }
+    store_row<T, C>(out, res);
+
+    if (!dyo) return;
+    // gridencoder.cu:201-243: d(out)/d(x_gd) = scale * sum over the other dims' corners of w' * (right - left) * deriv
+    #pragma unroll
+    for (int gd = 0; gd < D; ++gd) {
+        float rg[C];
+        #pragma unroll
+        for (int c = 0; c < C; ++c) rg[c] = 0.f;
+        #pragma unroll
+        for (int idx = 0; idx < (1 << (D - 1)); ++idx) {
+            float wt = lv.scale;
+            uint32_t pl[D];
+            #pragma unroll
+            for (int nd = 0; nd < D - 1; ++nd) {
+                const int d = (nd >= gd) ? nd + 1 : nd;
+                if ((idx >> nd) & 1) { wt = __fmul_rn(wt, pos[d]); pl[d] = pg[d] + 1; }
+                else { wt = __fmul_rn(wt, __fsub_rn(1.0f, pos[d])); pl[d] = pg[d]; }
+            }
+            float left[C], right[C];
+            pl[gd] = pg[gd];
+            RowVec<T, C>::ld(tab + (size_t)grid_index<D>(gridtype, align_corners, lv.hashmap_size, lv.resolution, pl) * C, left);
+            pl[gd] = pg[gd] + 1;
+            RowVec<T, C>::ld(tab + (size_t)grid_index<D>(gridtype, align_corners, lv.hashmap_size, lv.resolution, pl) * C, right);
+            #pragma unroll
+            for (int c = 0; c < C; ++c) {
+                if constexpr (sizeof(T) == 2) {
+                    const float diff = Elem<T>::rnd(__fsub_rn(right[c], left[c]));
+                    rg[c] = Elem<T>::rnd(__fadd_rn(rg[c], Elem<T>::rnd(__fmul_rn(__fmul_rn(wt, diff), pder[gd]))));
+                } else {
+                    rg[c] += wt * (right[c] - left[c]) * pder[gd];
+                }
+            }
+        }
+        #pragma unroll
+        for (int c = 0; c < C; ++c) Elem<T>::st(dyo + gd * C + c, rg[c]);
+    }
+}
+
+template <typename T, int D, int C>
+int launch_fwd(const float* inputs, const void* table, const int32_t* offsets, void* outputs, uint32_t B, uint32_t L,
+               float S, uint32_t H, void* dy_dx, uint32_t gridtype, bool ac, uint32_t interp, int layout, cudaStream_t st) {
+    if (layout == 0) {
+        dim3 grid(ceil_div(B, 256), L);
+        k_grid_fwd<T, D, C, 0><<<grid, 256, 0, st>>>(inputs, (const T*)table, offsets, (T*)outputs, B, L, S, H, (T*)dy_dx, gridtype, ac, interp);
+    } else {
+        const uint64_t total = (uint64_t)B * L;
+        k_grid_fwd<T, D, C, 1><<<(uint32_t)((total + 255) / 256), 256, 0, st>>>(inputs, (const T*)table, offsets, (T*)outputs, B, L, S, H, (T*)dy_dx, gridtype, ac, interp);
+    }
+    FOC_LAUNCH_CHECK(); return 0;
+}
+
+template <typename T, int D>
+int dispatch_c(uint32_t C, const float* inputs, const void* table, const int32_t* offsets, void* outputs, uint32_t B,
+               uint32_t L, float S, uint32_t H, void* dy_dx, uint32_t gridtype, bool ac, uint32_t interp, int layout, cudaStream_t st) {
+    switch (C) {
+        case 1: return launch_fwd<T, D, 1>(inputs, table, offsets, outputs, B, L, S, H, dy_dx, gridtype, ac, interp, layout, st);
+        case 2: return launch_fwd<T, D, 2>(inputs, table, offsets, outputs, B, L, S, H, dy_dx, gridtype, ac, interp, layout, st);
+        case 4: return launch_fwd<T, D, 4>(inputs, table, offsets, outputs, B, L, S, H, dy_dx, gridtype, ac, interp, layout, st);
+        case 8: return launch_fwd<T, D, 8>(inputs, table, offsets, outputs, B, L, S, H, dy_dx, gridtype, ac, interp, layout, st);
+        default: return FOC_ERR_UNSUPPORTED;     // the reference throws for other C (gridencoder.cu:381)
+    }
+}
+
+}  // namespace
+
+FOC_API int foc_grid_encode_forward(const float* inputs, const void* embeddings, const int32_t* offsets, void* outputs,
+                                    uint32_t B, uint32_t D, uint32_t C, uint32_t L, float S, uint32_t H, void* dy_dx,
+                                    uint32_t gridtype, int align_corners, uint32_t interp, int dtype, int layout, void* stream) {
+    if (B == 0 || L == 0) return 0;
+    cudaStream_t st = reinterpret_cast<cudaStream_t>(stream);
+    const bool ac = align_corners != 0;
+    if (dtype == 1) {
+        if (D == 2) return dispatch_c<__half, 2>(C, inputs, embeddings, offsets, outputs, B, L, S, H, dy_dx, gridtype, ac, interp, layout, st);
+        if (D == 3) return dispatch_c<__half, 3>(C, inputs, embeddings, offsets, outputs, B, L, S, H, dy_dx, gridtype, ac, interp, layout, st);
+    } else if (dtype == 0) {
+        if (D == 2) return dispatch_c<float, 2>(C, inputs, embeddings, offsets, outputs, B, L, S, H, dy_dx, gridtype, ac, interp, layout, st);
+        if (D == 3) return dispatch_c<float, 3>(C, inputs, embeddings, offsets, outputs, B, L, S, H, dy_dx, gridtype, ac, interp, layout, st);
+    }
+    return FOC_ERR_UNSUPPORTED;                  // the reference supports D in {2,3,4,5}; FOC uses 3 (gridencoder.cu:388-398)
+}

@@ -1,0 +1,89 @@
+"""`_backend` for the raymarching operators: same method names and positional arguments as the reference's pybind
+module `_raymarching` (raymarching/src/bindings.cpp:5-19, raymarching.h:7-18), implemented by unwrapping tensors
+to device pointers and calling libfoc_b200.so on the current CUDA stream.
+"""
+import torch
+
+from .._lib import check, lib, ptr, require_cuda, stream
+
+
+def _f32c(t, name):
+    if t.dtype != torch.float32 or not t.is_contiguous():
+        raise RuntimeError(f"{name} must be a contiguous float32 tensor")
+
+
+class _Backend:
+    @staticmethod
+    def near_far_from_aabb(rays_o, rays_d, aabb, N, min_near, nears, fars):
+        require_cuda(rays_o, rays_d, aabb, nears, fars)
+        check(lib().foc_near_far_from_aabb(ptr(rays_o), ptr(rays_d), ptr(aabb), N, min_near, ptr(nears), ptr(fars), stream()),
+              "near_far_from_aabb")
+
+    @staticmethod
+    def sph_from_ray(rays_o, rays_d, radius, N, coords):
+        require_cuda(rays_o, rays_d, coords)
+        check(lib().foc_sph_from_ray(ptr(rays_o), ptr(rays_d), radius, N, ptr(coords), stream()), "sph_from_ray")
+
+    @staticmethod
+    def morton3D(coords, N, indices):
+        require_cuda(coords, indices)
+        check(lib().foc_morton3D(ptr(coords), N, ptr(indices), stream()), "morton3D")
+
+    @staticmethod
+    def morton3D_invert(indices, N, coords):
+        require_cuda(indices, coords)
+        check(lib().foc_morton3D_invert(ptr(indices), N, ptr(coords), stream()), "morton3D_invert")
+
+    @staticmethod
+    def packbits(grid, N, density_thresh, bitfield):
+        require_cuda(grid, bitfield)
+        check(lib().foc_packbits(ptr(grid), N, density_thresh, ptr(bitfield), stream()), "packbits")
+
+    @staticmethod
+    def march_rays_train(rays_o, rays_d, grid, bound, dt_gamma, max_steps, N, C, H, M, nears, fars, xyzs, dirs, deltas,
+                         rays, counter, noises):
+        require_cuda(rays_o, rays_d, grid, nears, fars, xyzs, dirs, deltas, rays, counter, noises)
+        scratch = torch.empty(max(1, lib().foc_march_rays_train_scratch_bytes(N)), dtype=torch.uint8, device=rays_o.device)
+        check(lib().foc_march_rays_train(ptr(rays_o), ptr(rays_d), ptr(grid), bound, dt_gamma, max_steps, N, C, H, M,
+                                         ptr(nears), ptr(fars), ptr(xyzs), ptr(dirs), ptr(deltas), ptr(rays), ptr(counter),
+                                         ptr(noises), ptr(scratch), stream()), "march_rays_train")
+
+    @staticmethod
+    def composite_rays_train_forward(sigmas, rgbs, deltas, rays, M, N, T_thresh, weights_sum, depth, image):
+        require_cuda(sigmas, rgbs, deltas, rays, weights_sum, depth, image)
+        check(lib().foc_composite_rays_train_forward(ptr(sigmas), ptr(rgbs), ptr(deltas), ptr(rays), M, N, T_thresh,
+                                                     ptr(weights_sum), ptr(depth), ptr(image), stream()),
+              "composite_rays_train_forward")
+
+    @staticmethod
+    def composite_rays_train_backward(grad_weights_sum, grad_image, sigmas, rgbs, deltas, rays, weights_sum, image, M, N,
+                                      T_thresh, grad_sigmas, grad_rgbs):
+        require_cuda(grad_weights_sum, grad_image, sigmas, rgbs, deltas, rays, weights_sum, image, grad_sigmas, grad_rgbs)
+        check(lib().foc_composite_rays_train_backward(ptr(grad_weights_sum), ptr(grad_image), ptr(sigmas), ptr(rgbs),
+                                                      ptr(deltas), ptr(rays), ptr(weights_sum), ptr(image), M, N, T_thresh,
+                                                      ptr(grad_sigmas), ptr(grad_rgbs), stream()),
+              "composite_rays_train_backward")
+
+    @staticmethod
+    def march_rays(n_alive, n_step, rays_alive, rays_t, rays_o, rays_d, bound, dt_gamma, max_steps, C, H, grid, nears, fars,
+                   xyzs, dirs, deltas, noises):
+        require_cuda(rays_alive, rays_t, rays_o, rays_d, grid, nears, fars, xyzs, dirs, deltas, noises)
+        check(lib().foc_march_rays(n_alive, n_step, ptr(rays_alive), ptr(rays_t), ptr(rays_o), ptr(rays_d), bound, dt_gamma,
+                                   max_steps, C, H, ptr(grid), ptr(nears), ptr(fars), ptr(xyzs), ptr(dirs), ptr(deltas),
+                                   ptr(noises), stream()), "march_rays")
+
+    @staticmethod
+    def composite_rays(n_alive, n_step, T_thresh, rays_alive, rays_t, sigmas, rgbs, deltas, weights_sum, depth, image):
+        require_cuda(rays_alive, rays_t, sigmas, rgbs, deltas, weights_sum, depth, image)
+        check(lib().foc_composite_rays(n_alive, n_step, T_thresh, ptr(rays_alive), ptr(rays_t), ptr(sigmas), ptr(rgbs),
+                                       ptr(deltas), ptr(weights_sum), ptr(depth), ptr(image), stream()), "composite_rays")
+
+    # ---- new entry points (no reference counterpart) ---------------------------------------------------------------
+    @staticmethod
+    def compact_alive(rays_alive, n, out, n_out):
+        require_cuda(rays_alive, out, n_out)
+        scratch = torch.empty(max(4, lib().foc_compact_alive_scratch_bytes(n)), dtype=torch.uint8, device=rays_alive.device)
+        check(lib().foc_compact_alive(ptr(rays_alive), n, ptr(out), ptr(n_out), ptr(scratch), stream()), "compact_alive")
+
+
+_backend = _Backend()

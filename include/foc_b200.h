@@ -84,17 +84,23 @@ int foc_composite_multi(const float *sigmas, const float *rgbs, const float *nea
 #define FOC_F32 0
 #define FOC_F16 1
 
+/* output / incoming-gradient layouts of the grid encoder: FOC_LBC is the reference kernel's [L,B,C];
+ * FOC_BLC is [B,L,C] = the [B, L*C] tensor the network consumes (saves the wrapper's permute+reshape copy, grid.py:57) */
+#define FOC_LBC 0
+#define FOC_BLC 1
+
 /* replaces grid_encode_forward, gridencoder.h:12 (gridencoder.cu:87-245). inputs [B,D] f32 in [0,1];
- * embeddings [n,C]; offsets [L+1] i32; outputs [L,B,C]; dy_dx [B,L*D*C] or NULL.  D in {2,3}, C in {1,2,4,8}. */
+ * embeddings [n,C]; offsets [L+1] i32; outputs [L,B,C] or [B,L,C] (layout); dy_dx [B,L*D*C] or NULL.
+ * D in {2,3}, C in {1,2,4,8}. */
 int foc_grid_encode_forward(const float *inputs, const void *embeddings, const int32_t *offsets, void *outputs,
                             uint32_t B, uint32_t D, uint32_t C, uint32_t L, float S, uint32_t H, void *dy_dx,
-                            uint32_t gridtype, int align_corners, uint32_t interp, int dtype, void *stream);
+                            uint32_t gridtype, int align_corners, uint32_t interp, int dtype, int layout, void *stream);
 /* replaces grid_encode_backward, gridencoder.h:13 (gridencoder.cu:248-369). grad [L,B,C]; grad_embeddings [n,C]
  * (accumulated into; caller zeroes); dy_dx/grad_inputs NULL or [B,L*D*C]/[B,D] (table dtype). */
 int foc_grid_encode_backward(const void *grad, const float *inputs, const void *embeddings, const int32_t *offsets,
                              void *grad_embeddings, uint32_t B, uint32_t D, uint32_t C, uint32_t L, float S,
                              uint32_t H, const void *dy_dx, void *grad_inputs, uint32_t gridtype, int align_corners,
-                             uint32_t interp, int dtype, void *stream);
+                             uint32_t interp, int dtype, int layout, void *stream);
 /* replaces grad_total_variation, gridencoder.h:15 (gridencoder.cu:506-645). fp32 only (grid.py:164). */
 int foc_grad_total_variation(const float *inputs, const float *embeddings, float *grad, const int32_t *offsets,
                              float weight, uint32_t B, uint32_t D, uint32_t C, uint32_t L, float S, uint32_t H,
