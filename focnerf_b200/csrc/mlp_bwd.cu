@@ -1,0 +1,371 @@
+// mlp_bwd.cu -- fused MLP backward on tcgen05/TMEM: activation-gradient chain AND all weight gradients in ONE kernel.
+//
+// Replaces K16 + K17 + K18-backward (ffmlp/src/ffmlp.cu:410-518, 580-628, 749-895): the reference runs one fused
+// dgrad kernel that materialises backward_buffer[num_layers, B, 64], then num_layers+1 CUTLASS split-K GEMMs on side
+// streams (fp16 accumulation) that re-read forward_buffer and backward_buffer.  Here each persistent CTA, per 128-row
+// batch tile:
+//   * TMA-loads the tile's stored activations A_0..A_{L-1} and inputs X (hardware swizzle), copies the [128,16] output
+//     gradient G into shared memory;
+//   * dgrad:  dA_{l-1} = dZ_l . W_l   as tcgen05.mma M=128 (K-major A = dZ tile, K-major B = W_l^T staged once per CTA);
+//             the epilogue drains TMEM, applies the activation derivative from the stored A_{l-1}, rounds to fp16
+//             (the reference's backward_buffer precision) and writes dZ_{l-1} back to shared memory;
+//   * wgrad:  dW_l += dZ_l^T . A_{l-1}  as tcgen05.mma M=64, K=128 batch rows, reading THE SAME shared-memory tiles as
+//             MN-major operands (a [rows=batch][64 features] swizzled tile is the canonical MN-major layout with
+//             K = batch), accumulating in fp32 TMEM columns that persist across all tiles of the CTA.
+// dZ never goes to HBM unless the caller asks for backward_buffer.  At the end every CTA stores its fp32 partial dW
+// and a small second kernel reduces the partials in a fixed order (deterministic) and narrows to fp16.
+#include "tc_common.cuh"
+
+using namespace foc;
+using namespace foc::tc;
+
+namespace {
+
+constexpr int kTile = 128, kHidden = 64, kOutPad = 16, kMaxLayers = 8;
+constexpr uint32_t kTileBytes = kTile * kHidden * 2;     // 16 KB: one [128, 64] fp16 tile
+
+// ffmlp/src/utils.h:537-582: derivative through the stored POST-activation value
+__device__ __forceinline__ float act_bwd(uint32_t a, float g, float fwd) {
+    switch (a) {
+        case 0: return fwd > 0.f ? g : 0.f;
+        case 1: return g * fwd;
+        case 3: return g * (fwd * (1.0f - fwd));
+        case 4: { const float y = fwd * 10.0f; return g * (y * y / (y * y + 1.0f)); }
+        case 5: return g * (1.0f - __expf(-fwd * 10.0f));
+        default: return g;
+    }
+}
+
+struct BwdParams {
+    const __half* grad;          // [B, 16]
+    const __half* weights;       // flat
+    __half* backward_buffer;     // [num_layers, B, 64] or nullptr
+    __half* grad_inputs;         // [B, IN] or nullptr
+    float* partials;             // [gridDim.x, num_params] fp32
+    uint32_t B, num_layers, activation, num_tiles, num_params, tmem_cols;
+};
+
+template <int IN>
+struct BwdSmem {
+    static constexpr uint32_t kXBytes = kTile * IN * 2;
+    __host__ __device__ static uint32_t off_act(int l) { return l * kTileBytes; }
+    __host__ __device__ static uint32_t off_x(int L) { return L * kTileBytes; }
+    __host__ __device__ static uint32_t off_gz(int L) { return off_x(L) + ((kXBytes + 1023u) & ~1023u); }
+    __host__ __device__ static uint32_t off_wt_out(int L) { return off_gz(L) + kTileBytes; }
+    __host__ __device__ static uint32_t off_wt_h(int L, int i) { return off_wt_out(L) + 8192u + i * 8192u; }      // i = l-1
+    __host__ __device__ static uint32_t off_wt_in(int L) { return off_wt_h(L, L - 1); }
+    __host__ __device__ static uint32_t off_bars(int L) { return off_wt_in(L) + IN * 128u; }
+    __host__ __device__ static uint32_t total(int L) { return off_bars(L) + 64 + 1024; }
+};
+
+template <int IN>
+__global__ void __launch_bounds__(128)
+k_mlp_bwd(const __grid_constant__ CUtensorMap tm_fb, const __grid_constant__ CUtensorMap tm_in, BwdParams p) {
+    using SM = BwdSmem<IN>;
+    extern __shared__ uint8_t smem_raw[];
+    uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~(uintptr_t)1023);
+    const int L = (int)p.num_layers, n_hmm = L - 1;
+    uint64_t* bars = reinterpret_cast<uint64_t*>(smem + SM::off_bars(L));
+    uint64_t* bar_ld = bars;
+    uint64_t* bar_mma = bars + 1;
+    uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(bars + 2);
+    const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+
+    if (threadIdx.x == 0) {
+        tma_prefetch_desc(&tm_fb); tma_prefetch_desc(&tm_in);
+        mbar_init(bar_ld, 1); mbar_init(bar_mma, 1);
+        fence_barrier_init();
+    }
+    if (warp == 0) tmem_alloc(tmem_slot, p.tmem_cols);
+
+    // ---- stage the TRANSPOSED weights once: B operand of dgrad is [N = fan-in j][K = fan-out o], K-major, SWIZZLE_128B
+    const size_t in_sz = (size_t)kHidden * IN, hh = (size_t)kHidden * kHidden;
+    {
+        const __half* W_out = p.weights + in_sz + (size_t)n_hmm * hh;            // [16, 64]
+        __half* dst = reinterpret_cast<__half*>(smem + SM::off_wt_out(L));
+        for (uint32_t idx = threadIdx.x; idx < kOutPad * kHidden; idx += blockDim.x) {
+            const uint32_t o = idx / kHidden, j = idx % kHidden;
+            dst[(sw128_off(j, o >> 3) >> 1) + (o & 7u)] = __ldg(W_out + idx);
+        }
+        for (int l = 1; l <= n_hmm; ++l) {
+            const __half* W = p.weights + in_sz + (size_t)(l - 1) * hh;          // W_l [64 o, 64 j]
+            __half* d = reinterpret_cast<__half*>(smem + SM::off_wt_h(L, l - 1));
+            for (uint32_t idx = threadIdx.x; idx < kHidden * kHidden; idx += blockDim.x) {
+                const uint32_t o = idx / kHidden, j = idx % kHidden;
+                d[(sw128_off(j, o >> 3) >> 1) + (o & 7u)] = __ldg(W + idx);
+            }
+        }
+        if (p.grad_inputs) {
+            __half* d = reinterpret_cast<__half*>(smem + SM::off_wt_in(L));      // [N = IN i][K = 64 o]
+            for (uint32_t idx = threadIdx.x; idx < kHidden * IN; idx += blockDim.x) {
+                const uint32_t o = idx / IN, i = idx % IN;
+                d[(sw128_off(i, o >> 3) >> 1) + (o & 7u)] = __ldg(p.weights + idx);
+            }
+        }
+    }
+    fence_proxy_async_smem();
+    tc_fence_before();
+    __syncthreads();
+    tc_fence_after();
+    const uint32_t tmem = *tmem_slot;
+
+    // TMEM columns: [0,64) dgrad D | dW_0 (IN) | dW_1..dW_{L-1} (64 each) | dW_L^T (16)
+    const uint32_t col_dw0 = 64, col_dwh0 = 64 + IN, col_dwout = 64 + IN + 64 * (uint32_t)n_hmm;
+    constexpr uint32_t id_dgrad_h = umma_idesc_f16(128, 64, 0, 0), id_dgrad_in = umma_idesc_f16(128, IN, 0, 0);
+    constexpr uint32_t id_wg_h = umma_idesc_f16(64, 64, 1, 1), id_wg_in = umma_idesc_f16(64, IN, 1, 1), id_wg_out = umma_idesc_f16(64, 16, 1, 1);
+    constexpr uint32_t kXSwz = IN == 32 ? SWZ_64B : SWZ_128B, kXSbo = IN == 32 ? 512u : 1024u, kXk16 = IN == 32 ? 1024u : 2048u;
+    const uint32_t s_gz = smem_u32(smem + SM::off_gz(L));
+    const uint32_t row = (uint32_t)(warp * 32 + lane);
+    const uint32_t t_lane = tmem + ((uint32_t)(warp * 32) << 16);
+    uint32_t ld_phase = 0, mma_phase = 0, acc_w = 0;      // acc_w: 0 on the CTA's first tile (overwrite), 1 afterwards
+
+    for (uint32_t tile = blockIdx.x; tile < p.num_tiles; tile += gridDim.x) {
+        const size_t grow = (size_t)tile * kTile + row;
+        if (threadIdx.x == 0) {
+            mbar_expect_tx(bar_ld, (uint32_t)L * kTileBytes + SM::kXBytes);
+            for (int l = 0; l < L; ++l)
+                tma_load_2d(smem + SM::off_act(l), &tm_fb, bar_ld, 0, (int32_t)((size_t)l * p.B + (size_t)tile * kTile));
+            tma_load_2d(smem + SM::off_x(L), &tm_in, bar_ld, 0, (int32_t)(tile * kTile));
+        }
+        {   // G tile: this thread's row, 16 halfs = 2 chunks, into the 128-byte-pitch swizzled layout
+            const uint4* g = reinterpret_cast<const uint4*>(p.grad + grow * kOutPad);
+            const uint4 g0 = __ldg(g), g1 = __ldg(g + 1);
+            *reinterpret_cast<uint4*>(smem + SM::off_gz(L) + sw128_off(row, 0)) = g0;
+            *reinterpret_cast<uint4*>(smem + SM::off_gz(L) + sw128_off(row, 1)) = g1;
+        }
+        fence_proxy_async_smem();
+        tc_fence_before();
+        __syncthreads();
+        if (threadIdx.x == 0) {
+            mbar_wait(bar_ld, ld_phase);
+            tc_fence_after();
+            // dA_{L-1} = G . W_L  (K = 16)
+            umma_f16(tmem, umma_desc(s_gz, 16, 1024, SWZ_128B), umma_desc(smem_u32(smem + SM::off_wt_out(L)), 16, 1024, SWZ_128B), id_dgrad_h, 0);
+            // dW_L^T [64 j, 16 o] += A_{L-1}^T . G  (K = 128 batch rows)
+            const uint32_t s_a = smem_u32(smem + SM::off_act(L - 1));
+            #pragma unroll
+            for (int k = 0; k < kTile / 16; ++k)
+                umma_f16(tmem + col_dwout, umma_desc(s_a + k * 2048, 16, 1024, SWZ_128B), umma_desc(s_gz + k * 2048, 16, 1024, SWZ_128B),
+                         id_wg_out, acc_w | (k > 0));
+            umma_commit(bar_mma);
+        }
+        // every thread reads the TMA-written activation tiles with generic loads below, so every thread must itself
+        // observe the load barrier's phase (acquire), not just the MMA-issuing thread
+        mbar_wait(bar_ld, ld_phase);
+        ld_phase ^= 1u;
+
+        for (int l = L - 1; l >= 0; --l) {
+            // ---- epilogue: dZ_l = dA_l (.) act'(A_l)  -> fp16 -> GZ tile
+            mbar_wait(bar_mma, mma_phase); mma_phase ^= 1u;
+            tc_fence_after();
+            uint32_t acc[4][16];
+            #pragma unroll
+            for (int q = 0; q < 4; ++q) tmem_ld16(t_lane + q * 16, acc[q]);
+            uint4 fw[8];
+            #pragma unroll
+            for (int c = 0; c < 8; ++c) fw[c] = *reinterpret_cast<const uint4*>(smem + SM::off_act(l) + sw128_off(row, c));
+            tmem_ld_wait();
+            uint4 packed[8];
+            #pragma unroll
+            for (int c = 0; c < 8; ++c) {
+                const uint32_t f[4] = {fw[c].x, fw[c].y, fw[c].z, fw[c].w};
+                uint32_t w[4];
+                #pragma unroll
+                for (int j = 0; j < 4; ++j) {
+                    const int col = c * 8 + j * 2;
+                    const float2 a = __half22float2(*reinterpret_cast<const __half2*>(&f[j]));
+                    // the reference keeps dA in fp16 fragments before the activation transfer (ffmlp.cu:459-470)
+                    const float g0 = __half2float(__float2half_rn(__uint_as_float(acc[col >> 4][col & 15])));
+                    const float g1 = __half2float(__float2half_rn(__uint_as_float(acc[(col + 1) >> 4][(col + 1) & 15])));
+                    const __half2 h = __floats2half2_rn(act_bwd(p.activation, g0, a.x), act_bwd(p.activation, g1, a.y));
+                    w[j] = *reinterpret_cast<const uint32_t*>(&h);
+                }
+                packed[c] = make_uint4(w[0], w[1], w[2], w[3]);
+            }
+            #pragma unroll
+            for (int c = 0; c < 8; ++c) *reinterpret_cast<uint4*>(smem + SM::off_gz(L) + sw128_off(row, c)) = packed[c];
+            if (p.backward_buffer) {
+                uint4* dst = reinterpret_cast<uint4*>(p.backward_buffer + ((size_t)(L - 1 - l) * p.B + grow) * kHidden);
+                #pragma unroll
+                for (int c = 0; c < 8; ++c) dst[c] = packed[c];
+            }
+            fence_proxy_async_smem();
+            tc_fence_before();
+            __syncthreads();
+            if (threadIdx.x == 0) {
+                tc_fence_after();
+                if (l > 0) {
+                    const uint32_t s_prev = smem_u32(smem + SM::off_act(l - 1));
+                    #pragma unroll
+                    for (int k = 0; k < kTile / 16; ++k)       // dW_l [64 o, 64 j] += dZ_l^T . A_{l-1}
+                        umma_f16(tmem + col_dwh0 + 64u * (uint32_t)(l - 1), umma_desc(s_gz + k * 2048, 16, 1024, SWZ_128B),
+                                 umma_desc(s_prev + k * 2048, 16, 1024, SWZ_128B), id_wg_h, acc_w | (k > 0));
+                    const uint32_t s_wt = smem_u32(smem + SM::off_wt_h(L, l - 1));
+                    #pragma unroll
+                    for (int k = 0; k < kHidden / 16; ++k)     // dA_{l-1} = dZ_l . W_l
+                        umma_f16(tmem, umma_desc(s_gz + k * 32, 16, 1024, SWZ_128B), umma_desc(s_wt + k * 32, 16, 1024, SWZ_128B), id_dgrad_h, k > 0);
+                } else {
+                    const uint32_t s_x = smem_u32(smem + SM::off_x(L));
+                    #pragma unroll
+                    for (int k = 0; k < kTile / 16; ++k)       // dW_0 [64 o, IN] += dZ_0^T . X
+                        umma_f16(tmem + col_dw0, umma_desc(s_gz + k * 2048, 16, 1024, SWZ_128B), umma_desc(s_x + k * kXk16, 16, kXSbo, kXSwz),
+                                 id_wg_in, acc_w | (k > 0));
+                    if (p.grad_inputs) {
+                        const uint32_t s_wt = smem_u32(smem + SM::off_wt_in(L));
+                        #pragma unroll
+                        for (int k = 0; k < kHidden / 16; ++k) // dX = dZ_0 . W_0
+                            umma_f16(tmem, umma_desc(s_gz + k * 32, 16, 1024, SWZ_128B), umma_desc(s_wt + k * 32, 16, 1024, SWZ_128B), id_dgrad_in, k > 0);
+                    }
+                }
+                umma_commit(bar_mma);
+            }
+        }
+        // ---- all MMAs of this tile done: optional dX epilogue; shared-memory tiles become free for the next TMA
+        mbar_wait(bar_mma, mma_phase); mma_phase ^= 1u;
+        tc_fence_after();
+        if (p.grad_inputs) {
+            uint32_t gi[IN / 16][16];
+            #pragma unroll
+            for (int q = 0; q < IN / 16; ++q) tmem_ld16(t_lane + q * 16, gi[q]);
+            tmem_ld_wait();
+            uint4* dst = reinterpret_cast<uint4*>(p.grad_inputs + grow * IN);
+            #pragma unroll
+            for (int c = 0; c < IN / 8; ++c) {
+                uint32_t w[4];
+                #pragma unroll
+                for (int j = 0; j < 4; ++j) {
+                    const int col = c * 8 + j * 2;
+                    const __half2 h = __floats2half2_rn(__uint_as_float(gi[col >> 4][col & 15]), __uint_as_float(gi[(col + 1) >> 4][(col + 1) & 15]));
+                    w[j] = *reinterpret_cast<const uint32_t*>(&h);
+                }
+                dst[c] = make_uint4(w[0], w[1], w[2], w[3]);
+            }
+        }
+        tc_fence_before();
+        __syncthreads();
+        acc_w = 1;
+    }
+
+    // ---- flush this CTA's fp32 weight-gradient partials.  M = 64 accumulators live in lanes {0-15, 32-47, 64-79, 96-111}:
+    // row (16 * warp + lane) for lane < 16.
+    float* part = p.partials + (size_t)blockIdx.x * p.num_params;
+    const bool has_row = lane < 16;
+    const uint32_t orow = (uint32_t)(warp * 16 + lane);
+    const bool worked = blockIdx.x < p.num_tiles;
+    {   // dW_0 [64, IN]
+        #pragma unroll
+        for (int q = 0; q < IN / 16; ++q) {
+            uint32_t v[16];
+            tmem_ld16(t_lane + col_dw0 + q * 16, v);
+            tmem_ld_wait();
+            if (has_row) {
+                float4* d = reinterpret_cast<float4*>(part + (size_t)orow * IN + q * 16);
+                #pragma unroll
+                for (int j = 0; j < 4; ++j)
+                    d[j] = worked ? make_float4(__uint_as_float(v[4 * j]), __uint_as_float(v[4 * j + 1]), __uint_as_float(v[4 * j + 2]), __uint_as_float(v[4 * j + 3]))
+                                  : make_float4(0.f, 0.f, 0.f, 0.f);
+            }
+        }
+    }
+    for (int l = 1; l <= n_hmm; ++l) {      // dW_l [64, 64]
+        #pragma unroll
+        for (int q = 0; q < 4; ++q) {
+            uint32_t v[16];
+            tmem_ld16(t_lane + col_dwh0 + 64u * (uint32_t)(l - 1) + q * 16, v);
+            tmem_ld_wait();
+            if (has_row) {
+                float4* d = reinterpret_cast<float4*>(part + in_sz + (size_t)(l - 1) * hh + (size_t)orow * kHidden + q * 16);
+                #pragma unroll
+                for (int j = 0; j < 4; ++j)
+                    d[j] = worked ? make_float4(__uint_as_float(v[4 * j]), __uint_as_float(v[4 * j + 1]), __uint_as_float(v[4 * j + 2]), __uint_as_float(v[4 * j + 3]))
+                                  : make_float4(0.f, 0.f, 0.f, 0.f);
+            }
+        }
+    }
+    {   // dW_L^T [64 j, 16 o] -> dW_L [16 o, 64 j]
+        uint32_t v[16];
+        tmem_ld16(t_lane + col_dwout, v);
+        tmem_ld_wait();
+        if (has_row) {
+            float* d = part + in_sz + (size_t)n_hmm * hh;
+            #pragma unroll
+            for (int o = 0; o < 16; ++o) d[(size_t)o * kHidden + orow] = worked ? __uint_as_float(v[o]) : 0.f;
+        }
+    }
+    tc_fence_before();
+    __syncthreads();
+    if (warp == 0) tmem_dealloc(tmem, p.tmem_cols);
+}
+
+// fixed-order reduction of the per-CTA partials, narrowed to fp16 (the reference's grad_weights dtype)
+__global__ void __launch_bounds__(256)
+k_mlp_wgrad_finish(const float* __restrict__ partials, uint32_t n_cta, uint32_t num_params, __half* __restrict__ grad_weights) {
+    const uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= num_params) return;
+    float s = 0.f;
+    for (uint32_t c = 0; c < n_cta; ++c) s += __ldg(partials + (size_t)c * num_params + i);
+    grad_weights[i] = __float2half_rn(s);
+}
+
+uint32_t bwd_grid(uint32_t B) {
+    const uint32_t tiles = B / kTile, cap = (uint32_t)kNumSMs * 2u;
+    return tiles < cap ? tiles : cap;
+}
+uint32_t num_params_of(uint32_t input_dim, uint32_t num_layers) { return kHidden * (input_dim + kHidden * (num_layers - 1) + kOutPad); }
+
+template <int IN>
+int launch_bwd(const uint16_t* grad, const uint16_t* inputs, const uint16_t* weights, const uint16_t* forward_buffer, uint32_t B,
+               uint32_t num_layers, uint32_t activation, int calc_grad_inputs, uint16_t* backward_buffer, uint16_t* grad_inputs,
+               uint16_t* grad_weights, void* scratch, cudaStream_t st) {
+    using SM = BwdSmem<IN>;
+    CUtensorMap tm_fb, tm_in;
+    int rc = make_tmap_f16_2d(&tm_fb, forward_buffer, (uint64_t)num_layers * B, kHidden, kTile, kHidden);
+    if (rc) return rc;
+    rc = make_tmap_f16_2d(&tm_in, inputs, B, IN, kTile, IN);
+    if (rc) return rc;
+    const uint32_t smem = SM::total((int)num_layers);
+    if (smem > 227 * 1024) return FOC_ERR_UNSUPPORTED;
+    static bool attr_set = false;
+    if (!attr_set) {
+        cudaError_t e = cudaFuncSetAttribute(k_mlp_bwd<IN>, cudaFuncAttributeMaxDynamicSharedMemorySize, 227 * 1024);
+        if (e != cudaSuccess) return (int)e;
+        attr_set = true;
+    }
+    BwdParams p;
+    p.grad = reinterpret_cast<const __half*>(grad);
+    p.weights = reinterpret_cast<const __half*>(weights);
+    p.backward_buffer = reinterpret_cast<__half*>(backward_buffer);
+    p.grad_inputs = calc_grad_inputs ? reinterpret_cast<__half*>(grad_inputs) : nullptr;
+    p.partials = static_cast<float*>(scratch);
+    p.B = B; p.num_layers = num_layers; p.activation = activation; p.num_tiles = B / kTile;
+    p.num_params = num_params_of(IN, num_layers);
+    const uint32_t need = 64 + IN + 64 * (num_layers - 1) + 16;
+    p.tmem_cols = need <= 128 ? 128 : need <= 256 ? 256 : 512;
+    if (need > 512) return FOC_ERR_UNSUPPORTED;
+    const uint32_t grid = bwd_grid(B);
+    k_mlp_bwd<IN><<<grid, 128, smem, st>>>(tm_fb, tm_in, p);
+    FOC_LAUNCH_CHECK();
+    k_mlp_wgrad_finish<<<ceil_div(p.num_params, 256), 256, 0, st>>>(p.partials, grid, p.num_params, reinterpret_cast<__half*>(grad_weights));
+    FOC_LAUNCH_CHECK(); return 0;
+}
+
+}  // namespace
+
+FOC_API size_t foc_ffmlp_backward_scratch_bytes(uint32_t B, uint32_t input_dim, uint32_t hidden_dim, uint32_t num_layers) {
+    if (hidden_dim != (uint32_t)kHidden || B % kTile != 0 || num_layers < 1) return 0;
+    return (size_t)bwd_grid(B) * num_params_of(input_dim, num_layers) * sizeof(float);
+}
+
+FOC_API int foc_ffmlp_backward(const uint16_t* grad, const uint16_t* inputs, const uint16_t* weights, const uint16_t* forward_buffer,
+                               uint32_t B, uint32_t input_dim, uint32_t output_dim, uint32_t hidden_dim, uint32_t num_layers,
+                               uint32_t activation, uint32_t output_activation, int calc_grad_inputs, uint16_t* backward_buffer,
+                               uint16_t* grad_inputs, uint16_t* grad_weights, void* scratch, void* stream) {
+    if (B == 0) return 0;
+    // output activation is always `none` in the reference module (ffmlp.py:108); activation 2 (sine) has no stored-value derivative
+    if (hidden_dim != (uint32_t)kHidden || output_dim != (uint32_t)kOutPad || num_layers < 1 || num_layers > (uint32_t)kMaxLayers ||
+        B % kTile != 0 || output_activation != 6 || activation == 2 || !scratch) return FOC_ERR_UNSUPPORTED;
+    cudaStream_t st = reinterpret_cast<cudaStream_t>(stream);
+    if (input_dim == 32) return launch_bwd<32>(grad, inputs, weights, forward_buffer, B, num_layers, activation, calc_grad_inputs, backward_buffer, grad_inputs, grad_weights, scratch, st);
+    if (input_dim == 64) return launch_bwd<64>(grad, inputs, weights, forward_buffer, B, num_layers, activation, calc_grad_inputs, backward_buffer, grad_inputs, grad_weights, scratch, st);
+    return FOC_ERR_UNSUPPORTED;
+}
