@@ -19,8 +19,11 @@ __device__ __forceinline__ void mbar_expect_tx(uint64_t* bar, uint32_t bytes) {
 }
 __device__ __forceinline__ void mbar_wait(uint64_t* bar, uint32_t parity) {
     const uint32_t addr = smem_u32(bar);
-    uint32_t done;
+    uint32_t done, spins = 0;
     do {
+        // a barrier that never completes is a programming error (wrong tx count / descriptor): fail with a CUDA error
+        // after ~seconds instead of hanging the device
+        if (++spins > (1u << 24)) __trap();
         asm volatile(
             "{\n\t"
             ".reg .pred p;\n\t"

@@ -1,0 +1,158 @@
+"""`ffmlp.FFMLP` and `ffmlp_forward` of the reference (ffmlp/ffmlp.py:15-169) over the tcgen05/TMEM kernels.
+
+Kept: constructor + assertions, the flat fp32 `weights` Parameter and its layout ([hidden,in] + (L-1)x[hidden,hidden]
++ [16,hidden], ffmlp.cu:632), `reset_parameters` (reseeds the global RNG with 42, ffmlp.py:141-144), the batch padding
+that always appends 1..128 zero rows (ffmlp.py:157-159), `custom_fwd(cast_inputs=torch.half)`, `__repr__`, and the
+`_backend` method names (ffmlp/src/bindings.cpp:5-11).  Not imported: `turtle` (ffmlp.py:2, needs tkinter).
+
+Differences, on purpose: `backward_buffer` is not materialised (the kernel keeps dL/dact in shared memory and reduces
+the weight gradients itself); `allocate_splitk/free_splitk` are no-ops; only hidden_dim == 64 and input_dim in
+{32, 64} are implemented by the sm_100a kernels (the FOC field networks) -- other shapes raise RuntimeError.
+"""
+import math
+
+import torch
+import torch.nn as nn
+from torch.autograd import Function
+from torch.amp import custom_bwd, custom_fwd
+
+from .._lib import check, lib, ptr, require_cuda, stream
+
+
+def _chk_half(t, name):
+    if t is None:
+        return
+    if not t.is_cuda or not t.is_contiguous() or t.dtype != torch.float16:
+        raise RuntimeError(f"{name} must be a contiguous CUDA half tensor")
+
+
+class _Backend:
+    @staticmethod
+    def ffmlp_forward(inputs, weights, B, input_dim, output_dim, hidden_dim, num_layers, activation, output_activation,
+                      forward_buffer, outputs):
+        _chk_half(inputs, "inputs"); _chk_half(weights, "weights"); _chk_half(forward_buffer, "forward_buffer"); _chk_half(outputs, "outputs")
+        check(lib().foc_ffmlp_forward(ptr(inputs), ptr(weights), B, input_dim, output_dim, hidden_dim, num_layers, activation,
+                                      output_activation, ptr(forward_buffer), ptr(outputs), stream()), "ffmlp_forward")
+
+    @staticmethod
+    def ffmlp_inference(inputs, weights, B, input_dim, output_dim, hidden_dim, num_layers, activation, output_activation,
+                        inference_buffer, outputs):
+        # inference_buffer ([B, hidden], ffmlp.py:40) is accepted for signature compatibility and left untouched:
+        # activations stay in shared memory / TMEM.
+        _chk_half(inputs, "inputs"); _chk_half(weights, "weights"); _chk_half(outputs, "outputs")
+        check(lib().foc_ffmlp_forward(ptr(inputs), ptr(weights), B, input_dim, output_dim, hidden_dim, num_layers, activation,
+                                      output_activation, None, ptr(outputs), stream()), "ffmlp_inference")
+
+    @staticmethod
+    def ffmlp_backward(grad, inputs, weights, forward_buffer, B, input_dim, output_dim, hidden_dim, num_layers, activation,
+                       output_activation, calc_grad_inputs, backward_buffer, grad_inputs, grad_weights):
+        _chk_half(grad, "grad"); _chk_half(inputs, "inputs"); _chk_half(weights, "weights"); _chk_half(forward_buffer, "forward_buffer")
+        _chk_half(backward_buffer, "backward_buffer"); _chk_half(grad_weights, "grad_weights")
+        if calc_grad_inputs:
+            _chk_half(grad_inputs, "grad_inputs")
+        nbytes = lib().foc_ffmlp_backward_scratch_bytes(B, input_dim, hidden_dim, num_layers)
+        if nbytes == 0:
+            raise RuntimeError("ffmlp_backward: unsupported configuration for the sm_100a kernels")
+        scratch = torch.empty(nbytes, dtype=torch.uint8, device=grad.device)
+        check(lib().foc_ffmlp_backward(ptr(grad), ptr(inputs), ptr(weights), ptr(forward_buffer), B, input_dim, output_dim,
+                                       hidden_dim, num_layers, activation, output_activation, int(bool(calc_grad_inputs)),
+                                       ptr(backward_buffer), ptr(grad_inputs) if calc_grad_inputs else None, ptr(grad_weights),
+                                       ptr(scratch), stream()), "ffmlp_backward")
+
+    @staticmethod
+    def allocate_splitk(size):
+        check(lib().foc_allocate_splitk(size), "allocate_splitk")
+
+    @staticmethod
+    def free_splitk():
+        check(lib().foc_free_splitk(), "free_splitk")
+
+
+_backend = _Backend()
+
+
+class _ffmlp_forward(Function):
+    @staticmethod
+    @custom_fwd(device_type="cuda", cast_inputs=torch.half)
+    def forward(ctx, inputs, weights, input_dim, output_dim, hidden_dim, num_layers, activation, output_activation,
+                inference=False, calc_grad_inputs=False):
+        require_cuda(inputs, weights)
+        B = inputs.shape[0]
+        inputs, weights = inputs.contiguous(), weights.contiguous()
+        outputs = torch.empty(B, output_dim, device=inputs.device, dtype=inputs.dtype)
+        if not inference:
+            forward_buffer = torch.empty(num_layers, B, hidden_dim, device=inputs.device, dtype=inputs.dtype)
+            _backend.ffmlp_forward(inputs, weights, B, input_dim, output_dim, hidden_dim, num_layers, activation,
+                                   output_activation, forward_buffer, outputs)
+            ctx.save_for_backward(inputs, weights, outputs, forward_buffer)
+            ctx.dims = (input_dim, output_dim, hidden_dim, num_layers, activation, output_activation, calc_grad_inputs)
+        else:
+            _backend.ffmlp_inference(inputs, weights, B, input_dim, output_dim, hidden_dim, num_layers, activation,
+                                     output_activation, None, outputs)
+        return outputs
+
+    @staticmethod
+    @custom_bwd(device_type="cuda")
+    def backward(ctx, grad):
+        B = grad.shape[0]
+        grad = grad.contiguous()
+        inputs, weights, outputs, forward_buffer = ctx.saved_tensors
+        input_dim, output_dim, hidden_dim, num_layers, activation, output_activation, calc_grad_inputs = ctx.dims
+        grad_inputs = torch.empty_like(inputs) if calc_grad_inputs else None
+        grad_weights = torch.empty_like(weights)              # fully overwritten by the reduction kernel
+        _backend.ffmlp_backward(grad, inputs, weights, forward_buffer, B, input_dim, output_dim, hidden_dim, num_layers,
+                                activation, output_activation, calc_grad_inputs, None, grad_inputs, grad_weights)
+        return (grad_inputs if calc_grad_inputs else None), grad_weights, None, None, None, None, None, None, None, None
+
+
+ffmlp_forward = _ffmlp_forward.apply
+
+
+def convert_activation(act):
+    return {'relu': 0, 'exponential': 1, 'sine': 2, 'sigmoid': 3, 'squareplus': 4, 'softplus': 5}.get(act, 6)
+
+
+class FFMLP(nn.Module):
+    def __init__(self, input_dim, output_dim, hidden_dim, num_layers, activation='relu'):
+        super().__init__()
+        self.input_dim = input_dim
+        self.output_dim = output_dim
+        self.hidden_dim = hidden_dim
+        self.num_layers = num_layers
+        self.activation = convert_activation(activation)
+        self.output_activation = convert_activation('none')     # not supported by the reference either (ffmlp.py:108)
+        self.tensorcore_width = 16
+
+        assert hidden_dim in [16, 32, 64, 128, 256], f"FFMLP only support hidden_dim in [16, 32, 64, 128, 256], but got {hidden_dim}"
+        assert input_dim > 0 and input_dim % 16 == 0, f"FFMLP input_dim should be 16 * m (m  > 0), but got {input_dim}"
+        assert output_dim <= 16, f"FFMLP current only supports output dim <= 16, but got {output_dim}"
+        assert num_layers >= 2, f"FFMLP num_layers should be larger than 2 (3 matmuls), but got {num_layers}"
+
+        self.padded_output_dim = int(math.ceil(output_dim / 16)) * 16
+        self.num_parameters = hidden_dim * (input_dim + hidden_dim * (num_layers - 1) + self.padded_output_dim)
+        self.weights = nn.Parameter(torch.zeros(self.num_parameters))
+        self.reset_parameters()
+        _backend.allocate_splitk(self.num_layers + 1)
+
+    def cleanup(self):
+        _backend.free_splitk()
+
+    def __repr__(self):
+        return (f"FFMLP: input_dim={self.input_dim} output_dim={self.output_dim} hidden_dim={self.hidden_dim} "
+                f"num_layers={self.num_layers} activation={self.activation}")
+
+    def reset_parameters(self):
+        torch.manual_seed(42)
+        std = math.sqrt(3 / self.hidden_dim)
+        self.weights.data.uniform_(-std, std)
+
+    def forward(self, inputs):
+        B, C = inputs.shape
+        pad = 128 - (B % 128)                                   # always pads, by a full 128 when B % 128 == 0 (ffmlp.py:157)
+        if pad > 0:
+            inputs = torch.cat([inputs, torch.zeros(pad, C, dtype=inputs.dtype, device=inputs.device)], dim=0)
+        outputs = ffmlp_forward(inputs, self.weights, self.input_dim, self.padded_output_dim, self.hidden_dim, self.num_layers,
+                                self.activation, self.output_activation, not self.training, inputs.requires_grad)
+        if B != outputs.shape[0] or self.padded_output_dim != self.output_dim:
+            outputs = outputs[:B, :self.output_dim]
+        return outputs

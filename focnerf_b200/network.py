@@ -1,0 +1,63 @@
+"""Field network with the wiring of the reference's nerf/network_ff.py:10-149 (hash grid -> FFMLP sigma net -> trunc_exp;
+SH-4 directions + 15 geo features + 1 zero pad -> FFMLP colour net -> sigmoid), as a plain nn.Module (the reference
+class also IS its renderer by inheritance; here rendering lives in trainer.py).  Parameter names match the reference
+(`encoder.embeddings`, `sigma_net.weights`, `color_net.weights`) so state_dicts interchange."""
+import torch
+import torch.nn as nn
+
+from .activation import trunc_exp
+from .encoding import get_encoder
+from .ffmlp import FFMLP
+
+
+class NeRFNetwork(nn.Module):
+    def __init__(self, encoding="hashgrid", encoding_dir="sphere_harmonics", num_layers=2, hidden_dim=64, geo_feat_dim=15,
+                 num_layers_color=3, hidden_dim_color=64, bound=1, **kwargs):
+        super().__init__()
+        self.bound = bound
+        self.num_layers, self.hidden_dim, self.geo_feat_dim = num_layers, hidden_dim, geo_feat_dim
+        self.encoder, self.in_dim = get_encoder(encoding, desired_resolution=2048 * bound)
+        self.sigma_net = FFMLP(input_dim=self.in_dim, output_dim=1 + self.geo_feat_dim, hidden_dim=self.hidden_dim,
+                               num_layers=self.num_layers)
+        self.num_layers_color, self.hidden_dim_color = num_layers_color, hidden_dim_color
+        self.encoder_dir, self.in_dim_color = get_encoder(encoding_dir)
+        self.in_dim_color += self.geo_feat_dim + 1                  # padded to 32 (network_ff.py:42)
+        self.color_net = FFMLP(input_dim=self.in_dim_color, output_dim=3, hidden_dim=self.hidden_dim_color,
+                               num_layers=self.num_layers_color)
+
+    def forward(self, x, d):
+        x = self.encoder(x, bound=self.bound)
+        h = self.sigma_net(x)
+        sigma = trunc_exp(h[..., 0])
+        geo_feat = h[..., 1:]
+        d = self.encoder_dir(d)
+        p = torch.zeros_like(geo_feat[..., :1])
+        h = torch.cat([d.to(geo_feat.dtype), geo_feat, p], dim=-1)
+        h = self.color_net(h)
+        rgb = torch.sigmoid(h)
+        return sigma, rgb
+
+    def density(self, x):
+        x = self.encoder(x, bound=self.bound)
+        h = self.sigma_net(x)
+        return {'sigma': trunc_exp(h[..., 0]), 'geo_feat': h[..., 1:]}
+
+    def color(self, x, d, mask=None, geo_feat=None, **kwargs):
+        """Masked colour evaluation (network_ff.py:92-123): rgb is 0 where mask is False."""
+        if mask is not None:
+            rgbs = torch.zeros(mask.shape[0], 3, dtype=x.dtype, device=x.device)
+            if not mask.any():
+                return rgbs
+            x, d, geo_feat = x[mask], d[mask], geo_feat[mask]
+        d = self.encoder_dir(d)
+        p = torch.zeros_like(geo_feat[..., :1])
+        h = torch.cat([d.to(geo_feat.dtype), geo_feat, p], dim=-1)
+        h = torch.sigmoid(self.color_net(h))
+        if mask is not None:
+            rgbs[mask] = h.to(rgbs.dtype)
+            return rgbs
+        return h
+
+    def get_params(self, lr):
+        return [{'params': self.encoder.parameters(), 'lr': lr}, {'params': self.sigma_net.parameters(), 'lr': lr},
+                {'params': self.encoder_dir.parameters(), 'lr': lr}, {'params': self.color_net.parameters(), 'lr': lr}]

@@ -1,0 +1,120 @@
+"""Train step and render loop of the cuda_ray path, restating `NeRFRenderer.run_cuda`
+(legacy/nerf/renderer.py:256-377 -- the working copy) and the optimisation step of
+legacy/nerf/utils.py:468-560, 863-868 (fp16 autocast, MSE, GradScaler, Adam(betas=(0.9,0.99), eps=1e-15)).
+
+This is the repo's public API for the hot path (bench.py's `e2e` goes through `Trainer.train_step_host`); the operators
+it calls are the same ones the reference's unchanged renderer reaches through `focnerf_b200.install_aliases()`.
+"""
+import torch
+
+from . import raymarching
+from .network import NeRFNetwork
+
+
+class Trainer:
+    def __init__(self, bound=1.0, density_grid=None, density_thresh=10.0, min_near=0.2, dt_gamma=0.0, max_steps=1024,
+                 lr=1e-2, fp16=True, device="cuda", grid_size=128, seed=0):
+        if not torch.cuda.is_available():
+            raise RuntimeError("focnerf_b200.Trainer needs a CUDA device (there is no CPU path)")
+        import math
+        torch.manual_seed(seed)
+        self.device = torch.device(device)
+        self.bound, self.min_near, self.dt_gamma, self.max_steps = float(bound), min_near, dt_gamma, max_steps
+        self.cascade = 1 + math.ceil(math.log2(bound))
+        self.grid_size, self.fp16 = grid_size, fp16
+        self.model = NeRFNetwork(bound=bound).to(self.device)
+        self.aabb = torch.tensor([-bound, -bound, -bound, bound, bound, bound], dtype=torch.float32, device=self.device)
+        self.density_bitfield = torch.zeros(self.cascade * grid_size ** 3 // 8, dtype=torch.uint8, device=self.device)
+        if density_grid is not None:
+            self.set_density_grid(density_grid, density_thresh)
+        self.step_counter = torch.zeros(16, 2, dtype=torch.int32, device=self.device)     # renderer.py:96-98
+        self.mean_count, self.local_step = 0, 0
+        self.optimizer = torch.optim.Adam(self.model.get_params(lr), betas=(0.9, 0.99), eps=1e-15, fused=True)
+        self.scaler = torch.amp.GradScaler("cuda", enabled=fp16)
+
+    def set_density_grid(self, density_grid, density_thresh=10.0):
+        """density_grid [cascade, H^3] (Morton order) -> bitfield, as update_extra_state does (renderer.py:529-531)."""
+        g = density_grid.to(self.device, torch.float32).contiguous()
+        thresh = min(float(g.clamp(min=0).mean()), density_thresh)
+        raymarching.packbits(g, thresh, self.density_bitfield)
+
+    # ------------------------------------------------------------------------------------------------ training
+    def render_train(self, rays_o, rays_d, bg_color=1.0, perturb=True, force_all_rays=False):
+        """run_cuda, training branch (legacy/nerf/renderer.py:268-319)."""
+        nears, fars = raymarching.near_far_from_aabb(rays_o, rays_d, self.aabb, self.min_near)
+        counter = self.step_counter[self.local_step % 16]
+        counter.zero_()
+        self.local_step += 1
+        xyzs, dirs, deltas, rays = raymarching.march_rays_train(
+            rays_o, rays_d, self.bound, self.density_bitfield, self.cascade, self.grid_size, nears, fars, counter,
+            self.mean_count, perturb, 128, force_all_rays, self.dt_gamma, self.max_steps)
+        sigmas, rgbs = self.model(xyzs, dirs)
+        weights_sum, depth, image = raymarching.composite_rays_train(sigmas, rgbs, deltas, rays)
+        image = image + (1 - weights_sum).unsqueeze(-1) * bg_color
+        depth = torch.clamp(depth - nears, min=0) / (fars - nears)
+        return image, depth, weights_sum
+
+    def train_step(self, rays_o, rays_d, gt_rgb, bg_color=1.0):
+        """One optimisation step on device-resident rays; returns the loss tensor (no host sync)."""
+        self.model.train()
+        self.optimizer.zero_grad(set_to_none=True)
+        with torch.autocast("cuda", dtype=torch.float16, enabled=self.fp16):
+            image, _, _ = self.render_train(rays_o, rays_d, bg_color)
+            loss = torch.nn.functional.mse_loss(image, gt_rgb)
+        self.scaler.scale(loss).backward()
+        self.scaler.step(self.optimizer)
+        self.scaler.update()
+        return loss
+
+    def train_step_host(self, rays_o_h, rays_d_h, gt_rgb_h, stage):
+        """End-to-end step from PINNED HOST buffers: H2D copies of the batch, the step, D2H read of the loss."""
+        stage[0].copy_(rays_o_h, non_blocking=True)
+        stage[1].copy_(rays_d_h, non_blocking=True)
+        stage[2].copy_(gt_rgb_h, non_blocking=True)
+        loss = self.train_step(stage[0], stage[1], stage[2])
+        return float(loss.item())
+
+    def update_mean_count(self):
+        """renderer.py:533-536: mean samples of the last 16 steps (one D2H sync, every 16 steps)."""
+        total = min(self.local_step, 16)
+        if total > 0:
+            self.mean_count = int(self.step_counter[:total, 0].sum().item() / total)
+
+    # ------------------------------------------------------------------------------------------------ inference
+    @torch.no_grad()
+    def render(self, rays_o, rays_d, bg_color=1.0, T_thresh=1e-4, device_compaction=True):
+        """run_cuda, inference branch (legacy/nerf/renderer.py:331-372).  device_compaction=True swaps the reference's
+        boolean-mask indexing for raymarching.compact_alive; the alive count is still read once per iteration because
+        the caller-owned loop sizes its launches with it."""
+        self.model.eval()
+        rays_o, rays_d = rays_o.contiguous().view(-1, 3), rays_d.contiguous().view(-1, 3)
+        N, dev = rays_o.shape[0], rays_o.device
+        nears, fars = raymarching.near_far_from_aabb(rays_o, rays_d, self.aabb, self.min_near)
+        weights_sum = torch.zeros(N, dtype=torch.float32, device=dev)
+        depth = torch.zeros(N, dtype=torch.float32, device=dev)
+        image = torch.zeros(N, 3, dtype=torch.float32, device=dev)
+        n_alive = N
+        rays_alive = torch.arange(n_alive, dtype=torch.int32, device=dev)
+        rays_t = nears.clone()
+        step = 0
+        with torch.autocast("cuda", dtype=torch.float16, enabled=self.fp16):
+            while step < self.max_steps:
+                n_alive = rays_alive.shape[0]
+                if n_alive <= 0:
+                    break
+                n_step = max(min(N // n_alive, 8), 1)
+                xyzs, dirs, deltas = raymarching.march_rays(n_alive, n_step, rays_alive, rays_t, rays_o, rays_d, self.bound,
+                                                            self.density_bitfield, self.cascade, self.grid_size, nears, fars,
+                                                            128, False, self.dt_gamma, self.max_steps)
+                sigmas, rgbs = self.model(xyzs, dirs)
+                raymarching.composite_rays(n_alive, n_step, rays_alive, rays_t, sigmas, rgbs, deltas, weights_sum, depth, image,
+                                           T_thresh)
+                if device_compaction:
+                    out, n_out = raymarching.compact_alive(rays_alive, n_alive)
+                    rays_alive = out[:int(n_out.item())]
+                else:
+                    rays_alive = rays_alive[rays_alive >= 0]
+                step += n_step
+        image = image + (1 - weights_sum).unsqueeze(-1) * bg_color
+        depth = torch.clamp(depth - nears, min=0) / (fars - nears)
+        return image, depth, weights_sum

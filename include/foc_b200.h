@@ -72,11 +72,24 @@ int foc_composite_rays(uint32_t n_alive, uint32_t n_step, float T_thresh, int32_
 size_t foc_compact_alive_scratch_bytes(uint32_t n);
 int foc_compact_alive(const int32_t *rays_alive, uint32_t n, int32_t *out, int32_t *n_out, void *scratch, void *stream);
 
-/* FOC-NeRF multi-object composite (COMBINED.py:141-200, 247-251; editable.py:443-471), one fused kernel:
+/* FOC-NeRF per-object uniform sampling (COMBINED.py:451-474 `run`; editable.py:443-471 `modify_rays_for_object`):
+ * o' = rays_o + offset (offset [3] or NULL), d' = normalize(rays_d) when normalize_d, near/far of (o', d') against aabb
+ * (raymarching.cu:92-145), then xyzs[n,i] = clip(o' + d' * (near + (far-near) * linspace(0,1,T)[i]), aabb).
+ * out_o/out_d [N,3], nears/fars [N], xyzs [N,T,3] (NULL or T == 0: rays only). */
+int foc_sample_uniform(const float *rays_o, const float *rays_d, const float *offset, int normalize_d, const float *aabb,
+                       float min_near, uint32_t N, uint32_t T, float *out_o, float *out_d, float *nears, float *fars,
+                       float *xyzs, void *stream);
+
+/* FOC-NeRF multi-object composite (COMBINED.py:141-200, 247-251, 515-526), one fused kernel:
  * sigmas [K,N,T], rgbs [K,N,T,3] f32; per-sample argmax-sigma selection (earlier object wins ties), then a
- * front-to-back composite over T uniform samples in [near,far].  image [N,4], depth [N], weights_sum [N]. */
-int foc_composite_multi(const float *sigmas, const float *rgbs, const float *nears, const float *fars, uint32_t K,
-                        uint32_t N, uint32_t T, float bg, float *image, float *depth, float *weights_sum, void *stream);
+ * front-to-back composite over T uniform samples in [near,far] of the UNSHIFTED rays.  obj_nears/obj_fars [K,N]
+ * (both or neither): when given, object k's colour counts only where its OWN weight along its own (possibly shifted)
+ * ray exceeds mask_thresh (1e-10 in the reference); NULL = rgbs already masked.  T_thresh = 0 is the reference's
+ * behaviour (no early termination); > 0 stops a ray once its transmittance falls below it.
+ * image [N,4] (rgb + sum w*sigma, + (1-sum w)*bg, clamped to [0,1]), depth [N], weights_sum [N]. */
+int foc_composite_multi(const float *sigmas, const float *rgbs, const float *nears, const float *fars,
+                        const float *obj_nears, const float *obj_fars, uint32_t K, uint32_t N, uint32_t T, float bg,
+                        float mask_thresh, float T_thresh, float *image, float *depth, float *weights_sum, void *stream);
 
 /* ---------------------------------------------------------------- gridencoder (gridencoder/src/gridencoder.h:12-15) */
 
@@ -132,6 +145,10 @@ int foc_free_splitk(void);
 int foc_freq_encode_forward(const float *inputs, uint32_t B, uint32_t D, uint32_t deg, uint32_t C, float *outputs, void *stream);
 int foc_freq_encode_backward(const float *grad, const float *outputs, uint32_t B, uint32_t D, uint32_t deg, uint32_t C,
                              float *grad_inputs, void *stream);
+
+/* degree <= 4 real spherical-harmonics direction encoding (`shencoder`, imported by nerf/network_ff.py:5 but ABSENT
+ * from the reference tree: closed form, parity unpinned).  dirs [B,3] -> outputs [B, degree^2] f32. */
+int foc_sh_encode_forward(const float *dirs, uint32_t B, uint32_t degree, float *outputs, void *stream);
 
 #ifdef __cplusplus
 }

@@ -1,0 +1,143 @@
+"""CPU: the oracle (oracle/*.c) against (1) golden vectors produced by the REFERENCE's own CUDA extensions on a B200
+(tests/golden/*.npz, written by tests/golden/make_golden.py) and (2) its own invariants.  No GPU, no CUDA library."""
+import os
+
+import numpy as np
+import pytest
+
+import cases
+import runners_cpu as rc
+
+GOLD = os.path.join(os.path.dirname(os.path.abspath(__file__)), "golden")
+
+
+def gold(name):
+    p = os.path.join(GOLD, name + ".npz")
+    if not os.path.exists(p):
+        pytest.skip(f"{name}.npz not generated yet (run tests/golden/make_golden.py on the GPU box)")
+    return np.load(p)
+
+
+def rel(a, b):
+    return float(np.abs(a.astype(np.float64) - b.astype(np.float64)).max()) / (float(np.abs(b).max()) + 1e-20)
+
+
+def bits_equal(a, b):
+    return a.shape == b.shape and np.array_equal(np.ascontiguousarray(a).view(np.uint32), np.ascontiguousarray(b).view(np.uint32))
+
+
+@pytest.mark.parametrize("name", ["march_b1", "march_b2"])
+def test_oracle_march_matches_reference_golden(name):
+    import oracle
+    from golden.make_golden import GOLDEN_CASES
+    g, k = gold(name), GOLDEN_CASES[name]
+    c = cases.march_case(k["n"], k["seed"], k["bound"], k["dt_gamma"])
+    assert bits_equal(c["nears"], g["nears"]) and bits_equal(c["fars"], g["fars"])
+    r = rc.march_train(c)
+    assert np.array_equal(r["counts"], g["counts"]) and np.array_equal(r["counter"], g["counter"])
+    for key in ("xyzs", "dirs", "deltas"):
+        assert bits_equal(r[key], g[key]), key
+    N = c["rays_o"].shape[0]
+    x, d, dl = oracle.march_rays(N, 1, np.arange(N, dtype=np.int32), c["nears"].copy(), c["rays_o"], c["rays_d"], c["bound"],
+                                 c["bitfield"], c["cascade"], c["H"], c["nears"], c["fars"], np.zeros(N, np.float32),
+                                 dt_gamma=c["dt_gamma"], max_steps=c["max_steps"])
+    assert bits_equal(x, g["infer_xyzs"]) and bits_equal(dl, g["infer_deltas"])
+
+
+def test_oracle_composite_matches_reference_golden():
+    import oracle
+    from golden.make_golden import GOLDEN_CASES
+    g, k = gold("composite"), GOLDEN_CASES["composite"]
+    c = cases.composite_case(k["n"], k["seed"], k["bound"])
+    ws, dep, img = oracle.composite_rays_train_forward(c["sigmas"], c["rgbs"], c["deltas"], c["rays"])
+    gs, gc = oracle.composite_rays_train_backward(c["grad_ws"], c["grad_image"], c["sigmas"], c["rgbs"], c["deltas"], c["rays"], ws, img)
+    for a, key in ((ws, "ws"), (dep, "depth"), (img, "image"), (gs, "grad_sigmas"), (gc, "grad_rgbs")):
+        assert rel(a, g[key]) <= 1e-3, key                       # __expf vs expf: tolerance, never bitwise
+
+
+@pytest.mark.parametrize("half", [True, False])
+def test_oracle_grid_matches_reference_golden(half):
+    import oracle
+    from golden.make_golden import GOLDEN_CASES
+    g, k = gold("grid_f16" if half else "grid_f32"), GOLDEN_CASES["grid"]
+    c = cases.grid_case(k["B"], k["seed"])
+    out, dy = oracle.grid_encode_forward(c["inputs"], c["embeddings"], c["offsets"], c["per_level_scale"], c["H"], True, half=half)
+    if half:
+        nbad = int((out.view(np.uint16) != g["out"].view(np.uint16)).sum())
+        assert nbad <= out.size // 1000, f"{nbad}/{out.size} fp16 encodings differ bitwise (exp2f last-bit cases only)"
+    assert rel(out.astype(np.float32), g["out"].astype(np.float32)) <= 1e-3
+    assert rel(dy.astype(np.float32), g["dy_dx"].astype(np.float32)) <= 2e-3
+    L = c["offsets"].shape[0] - 1
+    g_lbc = np.ascontiguousarray(c["grad"].reshape(-1, L, 2).transpose(1, 0, 2))
+    acc = oracle.grid_encode_backward(g_lbc, c["inputs"], c["offsets"], c["per_level_scale"], c["H"], 2, half=half).reshape(-1)
+    ref = np.zeros_like(acc); ref[g["grad_idx"]] = g["grad_val"]
+    assert rel(acc, ref) <= (3e-2 if half else 1e-4)
+
+
+@pytest.mark.parametrize("name", ["mlp_sigma", "mlp_color"])
+def test_oracle_mlp_matches_reference_golden(name):
+    import oracle
+    from golden.make_golden import GOLDEN_CASES
+    g, k = gold(name), GOLDEN_CASES[name]
+    c = cases.mlp_case(**k)
+    out, fb = oracle.ffmlp_forward(c["inputs"], c["weights"], c["input_dim"], 16, 64, c["num_layers"])
+    gw, bb, gi = oracle.ffmlp_backward(c["grad"], c["inputs"], c["weights"], fb, c["input_dim"], 16, 64, c["num_layers"], calc_grad_inputs=True)
+    # the reference accumulates in fp16 (ffmlp.cu:564): its distance from the exact oracle is a few fp16 ulps of the scale
+    assert rel(out.astype(np.float32), g["out"]) <= 1e-2
+    assert rel(fb.astype(np.float32), g["fb"]) <= 1e-2
+    assert rel(gi.astype(np.float32), g["grad_inputs"]) <= 2e-2
+    assert rel(gw, g["grad_weights"]) <= 2e-2
+
+
+def test_oracle_freq_matches_reference_golden():
+    import oracle
+    from golden.make_golden import GOLDEN_CASES
+    g, k = gold("freq"), GOLDEN_CASES["freq"]
+    x = np.random.RandomState(k["seed"]).uniform(-1, 1, (k["B"], 3)).astype(np.float32)
+    np.testing.assert_allclose(oracle.freq_encode_forward(x, k["deg"]), g["out"], rtol=0, atol=1e-5)
+    np.testing.assert_allclose(oracle.freq_encode_backward(g["grad"], g["out"], 3, k["deg"]), g["grad_inputs"], rtol=1e-4, atol=1e-4)
+
+
+# ---------------------------------------------------------------- invariants that need no fixture
+def test_march_invariants():
+    c = cases.march_case(256, 41, 2.0, 1.0 / 128)
+    r = rc.march_train(c)
+    assert r["counter"][1] == c["rays_o"].shape[0] and r["counter"][0] == r["counts"].sum()
+    miss = c["nears"] > 1e30
+    assert miss.any() and np.all(r["counts"][miss] == 0)
+    assert np.all(np.abs(r["xyzs"]) <= c["bound"]) and np.all(r["deltas"][:, 0] > 0)
+    assert np.all(r["counts"] <= c["max_steps"])
+
+
+def test_composite_invariants():
+    import oracle
+    c = cases.composite_case(256, 42, 1.0)
+    ws, dep, img = oracle.composite_rays_train_forward(c["sigmas"], c["rgbs"], c["deltas"], c["rays"])
+    assert np.all(ws >= 0) and np.all(ws <= 1 + 1e-5) and np.all(img <= 1 + 1e-5)
+    # linearity in colour: compositing 2*rgb doubles the image, leaves weights unchanged
+    ws2, _, img2 = oracle.composite_rays_train_forward(c["sigmas"], 2 * c["rgbs"], c["deltas"], c["rays"])
+    np.testing.assert_allclose(img2, 2 * img, rtol=1e-6, atol=1e-7); assert np.array_equal(ws2, ws)
+    # finite-difference check of grad_sigmas on a few samples
+    gs, _ = oracle.composite_rays_train_backward(c["grad_ws"], c["grad_image"], c["sigmas"], c["rgbs"], c["deltas"], c["rays"], ws, img)
+    loss = lambda s: float((oracle.composite_rays_train_forward(s, c["rgbs"], c["deltas"], c["rays"])[2].astype(np.float64) * c["grad_image"]).sum()
+                           + (oracle.composite_rays_train_forward(s, c["rgbs"], c["deltas"], c["rays"])[0].astype(np.float64) * c["grad_ws"]).sum())
+    ray = c["rays"][np.argmax(c["rays"][:, 2])]
+    for i in (int(ray[1]), int(ray[1]) + 1):
+        if c["sigmas"][i] > 100:
+            continue
+        s1, s0 = c["sigmas"].copy(), c["sigmas"].copy()
+        h = max(1e-2, 1e-2 * float(c["sigmas"][i]))
+        s1[i] += h; s0[i] -= h
+        assert abs((loss(s1) - loss(s0)) / (2 * h) - gs[i]) <= 5e-2 * max(1.0, abs(gs[i]))
+
+
+def test_foc_composite_selection_rule():
+    import oracle
+    c = cases.multi_case(K=3, N=64, T=32)
+    on, of = oracle.near_far_from_aabb(c["rays_o"], c["rays_d"], c["aabb"], 0.2)
+    img, dep, ws = oracle.foc_composite(c["sigmas"], c["rgbs"], on, of, 1.0)
+    # object order matters only through ties: swapping objects 0 and 1 changes the colour picked at the tied sample 3
+    sw = c["sigmas"][[1, 0, 2]], c["rgbs"][[1, 0, 2]]
+    img2, _, ws2 = oracle.foc_composite(sw[0], sw[1], on, of, 1.0)
+    np.testing.assert_allclose(ws2, ws, rtol=1e-6)
+    assert np.all(img >= 0) and np.all(img <= 1)

@@ -1,0 +1,86 @@
+"""-m gpu: hash-grid encoder vs the CPU oracle and the reference extension."""
+import numpy as np
+import pytest
+import torch
+
+import cases
+import ref_ext
+import runners
+
+pytestmark = pytest.mark.gpu
+
+
+def ours():
+    from focnerf_b200.gridencoder.grid import _backend
+    return _backend
+
+
+def rel(a, b):
+    return float(np.abs(a.astype(np.float64) - b.astype(np.float64)).max()) / (float(np.abs(b).max()) + 1e-20)
+
+
+@pytest.mark.parametrize("half", [True, False])
+@pytest.mark.parametrize("res", [2048, None])
+def test_grid_vs_oracle(half, res):
+    import oracle
+    c = cases.grid_case(4096, 3, desired_resolution=res)
+    got = runners.grid_fwd_bwd(ours(), c, half=half)
+    out, dy = oracle.grid_encode_forward(c["inputs"], c["embeddings"], c["offsets"], c["per_level_scale"], c["H"], True, half=half)
+    assert rel(got["out"].astype(np.float32), out.astype(np.float32)) <= 1e-3
+    assert np.all(got["out"][:, 0] == 0) and np.all(got["out"][:, 1] == 0)            # out-of-range points encode to zero
+    assert rel(got["dy_dx"].astype(np.float32), dy.astype(np.float32)) <= 2e-3
+    L = c["offsets"].shape[0] - 1
+    g_lbc = np.ascontiguousarray(c["grad"].reshape(-1, L, 2).transpose(1, 0, 2))
+    acc = oracle.grid_encode_backward(g_lbc, c["inputs"], c["offsets"], c["per_level_scale"], c["H"], 2, half=half)
+    assert rel(got["grad_emb"], acc) <= (2e-2 if half else 1e-4)                       # fp16 atomics: order-dependent rounding
+    gi = oracle.grid_input_backward(g_lbc.astype(np.float16 if half else np.float32), dy, c["inputs"].shape[0], 3, 2, L, half=half)
+    assert rel(got["grad_inputs"], gi.astype(np.float32)) <= (2e-2 if half else 1e-4)
+
+
+@pytest.mark.parametrize("half", [True, False])
+def test_grid_vs_reference(half):
+    ref = ref_ext.load("gridencoder")
+    if ref is None:
+        pytest.skip("oracle/_ref/gridencoder not built")
+    c = cases.grid_case(65536, 13)
+    a, b = runners.grid_fwd_bwd(ours(), c, half=half), runners.grid_fwd_bwd(ref, c, half=half)
+    if half:
+        nbad = int((a["out"].view(np.uint16) != b["out"].view(np.uint16)).sum())
+        assert nbad == 0, f"{nbad} of {a['out'].size} fp16 encodings differ from the reference bitwise"
+    assert rel(a["out"].astype(np.float32), b["out"].astype(np.float32)) <= 1e-3
+    assert rel(a["dy_dx"].astype(np.float32), b["dy_dx"].astype(np.float32)) <= 1e-3
+    assert rel(a["grad_emb"], b["grad_emb"]) <= (3e-2 if half else 1e-4)
+    assert rel(a["grad_inputs"], b["grad_inputs"]) <= (1e-2 if half else 1e-4)
+
+
+def test_grid_module_blc_layout_matches_lbc():
+    """GridEncoder (point-major [B, L*C] kernel layout) == permuted reference-layout output; backward == LBC backward."""
+    from focnerf_b200.gridencoder import GridEncoder
+    c = cases.grid_case(8192, 5)
+    enc = GridEncoder(desired_resolution=2048).cuda()
+    with torch.no_grad():
+        enc.embeddings.copy_(runners.T(c["embeddings"]))
+    x = (runners.T(c["inputs"]) * 2 - 1)
+    with torch.autocast("cuda", dtype=torch.float16):
+        y = enc(x, bound=1)
+        (y.float() * runners.T(c["grad"])).sum().backward()
+    c2 = dict(c); c2["inputs"] = ((x + 1) / 2).cpu().numpy()
+    r = runners.grid_fwd_bwd(ours(), c2, half=True, calc_grad_inputs=False)
+    exp = np.ascontiguousarray(r["out"].transpose(1, 0, 2)).reshape(x.shape[0], -1)
+    assert np.array_equal(y.cpu().numpy().view(np.uint16), exp.view(np.uint16))
+    assert enc.embeddings.grad.dtype == torch.float32
+    assert rel(enc.embeddings.grad.cpu().numpy(), r["grad_emb"]) <= 3e-2
+
+
+def test_grad_total_variation_vs_oracle():
+    import oracle
+    from focnerf_b200.gridencoder import GridEncoder
+    c = cases.grid_case(20000, 7, with_oob=False)
+    enc = GridEncoder(desired_resolution=2048).cuda()
+    with torch.no_grad():
+        enc.embeddings.copy_(runners.T(c["embeddings"]))
+    enc.embeddings.grad = torch.zeros_like(enc.embeddings)
+    enc.grad_total_variation(1e-3, inputs=runners.T(c["inputs"]) * 2 - 1, bound=1)
+    x01 = ((runners.T(c["inputs"]) * 2 - 1 + 1) / 2).cpu().numpy()
+    acc = oracle.grad_total_variation(x01, c["embeddings"], c["offsets"], c["per_level_scale"], c["H"], 1e-3)
+    assert rel(enc.embeddings.grad.cpu().numpy(), acc) <= 1e-3

@@ -1,0 +1,101 @@
+"""-m gpu: fused tcgen05 MLP vs the CPU oracle and the reference extension (wmma, fp16 accumulate), plus the
+frequency / SH encoders.  Tolerance: 1e-3 of each tensor's scale vs the exact-accumulation oracle; the reference's own
+fp16-accumulation noise is larger than that, so against it the bound is the reference's distance from the oracle."""
+import numpy as np
+import pytest
+import torch
+
+import cases
+import ref_ext
+import runners
+
+pytestmark = pytest.mark.gpu
+
+
+def ours():
+    from focnerf_b200.ffmlp.ffmlp import _backend
+    return _backend
+
+
+def rel(a, b):
+    return float(np.abs(a.astype(np.float64) - b.astype(np.float64)).max()) / (float(np.abs(b).max()) + 1e-20)
+
+
+def _oracle(c, calc_grad_inputs=True):
+    import oracle
+    out, fb = oracle.ffmlp_forward(c["inputs"], c["weights"], c["input_dim"], 16, 64, c["num_layers"])
+    gw, bb, gi = oracle.ffmlp_backward(c["grad"], c["inputs"], c["weights"], fb, c["input_dim"], 16, 64, c["num_layers"],
+                                      calc_grad_inputs=calc_grad_inputs)
+    return dict(out=out.astype(np.float32), fb=fb.astype(np.float32), grad_weights=gw, grad_inputs=None if gi is None else gi.astype(np.float32))
+
+
+@pytest.mark.parametrize("input_dim,num_layers,B", [(32, 2, 128), (32, 2, 1280), (32, 3, 1280), (64, 2, 640), (32, 3, 128 * 700)])
+def test_mlp_vs_oracle(input_dim, num_layers, B):
+    c = cases.mlp_case(B, input_dim, 16, num_layers)
+    got = runners.mlp_fwd_bwd(ours(), c)
+    exp = _oracle(c)
+    assert rel(got["out"], exp["out"]) <= 1e-3, "outputs"
+    assert rel(got["out_inf"], exp["out"]) <= 1e-3, "inference outputs"
+    assert rel(got["fb"], exp["fb"]) <= 1e-3, "forward_buffer"
+    assert rel(got["grad_inputs"], exp["grad_inputs"]) <= 2e-3, "grad_inputs"
+    assert rel(got["grad_weights"], exp["grad_weights"]) <= 2e-3, "grad_weights"
+
+
+@pytest.mark.parametrize("input_dim,num_layers", [(32, 2), (32, 3)])
+def test_mlp_vs_reference(input_dim, num_layers):
+    ref = ref_ext.load("ffmlp")
+    if ref is None:
+        pytest.skip("oracle/_ref/ffmlp not built")
+    ref.allocate_splitk(num_layers + 1)
+    c = cases.mlp_case(8192, input_dim, 16, num_layers, seed=14)
+    a, b, exp = runners.mlp_fwd_bwd(ours(), c), runners.mlp_fwd_bwd(ref, c), _oracle(c)
+    for k in ("out", "fb", "grad_inputs", "grad_weights"):
+        ref_noise = rel(b[k], exp[k])                       # the reference's own fp16-accumulation error
+        assert rel(a[k], exp[k]) <= max(1e-3, 0.5 * ref_noise) + 1e-3, k
+        assert rel(a[k], b[k]) <= 1.5 * ref_noise + 2e-3, f"{k}: ours vs reference {rel(a[k], b[k]):.2e}, reference vs exact {ref_noise:.2e}"
+
+
+def test_ffmlp_module_matches_reference_wrapper_semantics():
+    """FFMLP pads by 128 even when B % 128 == 0 and slices [:B, :output_dim] (ffmlp.py:157-165)."""
+    import oracle
+    from focnerf_b200.ffmlp import FFMLP
+    net = FFMLP(32, 3, 64, 3).cuda()
+    assert net.weights.numel() == 11264 and net.weights.dtype == torch.float32
+    x = torch.randn(256, 32, device="cuda").half().requires_grad_()
+    net.train()
+    y = net(x)
+    assert y.shape == (256, 3)
+    y.float().sum().backward()
+    assert x.grad.shape == x.shape and net.weights.grad.shape == net.weights.shape
+    out, _ = oracle.ffmlp_forward(x.detach().cpu().numpy(), net.weights.detach().half().cpu().numpy(), 32, 16, 64, 3)
+    assert rel(y.detach().float().cpu().numpy(), out[:, :3].astype(np.float32)) <= 1e-3
+    net.eval()
+    with torch.no_grad():
+        y2 = net(x.detach())
+    assert torch.equal(y2, y.detach())
+
+
+def test_unsupported_shapes_raise():
+    from focnerf_b200.ffmlp import FFMLP
+    net = FFMLP(32, 3, 128, 2).cuda()
+    with pytest.raises(RuntimeError):
+        net(torch.zeros(128, 32, device="cuda").half())
+
+
+def test_freq_and_sh_encoders():
+    import oracle
+    from focnerf_b200.freqencoder.freq import _backend as fb
+    from focnerf_b200.shencoder import sh_encode
+    x = np.random.RandomState(0).uniform(-1, 1, (5000, 3)).astype(np.float32)
+    for deg in (4, 10):
+        out, gi, g = runners.freq(fb, x, deg)
+        eo = oracle.freq_encode_forward(x, deg)
+        np.testing.assert_allclose(out, eo, rtol=0, atol=2e-3 if deg == 10 else 1e-5)      # __sinf absolute error grows with |arg|
+        np.testing.assert_allclose(gi, oracle.freq_encode_backward(g, out, 3, deg), rtol=1e-4, atol=1e-3)
+        ref = ref_ext.load("freqencoder")
+        if ref is not None:
+            ro, rgi, _ = runners.freq(ref, x, deg)
+            assert np.array_equal(out.view(np.uint32), ro.view(np.uint32)), "freq forward not bit-exact vs reference"
+            np.testing.assert_allclose(gi, rgi, rtol=1e-5, atol=1e-5)
+    d = x / np.linalg.norm(x, axis=-1, keepdims=True)
+    np.testing.assert_allclose(sh_encode(runners.T(d)).cpu().numpy(), oracle.sh4_encode(d), rtol=1e-5, atol=1e-6)

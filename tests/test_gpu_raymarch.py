@@ -1,0 +1,138 @@
+"""-m gpu: ray marching through the C ABI vs the CPU oracle and vs the reference's own extension (oracle/_ref).
+Integer results (counts, offsets, cell-derived sample positions) must be BIT-EXACT (BASELINE.json north_star)."""
+import numpy as np
+import pytest
+import torch
+
+import cases
+import ref_ext
+import runners
+
+pytestmark = pytest.mark.gpu
+
+
+def ours():
+    from focnerf_b200.raymarching.backend import _backend
+    return _backend
+
+
+def _oracle_march(c, M=None):
+    import oracle
+    N = c["rays_o"].shape[0]
+    M = N * c["max_steps"] if M is None else M
+    x, d, dl, rays, counter = oracle.march_rays_train(c["rays_o"], c["rays_d"], c["bound"], c["bitfield"], c["cascade"], c["H"],
+                                                      c["nears"], c["fars"], c["noises"], M, c["dt_gamma"], c["max_steps"])
+    out = runners.canonical_march(rays, x, d, dl, M)
+    out["counter"] = counter
+    return out
+
+
+def _assert_march_equal(a, b):
+    assert np.array_equal(a["counts"], b["counts"]), f"{(a['counts'] != b['counts']).sum()} rays differ in sample count"
+    assert np.array_equal(a["counter"], b["counter"])
+    for k in ("xyzs", "dirs", "deltas"):
+        assert a[k].shape == b[k].shape
+        assert np.array_equal(a[k].view(np.uint32), b[k].view(np.uint32)), f"{k} not bit-exact"
+
+
+@pytest.mark.parametrize("bound,dt_gamma", [(1.0, 0.0), (2.0, 1.0 / 128), (1.0, 1.0 / 128)])
+def test_march_train_vs_oracle(bound, dt_gamma):
+    c = cases.march_case(512, 1, bound, dt_gamma)
+    got = runners.march_train(ours(), c)
+    _assert_march_equal(got, _oracle_march(c))
+    # deterministic, ray-ordered slots: offsets are the exclusive scan of the counts
+    assert np.array_equal(got["offsets"], np.concatenate([[0], np.cumsum(got["counts"])[:-1]]))
+
+
+@pytest.mark.parametrize("bound,dt_gamma", [(1.0, 0.0), (2.0, 1.0 / 128)])
+def test_march_train_vs_reference(bound, dt_gamma):
+    ref = ref_ext.load("raymarching")
+    if ref is None:
+        pytest.skip("oracle/_ref/raymarching not built")
+    c = cases.march_case(2048, 11, bound, dt_gamma)
+    a, b = runners.march_train(ours(), c), runners.march_train(ref, c)
+    _assert_march_equal(a, b)
+    # both slot assignments tile [0, total) without gaps or overlaps (ours in ray order, the reference's in arrival order)
+    for r in (a, b):
+        iv = sorted((int(o), int(n)) for o, n in zip(r["offsets"], r["counts"]) if n > 0)
+        pos = 0
+        for o, n in iv:
+            assert o == pos
+            pos += n
+        assert pos == int(r["counter"][0])
+
+
+def test_march_train_truncated():
+    """mean_count underestimates (M too small): kept rays are exact, nothing is written past M."""
+    c = cases.march_case(512, 3, 1.0)
+    full = runners.march_train(ours(), c)
+    M = int(full["counter"][0]) // 2
+    got = runners.march_train(ours(), c, M=M)
+    assert np.array_equal(got["counts"], full["counts"])            # counts are still reported for every ray
+    assert int((got["counts"][got["kept"]]).sum()) <= M
+    ref_x = _oracle_march(c, M=M)
+    assert np.array_equal(got["xyzs"].view(np.uint32), ref_x["xyzs"].view(np.uint32))
+
+
+def test_near_far_packbits_morton_vs_oracle():
+    import oracle
+    c = cases.march_case(1024, 5, 1.0)
+    n, f = runners.near_far(ours(), c)
+    assert np.array_equal(n.view(np.uint32), c["nears"].view(np.uint32)) and np.array_equal(f.view(np.uint32), c["fars"].view(np.uint32))
+    _, _, grid, bits, thresh = cases.scene_bitfield(1.0)
+    assert np.array_equal(runners.packbits(ours(), grid, thresh), bits)
+    coords = np.random.RandomState(0).randint(0, 128, (5000, 3))
+    idx, back = runners.morton(ours(), coords)
+    assert np.array_equal(idx, oracle.morton3D(coords)) and np.array_equal(back, coords)
+    ref = ref_ext.load("raymarching")
+    if ref is not None:
+        rn, rf = runners.near_far(ref, c)
+        assert np.array_equal(n.view(np.uint32), rn.view(np.uint32)) and np.array_equal(f.view(np.uint32), rf.view(np.uint32))
+        assert np.array_equal(runners.packbits(ref, grid, thresh), bits)
+        ridx, _ = runners.morton(ref, coords)
+        assert np.array_equal(idx, ridx)
+
+
+def _field(scene):
+    def f(xyzs, dirs):
+        s, c = scene.sigma_color(xyzs, dirs)
+        return s, c
+    return f
+
+
+def test_infer_loop_vs_reference_and_oracle():
+    """march_rays + composite_rays through the caller's loop: sample positions bit-exact at every iteration,
+    accumulated image / depth / weights within 1e-3 relative."""
+    scene = cases.scene_bitfield(1.0)[0]
+    c = cases.march_case(1500, 21, 1.0)
+    a = runners.infer_loop(ours(), c, _field(scene))
+    ref = ref_ext.load("raymarching")
+    if ref is not None:
+        b = runners.infer_loop(ref, c, _field(scene))
+        assert len(a["trace"]) == len(b["trace"])
+        for ta, tb in zip(a["trace"], b["trace"]):
+            assert ta["n_alive"] == tb["n_alive"] and ta["n_step"] == tb["n_step"]
+            assert np.array_equal(ta["xyzs"].view(np.uint32), tb["xyzs"].view(np.uint32))
+            assert np.array_equal(ta["deltas"].view(np.uint32), tb["deltas"].view(np.uint32))
+            assert np.array_equal(ta["alive_after"], tb["alive_after"])
+        for k in ("ws", "depth", "image"):
+            np.testing.assert_allclose(a[k], b[k], rtol=1e-3, atol=1e-5)
+    # oracle: first iteration of the loop
+    import oracle
+    N = c["rays_o"].shape[0]
+    x, d, dl = oracle.march_rays(N, 1, np.arange(N, dtype=np.int32), c["nears"].copy(), c["rays_o"], c["rays_d"], 1.0, c["bitfield"],
+                                 c["cascade"], c["H"], c["nears"], c["fars"], np.zeros(N, np.float32))
+    assert np.array_equal(a["trace"][0]["xyzs"][:N].view(np.uint32), x.view(np.uint32))
+    assert np.array_equal(a["trace"][0]["deltas"][:N].view(np.uint32), dl.view(np.uint32))
+
+
+def test_compact_alive():
+    from focnerf_b200 import raymarching
+    g = torch.Generator().manual_seed(0)
+    for n in (1, 31, 2048, 2049, 640000):
+        v = torch.randint(-1, 5, (n,), generator=g, dtype=torch.int32)
+        v = torch.where(v < 0, v, torch.arange(n, dtype=torch.int32)).cuda()
+        out, n_out = raymarching.compact_alive(v)
+        exp = v[v >= 0]
+        assert int(n_out.item()) == exp.numel()
+        assert torch.equal(out[:exp.numel()], exp)
