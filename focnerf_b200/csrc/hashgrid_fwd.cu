@@ -170,6 +170,18 @@ int dispatch_c(uint32_t C, const float* inputs, const void* table, const int32_t
 
 }  // namespace
 
+// The per-level scale exp2f(level * S) * H - 1 exactly as the encoder kernels evaluate it (device exp2f is an
+// approximation for non-integer arguments).  Test hook: lets the CPU oracle reproduce fp16 encodings bit for bit.
+__global__ void k_grid_level_scales(float S, uint32_t H, uint32_t L, float* __restrict__ scales) {
+    const uint32_t l = blockIdx.x * blockDim.x + threadIdx.x;
+    if (l < L) scales[l] = fmaf(exp2f((float)l * S), (float)H, -1.0f);
+}
+FOC_API int foc_grid_level_scales(float S, uint32_t H, uint32_t L, float* scales, void* stream) {
+    if (L == 0) return 0;
+    k_grid_level_scales<<<ceil_div(L, 32), 32, 0, reinterpret_cast<cudaStream_t>(stream)>>>(S, H, L, scales);
+    FOC_LAUNCH_CHECK(); return 0;
+}
+
 FOC_API int foc_grid_encode_forward(const float* inputs, const void* embeddings, const int32_t* offsets, void* outputs,
                                     uint32_t B, uint32_t D, uint32_t C, uint32_t L, float S, uint32_t H, void* dy_dx,
                                     uint32_t gridtype, int align_corners, uint32_t interp, int dtype, int layout, void* stream) {

@@ -72,6 +72,13 @@ class _Backend:
                                              H, gridtype, int(align_corners), stream()), "grad_total_variation")
 
 
+def level_scales(per_level_scale, base_resolution, num_levels, device="cuda"):
+    """Device-evaluated exp2f(l * log2(per_level_scale)) * H - 1 for l < num_levels (diagnostic / test hook)."""
+    out = torch.empty(num_levels, dtype=torch.float32, device=device)
+    check(lib().foc_grid_level_scales(float(np.log2(per_level_scale)), base_resolution, num_levels, ptr(out), stream()), "grid_level_scales")
+    return out
+
+
 _backend = _Backend()
 
 

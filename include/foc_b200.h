@@ -108,6 +108,8 @@ int foc_composite_multi(const float *sigmas, const float *rgbs, const float *nea
 int foc_grid_encode_forward(const float *inputs, const void *embeddings, const int32_t *offsets, void *outputs,
                             uint32_t B, uint32_t D, uint32_t C, uint32_t L, float S, uint32_t H, void *dy_dx,
                             uint32_t gridtype, int align_corners, uint32_t interp, int dtype, int layout, void *stream);
+/* New (diagnostic): scales[l] = exp2f(l * S) * H - 1 as the device evaluates it inside the encoder kernels. */
+int foc_grid_level_scales(float S, uint32_t H, uint32_t L, float *scales, void *stream);
 /* replaces grid_encode_backward, gridencoder.h:13 (gridencoder.cu:248-369). grad [L,B,C]; grad_embeddings [n,C]
  * (accumulated into; caller zeroes); dy_dx/grad_inputs NULL or [B,L*D*C]/[B,D] (table dtype). */
 int foc_grid_encode_backward(const void *grad, const float *inputs, const void *embeddings, const int32_t *offsets,

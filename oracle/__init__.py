@@ -177,6 +177,15 @@ def grid_offsets(input_dim=3, num_levels=16, level_dim=2, per_level_scale=2, bas
     return np.array(offsets, dtype=np.int32), per_level_scale
 
 
+def grid_set_level_scales(scales=None):
+    """Override the per-level scales with device-computed ones (None restores the host exp2f)."""
+    if scales is None:
+        lib().orc_grid_set_level_scales(None, u32(0))
+    else:
+        s = _f32(scales)
+        lib().orc_grid_set_level_scales(_p(s), u32(s.shape[0]))
+
+
 def _tbl(a, half):
     return np.ascontiguousarray(a, dtype=np.float16 if half else np.float32)
 

@@ -38,11 +38,22 @@ static inline uint32_t orc_grid_index(uint32_t D, uint32_t gridtype, int align_c
     return index % hashmap_size;
 }
 
+/* Optional override of the per-level scales (test hook): the GPU's exp2f is a 2-ulp approximation for non-integer
+ * arguments, so to compare fp16 encodings BITWISE against the reference's extension the oracle can be handed the
+ * scales the device computed (stored in the golden fixtures).  n == 0 restores the host exp2f. */
+static float orc_scale_override[64];
+static uint32_t orc_scale_override_n = 0;
+ORC_API void orc_grid_set_level_scales(const float *scales, uint32_t n) {
+    orc_scale_override_n = n > 64 ? 64 : n;
+    for (uint32_t i = 0; i < orc_scale_override_n; ++i) orc_scale_override[i] = scales[i];
+}
+
 typedef struct { float scale; uint32_t resolution, hashmap_size; } orc_level_t;
 static inline orc_level_t orc_level(const int32_t *offsets, uint32_t level, float S, uint32_t H) {
     orc_level_t l;
     l.hashmap_size = (uint32_t)(offsets[level + 1] - offsets[level]);
-    l.scale = fmaf(exp2f((float)level * S), (float)H, -1.0f);            /* gridencoder.cu:138 (FMA in SASS) */
+    l.scale = level < orc_scale_override_n ? orc_scale_override[level]
+                                           : fmaf(exp2f((float)level * S), (float)H, -1.0f);   /* gridencoder.cu:138 (FMA in SASS) */
     l.resolution = (uint32_t)ceilf(l.scale) + 1;
     return l;
 }

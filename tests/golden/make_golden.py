@@ -56,11 +56,13 @@ def main(out_dir):
     np.savez_compressed(os.path.join(out_dir, "composite.npz"), **runners.composite_train(rm, c))
     k = GOLDEN_CASES["grid"]
     c = cases.grid_case(k["B"], k["seed"])
+    from focnerf_b200.gridencoder.grid import level_scales
+    dev_scales = level_scales(c["per_level_scale"], c["H"], 16).cpu().numpy()
     for half in (True, False):
         r = runners.grid_fwd_bwd(ge, c, half=half)
         gi, gv = sparse(r["grad_emb"])
         np.savez_compressed(os.path.join(out_dir, f"grid_{'f16' if half else 'f32'}.npz"), out=r["out"], dy_dx=r["dy_dx"],
-                            grad_idx=gi, grad_val=gv, grad_inputs=r["grad_inputs"])
+                            grad_idx=gi, grad_val=gv, grad_inputs=r["grad_inputs"], device_level_scales=dev_scales)
     for name in ("mlp_sigma", "mlp_color"):
         k = GOLDEN_CASES[name]
         c = cases.mlp_case(**k)

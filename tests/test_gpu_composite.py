@@ -97,7 +97,7 @@ def test_sample_uniform_offset_and_masks():
     # editable.py:443-471 + COMBINED.py:460-474 in eager torch
     eo = ro + runners.T(c["offset"]); ed = torch.nn.functional.normalize(rd, dim=-1)
     assert torch.equal(o2, eo)
-    np.testing.assert_allclose(d2.cpu().numpy(), ed.cpu().numpy(), rtol=0, atol=1e-7)
+    np.testing.assert_allclose(d2.cpu().numpy(), ed.cpu().numpy(), rtol=0, atol=2.5e-7)   # 1-2 ulp vs torch's norm reduction
     hit = n2 < 1e30
     z = n2[:, None] + (f2 - n2)[:, None] * torch.linspace(0, 1, c["T"], device="cuda")[None]
     ex = torch.min(torch.max(o2[:, None] + d2[:, None] * z[..., None], aabb[:3]), aabb[3:])

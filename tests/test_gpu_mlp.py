@@ -63,14 +63,15 @@ def test_ffmlp_module_matches_reference_wrapper_semantics():
     assert net.weights.numel() == 11264 and net.weights.dtype == torch.float32
     x = torch.randn(256, 32, device="cuda").half().requires_grad_()
     net.train()
-    y = net(x)
+    with torch.autocast("cuda", dtype=torch.float16):         # cast_inputs=torch.half only acts under autocast (ffmlp.py:18)
+        y = net(x)
     assert y.shape == (256, 3)
     y.float().sum().backward()
     assert x.grad.shape == x.shape and net.weights.grad.shape == net.weights.shape
     out, _ = oracle.ffmlp_forward(x.detach().cpu().numpy(), net.weights.detach().half().cpu().numpy(), 32, 16, 64, 3)
     assert rel(y.detach().float().cpu().numpy(), out[:, :3].astype(np.float32)) <= 1e-3
     net.eval()
-    with torch.no_grad():
+    with torch.no_grad(), torch.autocast("cuda", dtype=torch.float16):
         y2 = net(x.detach())
     assert torch.equal(y2, y.detach())
 
@@ -78,7 +79,7 @@ def test_ffmlp_module_matches_reference_wrapper_semantics():
 def test_unsupported_shapes_raise():
     from focnerf_b200.ffmlp import FFMLP
     net = FFMLP(32, 3, 128, 2).cuda()
-    with pytest.raises(RuntimeError):
+    with pytest.raises(RuntimeError), torch.autocast("cuda", dtype=torch.float16):
         net(torch.zeros(128, 32, device="cuda").half())
 
 
