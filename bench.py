@@ -1,0 +1,263 @@
+"""bench.py -- train rays/s of the FOC-NeRF per-ray hot path (BASELINE.json configs[1]).
+
+Workload: single-object hash-grid NeRF train step -- 16 levels, 2^19 table, F=2, 64-wide fused MLPs, 4096 rays/batch per
+GPU, cuda_ray occupancy marching, fp16 autocast, MSE, GradScaler, Adam -- on the synthetic table-top scene (analytic
+ground truth; there is no dataset in the reference tree).  A "step" = march -> encode -> MLPs -> composite -> loss ->
+backward -> optimizer on one fresh batch of rays.
+
+  python bench.py --gpus N --steps K --warmup W              (N>1 under torchrun, one rank per GPU, NCCL grad all-reduce)
+  python bench.py --impl reference ...                       the reference's own CUDA extensions (oracle/_ref) on the
+                                                             same GPU, same config (falls back to the CPU port)
+Prints ONE JSON line on rank 0.
+"""
+import argparse
+import json
+import math
+import os
+import subprocess
+import sys
+import threading
+import time
+
+ROOT = os.path.dirname(os.path.abspath(__file__))
+for p in (ROOT, os.path.join(ROOT, "tests")):
+    if p not in sys.path:
+        sys.path.insert(0, p)
+
+RAYS_PER_GPU = 4096
+POOL = 32                      # distinct pre-generated ray batches cycled through (fresh rays every step)
+HBM_FALLBACK_GBS, TC_FALLBACK_TFLOPS = 6650.0, 1590.0
+
+
+def peaks():
+    try:
+        d = json.load(open(os.path.join(ROOT, "MEASURED_PEAKS.json")))
+        return float(d["hbm_gbs"]), "measured"
+    except Exception:
+        return HBM_FALLBACK_GBS, "fallback"
+
+
+class ClockSampler:
+    """nvidia-smi clocks / throttle reasons sampled DURING the timed region (B200_PROFILING.md)."""
+    Q = "clocks.sm,clocks.max.sm,clocks_event_reasons.hw_slowdown,clocks_event_reasons.hw_thermal_slowdown," \
+        "clocks_event_reasons.sw_thermal_slowdown,clocks_event_reasons.sw_power_cap"
+
+    def __init__(self, index=0):
+        self.index, self.rows, self.proc = index, [], None
+
+    def start(self):
+        try:
+            self.proc = subprocess.Popen(["nvidia-smi", f"--query-gpu={self.Q}", "--format=csv,noheader,nounits", "-i", str(self.index),
+                                          "-lms", "100"], stdout=subprocess.PIPE, stderr=subprocess.DEVNULL, text=True)
+            self.th = threading.Thread(target=self._read, daemon=True)
+            self.th.start()
+        except Exception:
+            self.proc = None
+
+    def _read(self):
+        for line in self.proc.stdout:
+            self.rows.append([c.strip() for c in line.split(",")])
+
+    def stop(self):
+        if self.proc is None:
+            return {"sm_mhz": None, "sm_max_mhz": None, "reasons": ["nvidia-smi unavailable"]}
+        self.proc.terminate()
+        try:
+            self.proc.wait(timeout=2)
+        except Exception:
+            self.proc.kill()
+        sm = sorted(int(r[0]) for r in self.rows if r and r[0].isdigit())
+        mx = [int(r[1]) for r in self.rows if len(r) > 1 and r[1].isdigit()]
+        names = ["hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"]
+        reasons = [n for i, n in enumerate(names) if any(len(r) > 2 + i and r[2 + i].lower().startswith("active") for r in self.rows)]
+        return {"sm_mhz": sm[len(sm) // 2] if sm else None, "sm_max_mhz": max(mx) if mx else None, "reasons": reasons,
+                "samples": len(sm)}
+
+
+def make_pool(scene, n_batches, rays, seed, device):
+    """Pre-generated batches: device copies for `value`, pinned host copies for `e2e`."""
+    import cases
+    import torch
+    dev, host = [], []
+    for i in range(n_batches):
+        o, d = cases.camera_rays(rays, seed + i)
+        o, d = torch.from_numpy(o).to(device), torch.from_numpy(d).to(device)
+        gt = scene.render_gt(o, d)
+        dev.append((o, d, gt))
+        host.append(tuple(t.cpu().pin_memory() for t in (o, d, gt)))
+    return dev, host
+
+
+# algorithmic traffic per SAMPLE of each timed entry point (SURVEY.md 8d / DESIGN.md "algorithmic bytes")
+ALG_BYTES = {
+    "foc_grid_encode_forward": 12 + 512 + 64,          # coords + 16 levels x 8 corners x 4 B + fp16 [B,32] out
+    "foc_grid_encode_backward": 12 + 64 + 512,         # coords + fp16 grad + 16 x 8 x 4 B atomic targets
+    "foc_composite_rays_train_forward": 24,
+    "foc_composite_rays_train_backward": 24 + 16,
+    "foc_march_rays_train": 32,
+}
+TIMED = list(ALG_BYTES) + ["foc_ffmlp_forward", "foc_ffmlp_backward"]
+
+
+def cpu_baseline(scene, bits, cascade, rays=1024):
+    """The oracle port of the same train step on the host cores (OpenMP), bounded sample: `rays` rays of one batch."""
+    import numpy as np
+    import torch
+    import cases
+    from oracle import cpu_step
+    st = cpu_step.CpuState()
+    o, d = cases.camera_rays(rays, 999)
+    gt = scene.render_gt(torch.from_numpy(o), torch.from_numpy(d)).numpy()
+    nz = np.random.RandomState(0).rand(rays).astype(np.float32)
+    cpu_step.train_step(st, o[:128], d[:128], gt[:128], bits, cascade, nz[:128])          # warm-up (builds liborc, page-in)
+    t = time.perf_counter()
+    cpu_step.train_step(st, o, d, gt, bits, cascade, nz)
+    dt = time.perf_counter() - t
+    return {"value": rays / dt, "unit": "rays/s", "cores": os.cpu_count(), "kind": "port",
+            "sample": f"1 train step (fwd+bwd+Adam) on {rays} rays of the same scene, oracle C port with OpenMP, {dt:.1f} s"}
+
+
+def run_ours(args):
+    import numpy as np
+    import torch
+    import torch.distributed as dist
+    import cases
+    from focnerf_b200 import _lib
+    from focnerf_b200.trainer import Trainer
+
+    world, rank, local = int(os.environ.get("WORLD_SIZE", 1)), int(os.environ.get("RANK", 0)), int(os.environ.get("LOCAL_RANK", 0))
+    torch.cuda.set_device(local)
+    if world > 1:
+        dist.init_process_group("nccl")
+    dev = torch.device("cuda", local)
+    scene, cascade, grid, bits, thresh = cases.scene_bitfield(1.0)
+    tr = Trainer(bound=1.0, density_grid=torch.from_numpy(grid), device=dev, seed=0)
+    params = [p for p in tr.model.parameters()]
+    if world > 1:                                   # data-parallel: identical replicas, gradients all-reduced every step
+        for p in params:
+            dist.broadcast(p.data, 0)
+        tr.grad_sync = lambda: [dist.all_reduce(p.grad, op=dist.ReduceOp.AVG) for p in params if p.grad is not None]
+    pool_dev, pool_host = make_pool(scene, POOL, RAYS_PER_GPU, 1000 + 7919 * rank, dev)
+    stage = [torch.empty_like(t) for t in pool_dev[0]]
+
+    def sync_all():
+        if world > 1:
+            dist.barrier()
+        torch.cuda.synchronize()
+
+    def loop(n, host, first):
+        for i in range(n):
+            j = (first + i) % POOL
+            if host:
+                tr.train_step_host(*pool_host[j], stage)
+            else:
+                tr.train_step(*pool_dev[j])
+            if tr.local_step % 16 == 0:
+                tr.update_mean_count()              # renderer.py:533-536, every update_extra_interval = 16 steps
+
+    loop(16, False, 0)                              # first "epoch": sizes the sample buffers (mean_count), untimed
+    loop(max(3, args.warmup), False, 16)
+    clocks = ClockSampler(local)
+    if rank == 0:
+        clocks.start()
+    with _lib.KernelTimer(TIMED) as kt:
+        sync_all()
+        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        e0.record()
+        loop(args.steps, False, 100)
+        e1.record()
+        sync_all()
+    ms = torch.tensor([e0.elapsed_time(e1)], device=dev)
+    if world > 1:
+        dist.all_reduce(ms, op=dist.ReduceOp.MAX)
+    ms = float(ms.item())
+    clk = clocks.stop() if rank == 0 else None
+    samples = float(tr.step_counter[:, 0].float().mean().item())       # mean samples/step over the last 16 steps
+
+    # end to end: pinned host buffers -> H2D -> step -> D2H loss, through the public API
+    loop(3, True, 200)
+    sync_all()
+    t0 = torch.cuda.Event(enable_timing=True); t1 = torch.cuda.Event(enable_timing=True)
+    t0.record()
+    loop(args.steps, True, 300)
+    t1.record()
+    sync_all()
+    ms_e2e = torch.tensor([t0.elapsed_time(t1)], device=dev)
+    if world > 1:
+        dist.all_reduce(ms_e2e, op=dist.ReduceOp.MAX)
+    ms_e2e = float(ms_e2e.item())
+
+    if rank != 0:
+        if world > 1:
+            dist.destroy_process_group()
+        return
+    total_rays = world * RAYS_PER_GPU * args.steps
+    hbm, how = peaks()
+    # dominant kernel among OUR entry points, by mean device time per call inside the timed region
+    per = {k: kt.mean_ms(k) * len(kt.events[k]) / args.steps for k in TIMED if kt.events.get(k)}
+    top = max(per, key=per.get)
+    if top in ALG_BYTES:
+        achieved = ALG_BYTES[top] * samples / (kt.mean_ms(top) * 1e-3) / 1e9
+        roof = {"kernel": top, "bound": "hbm", "achieved": achieved, "peak": hbm, "unit": "GB/s", "frac": achieved / hbm, "traffic": None,
+                "peak_source": how, "ms_per_launch": kt.mean_ms(top)}
+    else:                                            # fused MLPs: the only dense contraction -> tensor pipe
+        calls = len(kt.events[top]) / args.steps     # sigma + colour net per step
+        flops = (36864 if top == "foc_ffmlp_forward" else 2 * 36864) * samples / calls
+        try:
+            tc = float(json.load(open(os.path.join(ROOT, "MEASURED_PEAKS.json")))["bf16_tflops_sustained"])
+        except Exception:
+            tc, how = TC_FALLBACK_TFLOPS, "fallback"
+        achieved = flops / (kt.mean_ms(top) * 1e-3) / 1e12
+        roof = {"kernel": top, "bound": "tensor", "achieved": achieved, "peak": tc, "unit": "TFLOP/s", "frac": achieved / tc, "traffic": None,
+                "peak_source": how, "ms_per_launch": kt.mean_ms(top)}
+    roof["ms_per_step_by_entry_point"] = {k: round(v, 4) for k, v in sorted(per.items(), key=lambda kv: -kv[1])}
+    out = {
+        "metric": "train rays/s", "value": total_rays / (ms * 1e-3), "unit": "rays/s", "n_gpus": world, "steps": args.steps,
+        "warmup": max(3, args.warmup), "ms_per_step": ms / args.steps, "higher_is_better": True, "scaling": "weak",
+        "vs_baseline": None, "dtype": "f16", "data": "synthetic",
+        "config": {"workload": "configs[1]: single-object hash-grid NeRF train step (16 levels, 2^19 table, F=2, 64-wide FFMLPs, "
+                               "4096 rays/batch per GPU, cuda_ray, fp16, Adam)", "rays_per_gpu": RAYS_PER_GPU,
+                   "samples_per_step": samples, "parallelism": f"dp{world}" if world > 1 else "single",
+                   "l2": "fresh ray batch every step; step working set (fp32 table + Adam moments + fp16 copy + grads ~ 260 MB) exceeds the 126 MB L2"},
+        "clocks": clk,
+        "e2e": {"value": total_rays / (ms_e2e * 1e-3), "unit": "rays/s", "ms_per_step": ms_e2e / args.steps,
+                "h2d_bytes_per_step": world * RAYS_PER_GPU * 9 * 4, "d2h_bytes_per_step": world * 4},
+        "gpu_launches": kt.kernel_launches(),
+        "roofline": roof,
+    }
+    if world == 1:
+        out["cpu_baseline"] = cpu_baseline(scene, bits, cascade)
+    print(json.dumps(out))
+    if world > 1:
+        dist.destroy_process_group()
+
+
+def run_reference(args):
+    """Reference arm.  The reference has no CPU implementation of this path; its own CUDA extensions (oracle/_ref) are
+    timed by bench_ref.py when they load, else the oracle port on the host cores."""
+    rank = int(os.environ.get("RANK", 0))
+    if rank != 0:
+        return
+    try:
+        import bench_ref
+        print(json.dumps(bench_ref.run(args)))
+        return
+    except Exception as e:
+        note = f"reference extensions unavailable ({type(e).__name__}: {e}); CPU port timed instead"
+    import cases
+    scene, cascade, grid, bits, thresh = cases.scene_bitfield(1.0)
+    cb = cpu_baseline(scene, bits, cascade)
+    print(json.dumps({"impl": "reference", "metric": "train rays/s", "value": cb["value"], "unit": "rays/s", "n_gpus": int(os.environ.get("WORLD_SIZE", 1)),
+                      "steps": 1, "warmup": 1, "ms_per_step": 1e3 * 1024 / cb["value"], "higher_is_better": True, "scaling": "weak",
+                      "vs_baseline": None, "dtype": "f16", "data": "synthetic", "config": {"workload": "configs[1] (bounded sample)", "note": note},
+                      "cpu_baseline": cb, "e2e": {"value": cb["value"], "unit": "rays/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0}}))
+
+
+if __name__ == "__main__":
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--gpus", type=int, default=1)
+    ap.add_argument("--steps", type=int, default=64)
+    ap.add_argument("--warmup", type=int, default=8)
+    ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
+    a = ap.parse_args()
+    (run_reference if a.impl == "reference" else run_ours)(a)

@@ -96,3 +96,54 @@ def require_cuda(*tensors):
     for t in tensors:
         if t is not None and not t.is_cuda:
             raise RuntimeError("focnerf_b200 operators need CUDA tensors (there is no CPU path)")
+
+
+# ---------------------------------------------------------------------------------------------- per-entry-point timing
+class KernelTimer:
+    """Wraps selected `foc_*` entry points so every call is bracketed by CUDA events recorded on the launching
+    (current) stream; also counts every call.  Used by bench.py for `roofline.achieved` and `gpu_launches`.
+    Launch counts per entry point (kernels per call) are declared in LAUNCHES below."""
+
+    # kernels launched by one call of each entry point (see the C ABI implementations in csrc/)
+    LAUNCHES = {"foc_march_rays_train": 3, "foc_compact_alive": 2, "foc_ffmlp_backward": 2, "foc_sample_uniform": 2}
+
+    def __init__(self, names=()):
+        self.names, self.events, self.calls, self._orig = tuple(names), {}, {}, {}
+
+    def __enter__(self):
+        l = lib()
+        for name in _protos:
+            fn = getattr(l, name)
+            self._orig[name] = fn
+            self.calls[name] = 0
+            timed = name in self.names
+            if timed:
+                self.events[name] = []
+
+            def wrapper(*a, _fn=fn, _name=name, _timed=timed):
+                self.calls[_name] += 1
+                if not _timed:
+                    return _fn(*a)
+                s = torch.cuda.current_stream()
+                e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+                e0.record(s)
+                r = _fn(*a)
+                e1.record(s)
+                self.events[_name].append((e0, e1))
+                return r
+            setattr(l, name, wrapper)
+        return self
+
+    def __exit__(self, *exc):
+        l = lib()
+        for name, fn in self._orig.items():
+            setattr(l, name, fn)
+        return False
+
+    def mean_ms(self, name):
+        ev = self.events.get(name, [])
+        return sum(a.elapsed_time(b) for a, b in ev) / max(1, len(ev))
+
+    def kernel_launches(self):
+        skip = ("foc_abi_version", "foc_allocate_splitk", "foc_free_splitk")
+        return sum(n * self.LAUNCHES.get(k, 1) for k, n in self.calls.items() if not k.endswith("_bytes") and k not in skip)

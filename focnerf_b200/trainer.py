@@ -29,6 +29,7 @@ class Trainer:
             self.set_density_grid(density_grid, density_thresh)
         self.step_counter = torch.zeros(16, 2, dtype=torch.int32, device=self.device)     # renderer.py:96-98
         self.mean_count, self.local_step = 0, 0
+        self.grad_sync = None
         self.optimizer = torch.optim.Adam(self.model.get_params(lr), betas=(0.9, 0.99), eps=1e-15, fused=True)
         self.scaler = torch.amp.GradScaler("cuda", enabled=fp16)
 
@@ -62,6 +63,8 @@ class Trainer:
             image, _, _ = self.render_train(rays_o, rays_d, bg_color)
             loss = torch.nn.functional.mse_loss(image, gt_rgb)
         self.scaler.scale(loss).backward()
+        if self.grad_sync is not None:                 # data-parallel: all-reduce the (scaled) gradients over NCCL
+            self.grad_sync()
         self.scaler.step(self.optimizer)
         self.scaler.update()
         return loss

@@ -142,29 +142,46 @@ ORC_API void orc_ffmlp_backward(const uint16_t *grad, const uint16_t *inputs, co
         }
     }
     (void)acc_mode;
-    /* pass 2: weight gradients dW = dPre^T * Act_prev */
-    for (uint32_t o = 0; o < output_dim; ++o) for (uint32_t j = 0; j < hidden_dim; ++j) {
-        double s = 0.0;
-        for (uint32_t b = 0; b < B; ++b)
-            s += (double)h2f(grad[(size_t)b * output_dim + o]) * (double)h2f(forward_buffer[((size_t)(num_layers - 1) * B + b) * hidden_dim + j]);
-        grad_weights[in_sz + (size_t)(num_layers - 1) * hh + (size_t)o * hidden_dim + j] = s;
-    }
-    #pragma omp parallel for schedule(static)
-    for (int64_t m = 0; m < (int64_t)num_layers - 1; ++m) {
-        const uint16_t *d = backward_buffer + (size_t)(num_layers - 2 - m) * B * hidden_dim;
-        const uint16_t *f = forward_buffer + (size_t)m * B * hidden_dim;
-        for (uint32_t o = 0; o < hidden_dim; ++o) for (uint32_t j = 0; j < hidden_dim; ++j) {
-            double s = 0.0;
-            for (uint32_t b = 0; b < B; ++b) s += (double)h2f(d[(size_t)b * hidden_dim + o]) * (double)h2f(f[(size_t)b * hidden_dim + j]);
-            grad_weights[in_sz + (size_t)m * hh + (size_t)o * hidden_dim + j] = s;
+    /* pass 2: weight gradients dW = dPre^T * Act_prev (exact double sums).  Row-major walk over the batch: each thread
+     * accumulates outer products of contiguous rows into a private copy, reduced at the end. */
+    const size_t n_params = in_sz + (size_t)(num_layers - 1) * hh + (size_t)output_dim * hidden_dim;
+    #pragma omp parallel
+    {
+        double *acc = (double *)calloc(n_params, sizeof(double));
+        float *dv = (float *)malloc(sizeof(float) * hidden_dim), *av = (float *)malloc(sizeof(float) * (hidden_dim > input_dim ? hidden_dim : input_dim));
+        #pragma omp for schedule(static)
+        for (int64_t b = 0; b < (int64_t)B; ++b) {
+            /* output layer: dW_out[o][j] += grad[b][o] * A_{L-1}[b][j] */
+            const uint16_t *fl = forward_buffer + ((size_t)(num_layers - 1) * B + (size_t)b) * hidden_dim;
+            for (uint32_t j = 0; j < hidden_dim; ++j) av[j] = h2f(fl[j]);
+            for (uint32_t o = 0; o < output_dim; ++o) {
+                const double gv = (double)h2f(grad[(size_t)b * output_dim + o]);
+                double *row = acc + in_sz + (size_t)(num_layers - 1) * hh + (size_t)o * hidden_dim;
+                if (gv != 0.0) for (uint32_t j = 0; j < hidden_dim; ++j) row[j] += gv * (double)av[j];
+            }
+            /* hidden matrices m: dW[o][j] += dZ_{m+1}[b][o] * A_m[b][j];  dZ_{m+1} is backward_buffer slot num_layers-2-m */
+            for (uint32_t m = 0; m + 1 < num_layers; ++m) {
+                const uint16_t *d = backward_buffer + ((size_t)(num_layers - 2 - m) * B + (size_t)b) * hidden_dim;
+                const uint16_t *f = forward_buffer + ((size_t)m * B + (size_t)b) * hidden_dim;
+                for (uint32_t j = 0; j < hidden_dim; ++j) av[j] = h2f(f[j]);
+                for (uint32_t o = 0; o < hidden_dim; ++o) {
+                    const double gv = (double)h2f(d[o]);
+                    double *row = acc + in_sz + (size_t)m * hh + (size_t)o * hidden_dim;
+                    if (gv != 0.0) for (uint32_t j = 0; j < hidden_dim; ++j) row[j] += gv * (double)av[j];
+                }
+            }
+            /* input matrix: dW_in[o][i] += dZ_0[b][o] * x[b][i] */
+            const uint16_t *d0 = backward_buffer + ((size_t)(num_layers - 1) * B + (size_t)b) * hidden_dim;
+            for (uint32_t i = 0; i < input_dim; ++i) av[i] = h2f(inputs[(size_t)b * input_dim + i]);
+            for (uint32_t o = 0; o < hidden_dim; ++o) {
+                const double gv = (double)h2f(d0[o]);
+                double *row = acc + (size_t)o * input_dim;
+                if (gv != 0.0) for (uint32_t i = 0; i < input_dim; ++i) row[i] += gv * (double)av[i];
+            }
         }
-    }
-    const uint16_t *d = backward_buffer + (size_t)(num_layers - 1) * B * hidden_dim;
-    #pragma omp parallel for schedule(static)
-    for (int64_t o = 0; o < (int64_t)hidden_dim; ++o) for (uint32_t i = 0; i < input_dim; ++i) {
-        double s = 0.0;
-        for (uint32_t b = 0; b < B; ++b) s += (double)h2f(d[(size_t)b * hidden_dim + o]) * (double)h2f(inputs[(size_t)b * input_dim + i]);
-        grad_weights[(size_t)o * input_dim + i] = s;
+        #pragma omp critical
+        for (size_t k = 0; k < n_params; ++k) grad_weights[k] += acc[k];
+        free(acc); free(dv); free(av);
     }
 }
 

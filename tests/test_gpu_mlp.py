@@ -21,10 +21,14 @@ def rel(a, b):
     return float(np.abs(a.astype(np.float64) - b.astype(np.float64)).max()) / (float(np.abs(b).max()) + 1e-20)
 
 
-def _oracle(c, calc_grad_inputs=True):
+def _oracle(c, calc_grad_inputs=True, fb_for_backward=None):
+    """fb_for_backward: the stored activations of the implementation under test.  The backward is a function of those
+    (ReLU mask + wgrad operand): a unit whose exact pre-activation is ~0 can be 0 in one implementation and 1 fp16 ulp in
+    another, which switches a whole gradient row on or off -- a discontinuity, not an arithmetic error."""
     import oracle
     out, fb = oracle.ffmlp_forward(c["inputs"], c["weights"], c["input_dim"], 16, 64, c["num_layers"])
-    gw, bb, gi = oracle.ffmlp_backward(c["grad"], c["inputs"], c["weights"], fb, c["input_dim"], 16, 64, c["num_layers"],
+    fbb = fb if fb_for_backward is None else fb_for_backward.astype(np.float16)
+    gw, bb, gi = oracle.ffmlp_backward(c["grad"], c["inputs"], c["weights"], fbb, c["input_dim"], 16, 64, c["num_layers"],
                                       calc_grad_inputs=calc_grad_inputs)
     return dict(out=out.astype(np.float32), fb=fb.astype(np.float32), grad_weights=gw, grad_inputs=None if gi is None else gi.astype(np.float32))
 
@@ -33,7 +37,7 @@ def _oracle(c, calc_grad_inputs=True):
 def test_mlp_vs_oracle(input_dim, num_layers, B):
     c = cases.mlp_case(B, input_dim, 16, num_layers)
     got = runners.mlp_fwd_bwd(ours(), c)
-    exp = _oracle(c)
+    exp = _oracle(c, fb_for_backward=got["fb"])
     assert rel(got["out"], exp["out"]) <= 1e-3, "outputs"
     assert rel(got["out_inf"], exp["out"]) <= 1e-3, "inference outputs"
     assert rel(got["fb"], exp["fb"]) <= 1e-3, "forward_buffer"
@@ -48,11 +52,16 @@ def test_mlp_vs_reference(input_dim, num_layers):
         pytest.skip("oracle/_ref/ffmlp not built")
     ref.allocate_splitk(num_layers + 1)
     c = cases.mlp_case(8192, input_dim, 16, num_layers, seed=14)
-    a, b, exp = runners.mlp_fwd_bwd(ours(), c), runners.mlp_fwd_bwd(ref, c), _oracle(c)
+    a, b = runners.mlp_fwd_bwd(ours(), c), runners.mlp_fwd_bwd(ref, c)
+    exp_a, exp_b = _oracle(c, fb_for_backward=a["fb"]), _oracle(c, fb_for_backward=b["fb"])
     for k in ("out", "fb", "grad_inputs", "grad_weights"):
-        ref_noise = rel(b[k], exp[k])                       # the reference's own fp16-accumulation error
-        assert rel(a[k], exp[k]) <= max(1e-3, 0.5 * ref_noise) + 1e-3, k
-        assert rel(a[k], b[k]) <= 1.5 * ref_noise + 2e-3, f"{k}: ours vs reference {rel(a[k], b[k]):.2e}, reference vs exact {ref_noise:.2e}"
+        ref_noise = rel(b[k], exp_b[k])                     # the reference's own fp16-accumulation error vs exact
+        ours_err = rel(a[k], exp_a[k])
+        assert ours_err <= 2e-3, f"{k}: ours vs exact {ours_err:.2e}"
+        assert ours_err <= ref_noise + 1e-3, f"{k}: ours {ours_err:.2e} should be at least as close to exact as the reference {ref_noise:.2e}"
+    # forward results: ours vs the reference directly, bounded by the reference's own distance from exact
+    for k in ("out", "fb"):
+        assert rel(a[k], b[k]) <= 2 * rel(b[k], exp_b[k]) + 1e-3, k
 
 
 def test_ffmlp_module_matches_reference_wrapper_semantics():
