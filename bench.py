@@ -131,7 +131,8 @@ def run_ours(args):
         dist.init_process_group("nccl")
     dev = torch.device("cuda", local)
     scene, cascade, grid, bits, thresh = cases.scene_bitfield(1.0)
-    tr = Trainer(bound=1.0, density_grid=torch.from_numpy(grid), device=dev, seed=0)
+    use_graph = (not args.no_graph) and (world == 1 or os.environ.get("FOC_GRAPH_DP", "1") == "1")
+    tr = Trainer(bound=1.0, density_grid=torch.from_numpy(grid), device=dev, seed=0, fused=not args.no_fused, use_graph=use_graph)
     params = [p for p in tr.model.parameters()]
     if world > 1:                                   # data-parallel: identical replicas, gradients all-reduced every step
         for p in params:
@@ -160,13 +161,17 @@ def run_ours(args):
     clocks = ClockSampler(local)
     if rank == 0:
         clocks.start()
-    with _lib.KernelTimer(TIMED) as kt:
-        sync_all()
-        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
-        e0.record()
-        loop(args.steps, False, 100)
-        e1.record()
-        sync_all()
+    sync_all()
+    prof = os.environ.get("FOC_PROFILE") == "1"     # ncu --profile-from-start off: capture the timed region only
+    if prof:
+        torch.cuda.profiler.start()
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    e0.record()
+    loop(args.steps, False, 100)
+    e1.record()
+    sync_all()
+    if prof:
+        torch.cuda.profiler.stop()
     ms = torch.tensor([e0.elapsed_time(e1)], device=dev)
     if world > 1:
         dist.all_reduce(ms, op=dist.ReduceOp.MAX)
@@ -187,6 +192,17 @@ def run_ours(args):
         dist.all_reduce(ms_e2e, op=dist.ReduceOp.MAX)
     ms_e2e = float(ms_e2e.item())
 
+    # per-entry-point device times: the SAME step run eagerly (a graph replay cannot carry per-kernel events), with CUDA
+    # events around every C-ABI call on the launching stream.  Not part of `value`; feeds roofline + gpu_launches.
+    tr.use_graph = False
+    n_prof = min(args.steps, 32)
+    loop(3, False, 400)
+    with _lib.KernelTimer(TIMED) as kt:
+        sync_all()
+        loop(n_prof, False, 500)
+        sync_all()
+    tr.use_graph = use_graph
+
     if rank != 0:
         if world > 1:
             dist.destroy_process_group()
@@ -194,14 +210,14 @@ def run_ours(args):
     total_rays = world * RAYS_PER_GPU * args.steps
     hbm, how = peaks()
     # dominant kernel among OUR entry points, by mean device time per call inside the timed region
-    per = {k: kt.mean_ms(k) * len(kt.events[k]) / args.steps for k in TIMED if kt.events.get(k)}
+    per = {k: kt.mean_ms(k) * len(kt.events[k]) / n_prof for k in TIMED if kt.events.get(k)}
     top = max(per, key=per.get)
     if top in ALG_BYTES:
         achieved = ALG_BYTES[top] * samples / (kt.mean_ms(top) * 1e-3) / 1e9
         roof = {"kernel": top, "bound": "hbm", "achieved": achieved, "peak": hbm, "unit": "GB/s", "frac": achieved / hbm, "traffic": None,
                 "peak_source": how, "ms_per_launch": kt.mean_ms(top)}
     else:                                            # fused MLPs: the only dense contraction -> tensor pipe
-        calls = len(kt.events[top]) / args.steps     # sigma + colour net per step
+        calls = len(kt.events[top]) / n_prof         # sigma + colour net per step
         flops = (36864 if top == "foc_ffmlp_forward" else 2 * 36864) * samples / calls
         try:
             tc = float(json.load(open(os.path.join(ROOT, "MEASURED_PEAKS.json")))["bf16_tflops_sustained"])
@@ -218,11 +234,12 @@ def run_ours(args):
         "config": {"workload": "configs[1]: single-object hash-grid NeRF train step (16 levels, 2^19 table, F=2, 64-wide FFMLPs, "
                                "4096 rays/batch per GPU, cuda_ray, fp16, Adam)", "rays_per_gpu": RAYS_PER_GPU,
                    "samples_per_step": samples, "parallelism": f"dp{world}" if world > 1 else "single",
+                   "cuda_graph": use_graph, "fused_glue": not args.no_fused,
                    "l2": "fresh ray batch every step; step working set (fp32 table + Adam moments + fp16 copy + grads ~ 260 MB) exceeds the 126 MB L2"},
         "clocks": clk,
         "e2e": {"value": total_rays / (ms_e2e * 1e-3), "unit": "rays/s", "ms_per_step": ms_e2e / args.steps,
                 "h2d_bytes_per_step": world * RAYS_PER_GPU * 9 * 4, "d2h_bytes_per_step": world * 4},
-        "gpu_launches": kt.kernel_launches(),
+        "gpu_launches": int(round(kt.kernel_launches() / n_prof * args.steps)),
         "roofline": roof,
     }
     if world == 1:
@@ -259,5 +276,7 @@ if __name__ == "__main__":
     ap.add_argument("--steps", type=int, default=64)
     ap.add_argument("--warmup", type=int, default=8)
     ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
+    ap.add_argument("--no-graph", action="store_true", help="launch the step eagerly instead of replaying a CUDA graph")
+    ap.add_argument("--no-fused", action="store_true", help="field network through the unfused operator modules")
     a = ap.parse_args()
     (run_reference if a.impl == "reference" else run_ours)(a)

@@ -24,8 +24,8 @@ namespace {
 constexpr int kTile = 128, kHidden = 64, kOutPad = 16, kMaxLayers = 8;
 constexpr uint32_t kTileBytes = kTile * kHidden * 2;     // 16 KB: one [128, 64] fp16 tile
 
-// ffmlp/src/utils.h:537-582: derivative through the stored POST-activation value
-__device__ __forceinline__ float act_bwd(uint32_t a, float g, float fwd) {
+// ffmlp/src/utils.h:537-582: derivative through the stored POST-activation value.  Out of line (code size; see mlp_fwd.cu).
+__device__ __noinline__ float act_bwd_generic(uint32_t a, float g, float fwd) {
     switch (a) {
         case 0: return fwd > 0.f ? g : 0.f;
         case 1: return g * fwd;
@@ -34,6 +34,13 @@ __device__ __forceinline__ float act_bwd(uint32_t a, float g, float fwd) {
         case 5: return g * (1.0f - __expf(-fwd * 10.0f));
         default: return g;
     }
+}
+
+template <int ACT>
+__device__ __forceinline__ float act_bwd(uint32_t a, float g, float fwd) {
+    if constexpr (ACT == 0) return fwd > 0.f ? g : 0.f;
+    else if constexpr (ACT == 6) return g;
+    else return act_bwd_generic(a, g, fwd);
 }
 
 struct BwdParams {
@@ -58,7 +65,7 @@ struct BwdSmem {
     __host__ __device__ static uint32_t total(int L) { return off_bars(L) + 64 + 1024; }
 };
 
-template <int IN>
+template <int IN, int ACT>
 __global__ void __launch_bounds__(128)
 k_mlp_bwd(const __grid_constant__ CUtensorMap tm_fb, const __grid_constant__ CUtensorMap tm_in, BwdParams p) {
     using SM = BwdSmem<IN>;
@@ -177,7 +184,7 @@ k_mlp_bwd(const __grid_constant__ CUtensorMap tm_fb, const __grid_constant__ CUt
                     // the reference keeps dA in fp16 fragments before the activation transfer (ffmlp.cu:459-470)
                     const float g0 = __half2float(__float2half_rn(__uint_as_float(acc[col >> 4][col & 15])));
                     const float g1 = __half2float(__float2half_rn(__uint_as_float(acc[(col + 1) >> 4][(col + 1) & 15])));
-                    const __half2 h = __floats2half2_rn(act_bwd(p.activation, g0, a.x), act_bwd(p.activation, g1, a.y));
+                    const __half2 h = __floats2half2_rn(act_bwd<ACT>(p.activation, g0, a.x), act_bwd<ACT>(p.activation, g1, a.y));
                     w[j] = *reinterpret_cast<const uint32_t*>(&h);
                 }
                 packed[c] = make_uint4(w[0], w[1], w[2], w[3]);
@@ -297,14 +304,27 @@ k_mlp_bwd(const __grid_constant__ CUtensorMap tm_fb, const __grid_constant__ CUt
     if (warp == 0) tmem_dealloc(tmem, p.tmem_cols);
 }
 
-// fixed-order reduction of the per-CTA partials, narrowed to fp16 (the reference's grad_weights dtype)
+// fixed-order reduction of the per-CTA partials, narrowed to fp16 (the reference's grad_weights dtype).
+// Block = 32 parameters x 8 slices of the CTA range: each thread sums its slice (coalesced 128-byte rows), the 8 slice
+// sums are combined in a fixed order through shared memory -> deterministic, and 8x shorter dependent-load chains.
 __global__ void __launch_bounds__(256)
 k_mlp_wgrad_finish(const float* __restrict__ partials, uint32_t n_cta, uint32_t num_params, __half* __restrict__ grad_weights) {
-    const uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
-    if (i >= num_params) return;
-    float s = 0.f;
-    for (uint32_t c = 0; c < n_cta; ++c) s += __ldg(partials + (size_t)c * num_params + i);
-    grad_weights[i] = __float2half_rn(s);
+    __shared__ float s[8][32];
+    const uint32_t lane = threadIdx.x & 31, slice = threadIdx.x >> 5;
+    const uint32_t i = blockIdx.x * 32 + lane;
+    float acc = 0.f;
+    if (i < num_params) {
+        const uint32_t per = (n_cta + 7) / 8, c0 = slice * per, c1 = min(n_cta, c0 + per);
+        for (uint32_t c = c0; c < c1; ++c) acc += __ldg(partials + (size_t)c * num_params + i);
+    }
+    s[slice][lane] = acc;
+    __syncthreads();
+    if (slice == 0 && i < num_params) {
+        float t = 0.f;
+        #pragma unroll
+        for (int k = 0; k < 8; ++k) t += s[k][lane];
+        grad_weights[i] = __float2half_rn(t);
+    }
 }
 
 uint32_t bwd_grid(uint32_t B) {
@@ -313,7 +333,7 @@ uint32_t bwd_grid(uint32_t B) {
 }
 uint32_t num_params_of(uint32_t input_dim, uint32_t num_layers) { return kHidden * (input_dim + kHidden * (num_layers - 1) + kOutPad); }
 
-template <int IN>
+template <int IN, int ACT>
 int launch_bwd(const uint16_t* grad, const uint16_t* inputs, const uint16_t* weights, const uint16_t* forward_buffer, uint32_t B,
                uint32_t num_layers, uint32_t activation, int calc_grad_inputs, uint16_t* backward_buffer, uint16_t* grad_inputs,
                uint16_t* grad_weights, void* scratch, cudaStream_t st) {
@@ -327,7 +347,7 @@ int launch_bwd(const uint16_t* grad, const uint16_t* inputs, const uint16_t* wei
     if (smem > 227 * 1024) return FOC_ERR_UNSUPPORTED;
     static bool attr_set = false;
     if (!attr_set) {
-        cudaError_t e = cudaFuncSetAttribute(k_mlp_bwd<IN>, cudaFuncAttributeMaxDynamicSharedMemorySize, 227 * 1024);
+        cudaError_t e = cudaFuncSetAttribute(k_mlp_bwd<IN, ACT>, cudaFuncAttributeMaxDynamicSharedMemorySize, 227 * 1024);
         if (e != cudaSuccess) return (int)e;
         attr_set = true;
     }
@@ -343,9 +363,9 @@ int launch_bwd(const uint16_t* grad, const uint16_t* inputs, const uint16_t* wei
     p.tmem_cols = need <= 128 ? 128 : need <= 256 ? 256 : 512;
     if (need > 512) return FOC_ERR_UNSUPPORTED;
     const uint32_t grid = bwd_grid(B);
-    k_mlp_bwd<IN><<<grid, 128, smem, st>>>(tm_fb, tm_in, p);
+    k_mlp_bwd<IN, ACT><<<grid, 128, smem, st>>>(tm_fb, tm_in, p);
     FOC_LAUNCH_CHECK();
-    k_mlp_wgrad_finish<<<ceil_div(p.num_params, 256), 256, 0, st>>>(p.partials, grid, p.num_params, reinterpret_cast<__half*>(grad_weights));
+    k_mlp_wgrad_finish<<<ceil_div(p.num_params, 32), 256, 0, st>>>(p.partials, grid, p.num_params, reinterpret_cast<__half*>(grad_weights));
     FOC_LAUNCH_CHECK(); return 0;
 }
 
@@ -365,7 +385,10 @@ FOC_API int foc_ffmlp_backward(const uint16_t* grad, const uint16_t* inputs, con
     if (hidden_dim != (uint32_t)kHidden || output_dim != (uint32_t)kOutPad || num_layers < 1 || num_layers > (uint32_t)kMaxLayers ||
         B % kTile != 0 || output_activation != 6 || activation == 2 || !scratch) return FOC_ERR_UNSUPPORTED;
     cudaStream_t st = reinterpret_cast<cudaStream_t>(stream);
-    if (input_dim == 32) return launch_bwd<32>(grad, inputs, weights, forward_buffer, B, num_layers, activation, calc_grad_inputs, backward_buffer, grad_inputs, grad_weights, scratch, st);
-    if (input_dim == 64) return launch_bwd<64>(grad, inputs, weights, forward_buffer, B, num_layers, activation, calc_grad_inputs, backward_buffer, grad_inputs, grad_weights, scratch, st);
+#define FOC_BWD(IN_, ACT_) launch_bwd<IN_, ACT_>(grad, inputs, weights, forward_buffer, B, num_layers, activation, calc_grad_inputs, \
+                                               backward_buffer, grad_inputs, grad_weights, scratch, st)
+    if (input_dim == 32) return activation == 0 ? FOC_BWD(32, 0) : activation == 6 ? FOC_BWD(32, 6) : FOC_BWD(32, -1);
+    if (input_dim == 64) return activation == 0 ? FOC_BWD(64, 0) : activation == 6 ? FOC_BWD(64, 6) : FOC_BWD(64, -1);
+#undef FOC_BWD
     return FOC_ERR_UNSUPPORTED;
 }

@@ -25,8 +25,9 @@ constexpr int kHidden = 64;         // hidden width (the FOC networks are 64 wid
 constexpr int kOutPad = 16;         // padded output rows of W_out (ffmlp.cu:632)
 constexpr int kMaxLayers = 8;
 
-// ffmlp/src/utils.h:424-470
-__device__ __forceinline__ float act_fwd(uint32_t a, float v) {
+// ffmlp/src/utils.h:424-470.  Kept OUT of line: inlining this switch at each of the 64 elements of the unrolled epilogue
+// made the kernel > 64 KB of SASS and a third of its stall samples were instruction-fetch misses (profiles/r1).
+__device__ __noinline__ float act_fwd_generic(uint32_t a, float v) {
     switch (a) {
         case 0: return v > 0.f ? v : 0.f;
         case 1: return __expf(v);
@@ -36,6 +37,14 @@ __device__ __forceinline__ float act_fwd(uint32_t a, float v) {
         case 5: return __logf(__expf(v * 10.0f) + 1.0f) / 10.0f;
         default: return v;
     }
+}
+
+// ACT is a compile-time activation: 0 = ReLU, 6 = none, anything else = run-time value through act_fwd_generic
+template <int ACT>
+__device__ __forceinline__ float act_fwd(uint32_t a, float v) {
+    if constexpr (ACT == 0) return fmaxf(v, 0.0f);
+    else if constexpr (ACT == 6) return v;
+    else return act_fwd_generic(a, v);
 }
 
 struct FwdParams {
@@ -61,7 +70,7 @@ struct FwdSmem {
     __host__ __device__ static uint32_t total(int n_hidden_mm) { return off_bars(n_hidden_mm) + 64 + 1024 /* base alignment slack */; }
 };
 
-template <int IN>
+template <int IN, int ACT>
 __global__ void __launch_bounds__(128)
 k_mlp_fwd(const __grid_constant__ CUtensorMap tm_in, const __grid_constant__ CUtensorMap tm_win,
           const __grid_constant__ CUtensorMap tm_w, FwdParams p) {
@@ -145,8 +154,8 @@ k_mlp_fwd(const __grid_constant__ CUtensorMap tm_in, const __grid_constant__ CUt
                 #pragma unroll
                 for (int j = 0; j < 4; ++j) {
                     const int col = c * 8 + j * 2;
-                    const float a = act_fwd(p.activation, __uint_as_float(acc[col >> 4][col & 15]));
-                    const float b = act_fwd(p.activation, __uint_as_float(acc[(col + 1) >> 4][(col + 1) & 15]));
+                    const float a = act_fwd<ACT>(p.activation, __uint_as_float(acc[col >> 4][col & 15]));
+                    const float b = act_fwd<ACT>(p.activation, __uint_as_float(acc[(col + 1) >> 4][(col + 1) & 15]));
                     const __half2 h = __floats2half2_rn(a, b);
                     w[j] = *reinterpret_cast<const uint32_t*>(&h);
                 }
@@ -184,8 +193,9 @@ k_mlp_fwd(const __grid_constant__ CUtensorMap tm_in, const __grid_constant__ CUt
         uint32_t w[8];
         #pragma unroll
         for (int j = 0; j < 8; ++j) {
-            const __half2 h = __floats2half2_rn(act_fwd(p.output_activation, __uint_as_float(o[2 * j])),
-                                                act_fwd(p.output_activation, __uint_as_float(o[2 * j + 1])));
+            float v0 = __uint_as_float(o[2 * j]), v1 = __uint_as_float(o[2 * j + 1]);
+            if (p.output_activation != 6) { v0 = act_fwd_generic(p.output_activation, v0); v1 = act_fwd_generic(p.output_activation, v1); }
+            const __half2 h = __floats2half2_rn(v0, v1);
             w[j] = *reinterpret_cast<const uint32_t*>(&h);
         }
         uint4* dst = reinterpret_cast<uint4*>(p.outputs + grow * kOutPad);
@@ -197,7 +207,7 @@ k_mlp_fwd(const __grid_constant__ CUtensorMap tm_in, const __grid_constant__ CUt
     if (warp == 0) tmem_dealloc(tmem, 64);
 }
 
-template <int IN>
+template <int IN, int ACT>
 int launch_fwd(const uint16_t* inputs, const uint16_t* weights, uint32_t B, uint32_t num_layers, uint32_t activation,
                uint32_t output_activation, uint16_t* forward_buffer, uint16_t* outputs, cudaStream_t st) {
     using SM = FwdSmem<IN>;
@@ -212,7 +222,7 @@ int launch_fwd(const uint16_t* inputs, const uint16_t* weights, uint32_t B, uint
     const uint32_t smem = SM::total(n_hmm);
     static bool attr_set = false;                                      // idempotent; racing threads set the same value
     if (!attr_set) {
-        cudaError_t e = cudaFuncSetAttribute(k_mlp_fwd<IN>, cudaFuncAttributeMaxDynamicSharedMemorySize, 96 * 1024);
+        cudaError_t e = cudaFuncSetAttribute(k_mlp_fwd<IN, ACT>, cudaFuncAttributeMaxDynamicSharedMemorySize, 96 * 1024);
         if (e != cudaSuccess) return (int)e;
         attr_set = true;
     }
@@ -225,7 +235,7 @@ int launch_fwd(const uint16_t* inputs, const uint16_t* weights, uint32_t B, uint
     p.num_tiles = B / kTile;
     const uint32_t ctas_per_sm = 4;                                    // 4 x 64 TMEM columns, ~4 x 45 KB shared memory
     const uint32_t grid = p.num_tiles < (uint32_t)kNumSMs * ctas_per_sm ? p.num_tiles : (uint32_t)kNumSMs * ctas_per_sm;
-    k_mlp_fwd<IN><<<grid, 128, smem, st>>>(tm_in, tm_win, tm_w, p);
+    k_mlp_fwd<IN, ACT><<<grid, 128, smem, st>>>(tm_in, tm_win, tm_w, p);
     FOC_LAUNCH_CHECK(); return 0;
 }
 
@@ -239,7 +249,12 @@ FOC_API int foc_ffmlp_forward(const uint16_t* inputs, const uint16_t* weights, u
     if (hidden_dim != (uint32_t)kHidden || output_dim > (uint32_t)kOutPad || num_layers < 1 || num_layers > (uint32_t)kMaxLayers ||
         B % kTile != 0) return FOC_ERR_UNSUPPORTED;
     cudaStream_t st = reinterpret_cast<cudaStream_t>(stream);
-    if (input_dim == 32) return launch_fwd<32>(inputs, weights, B, num_layers, activation, output_activation, forward_buffer, outputs, st);
-    if (input_dim == 64) return launch_fwd<64>(inputs, weights, B, num_layers, activation, output_activation, forward_buffer, outputs, st);
+#define FOC_FWD(IN_) \
+    return activation == 0 ? launch_fwd<IN_, 0>(inputs, weights, B, num_layers, activation, output_activation, forward_buffer, outputs, st) \
+         : activation == 6 ? launch_fwd<IN_, 6>(inputs, weights, B, num_layers, activation, output_activation, forward_buffer, outputs, st) \
+                           : launch_fwd<IN_, -1>(inputs, weights, B, num_layers, activation, output_activation, forward_buffer, outputs, st)
+    if (input_dim == 32) { FOC_FWD(32); }
+    if (input_dim == 64) { FOC_FWD(64); }
+#undef FOC_FWD
     return FOC_ERR_UNSUPPORTED;
 }

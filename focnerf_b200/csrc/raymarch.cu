@@ -185,20 +185,35 @@ __global__ void __launch_bounds__(256) k_packbits_bytes(const float* __restrict_
 
 // ------------------------------------------------------------------------------------------------ training march
 
-// pass 1 (raymarching.cu:353-400): count occupied steps of every ray.
-__global__ void __launch_bounds__(128) k_march_count(const float* __restrict__ rays_o, const float* __restrict__ rays_d,
-                                                     const float* __restrict__ nears, const float* __restrict__ fars,
-                                                     const float* __restrict__ noises, uint32_t N, uint32_t max_steps,
-                                                     MarchParams p, uint32_t* __restrict__ counts) {
-    const uint32_t n = blockIdx.x * blockDim.x + threadIdx.x;
-    if (n >= N) return;
+// Thread -> ray mapping of the serial pass.  A ray's march is a dependent chain of ~100-250 probes; with a 4096-ray
+// training batch, one ray per lane gives only 128 warps for 592 warp schedulers, and each warp iterates to the LONGEST of
+// its 32 rays while executing both sides of the occupied/empty branch (profiles/r1: IPC 0.15, 1.5 % of warp slots).
+// For small batches only RPW lanes of each warp carry a ray: 32/RPW x more warps in flight, max over RPW rays not 32.
+template <int RPW>
+__device__ __forceinline__ bool ray_of_thread(uint32_t N, uint32_t& n) {
+    const uint32_t g = blockIdx.x * blockDim.x + threadIdx.x, lane = g & 31u;
+    n = (g >> 5) * RPW + lane;
+    return lane < (uint32_t)RPW && n < N;
+}
+
+// pass 1 (raymarching.cu:353-400): walk the ray ONCE, count its occupied steps and record the parameter t of each.
+// tbuf[n * max_steps + s] = t at which sample s of ray n is taken.
+template <int RPW>
+__global__ void __launch_bounds__(128) k_march_record(const float* __restrict__ rays_o, const float* __restrict__ rays_d,
+                                                      const float* __restrict__ nears, const float* __restrict__ fars,
+                                                      const float* __restrict__ noises, uint32_t N, uint32_t max_steps,
+                                                      MarchParams p, uint32_t* __restrict__ counts, float* __restrict__ tbuf) {
+    uint32_t n;
+    if (!ray_of_thread<RPW>(N, n)) return;
     const Ray r = load_ray(rays_o, rays_d, n, __ldg(fars + n));
     const float near = __ldg(nears + n);
     float t = ffma(step_dt(p, near), __ldg(noises + n), near);          // t0 = near + clamp(near*gamma)*noise (one FMA, l.351)
+    float* tb = tbuf + (size_t)n * max_steps;
     uint32_t num = 0;
     float x, y, z, dt;
     while (t < r.far && num < max_steps) {
-        if (probe(p, r, t, x, y, z, dt)) { ++num; t = fadd(t, dt); }
+        const float tc = t;
+        if (probe(p, r, t, x, y, z, dt)) { tb[num++] = tc; t = fadd(tc, dt); }
     }
     counts[n] = num;
 }
@@ -236,30 +251,34 @@ __global__ void __launch_bounds__(1024) k_march_scan(const uint32_t* __restrict_
     if (threadIdx.x == 0) { counter[0] = (int32_t)s_base; counter[1] += (int32_t)N; }
 }
 
-// pass 2 (raymarching.cu:404-479): re-walk and write the ray's slice.
-__global__ void __launch_bounds__(128) k_march_write(const float* __restrict__ rays_o, const float* __restrict__ rays_d,
-                                                     const float* __restrict__ nears, const float* __restrict__ fars,
-                                                     const float* __restrict__ noises, uint32_t N, uint32_t M,
-                                                     MarchParams p, const int32_t* __restrict__ rays,
-                                                     float* __restrict__ xyzs, float* __restrict__ dirs, float* __restrict__ deltas) {
-    const uint32_t n = blockIdx.x * blockDim.x + threadIdx.x;
+// pass 2 (raymarching.cu:404-479), now data-parallel: ONE WARP PER RAY expands the recorded t's into samples with the
+// same float operations the serial walk would have applied, and writes its slice with coalesced 12/12/8-byte rows.
+//   x = clamp(o + t d);  dt = clamp(t gamma);  delta1 = (t + dt) - last_t,  last_t = previous sample's t + dt (t0 first).
+__global__ void __launch_bounds__(128) k_march_expand(const float* __restrict__ rays_o, const float* __restrict__ rays_d,
+                                                      const float* __restrict__ nears, const float* __restrict__ noises,
+                                                      uint32_t N, uint32_t M, uint32_t max_steps, MarchParams p,
+                                                      const int32_t* __restrict__ rays, const float* __restrict__ tbuf,
+                                                      float* __restrict__ xyzs, float* __restrict__ dirs, float* __restrict__ deltas) {
+    const uint32_t n = (blockIdx.x * blockDim.x + threadIdx.x) >> 5, lane = threadIdx.x & 31u;
     if (n >= N) return;
-    const uint32_t off = (uint32_t)rays[3 * (size_t)n + 1], num = (uint32_t)rays[3 * (size_t)n + 2];
-    if (num == 0 || off + num > M) return;
-    const Ray r = load_ray(rays_o, rays_d, n, __ldg(fars + n));
+    const uint32_t off = (uint32_t)__ldg(rays + 3 * (size_t)n + 1), num = (uint32_t)__ldg(rays + 3 * (size_t)n + 2);
+    if (num == 0 || (uint64_t)off + num > M) return;                  // raymarching.cu:415-416
+    const float ox = __ldg(rays_o + 3 * (size_t)n), oy = __ldg(rays_o + 3 * (size_t)n + 1), oz = __ldg(rays_o + 3 * (size_t)n + 2);
+    const float dx = __ldg(rays_d + 3 * (size_t)n), dy = __ldg(rays_d + 3 * (size_t)n + 1), dz = __ldg(rays_d + 3 * (size_t)n + 2);
     const float near = __ldg(nears + n);
-    float t = ffma(step_dt(p, near), __ldg(noises + n), near);
-    float last_t = t, x, y, z, dt;
-    float* px = xyzs + 3 * (size_t)off; float* pd = dirs + 3 * (size_t)off; float* pl = deltas + 2 * (size_t)off;
-    uint32_t step = 0;
-    while (t < r.far && step < num) {
-        if (!probe(p, r, t, x, y, z, dt)) continue;
-        px[0] = x; px[1] = y; px[2] = z;
-        pd[0] = r.dx; pd[1] = r.dy; pd[2] = r.dz;
-        t = fadd(t, dt);
-        pl[0] = dt; pl[1] = fsub(t, last_t);
-        last_t = t;
-        px += 3; pd += 3; pl += 2; ++step;
+    const float t0 = ffma(step_dt(p, near), __ldg(noises + n), near);
+    const float* tb = tbuf + (size_t)n * max_steps;
+    for (uint32_t s = lane; s < num; s += 32) {
+        const float t = __ldg(tb + s);
+        float last = t0;
+        if (s > 0) { const float tp = __ldg(tb + s - 1); last = fadd(tp, step_dt(p, tp)); }
+        const float dt = step_dt(p, t), tn = fadd(t, dt);
+        const size_t i = (size_t)off + s;
+        xyzs[3 * i] = clampf(ffma(t, dx, ox), -p.bound, p.bound);
+        xyzs[3 * i + 1] = clampf(ffma(t, dy, oy), -p.bound, p.bound);
+        xyzs[3 * i + 2] = clampf(ffma(t, dz, oz), -p.bound, p.bound);
+        dirs[3 * i] = dx; dirs[3 * i + 1] = dy; dirs[3 * i + 2] = dz;
+        reinterpret_cast<float2*>(deltas)[i] = make_float2(dt, fsub(tn, last));
     }
 }
 
@@ -324,7 +343,11 @@ FOC_API int foc_packbits(const float* grid, uint32_t N, float density_thresh, ui
     FOC_LAUNCH_CHECK(); return 0;
 }
 
-FOC_API size_t foc_march_rays_train_scratch_bytes(uint32_t N) { return (size_t)N * sizeof(uint32_t); }
+// scratch = counts [N] u32 (rounded up to 256 B) + recorded sample parameters [N, max_steps] f32
+static inline size_t march_counts_bytes(uint32_t N) { return (((size_t)N * sizeof(uint32_t)) + 255) & ~(size_t)255; }
+FOC_API size_t foc_march_rays_train_scratch_bytes(uint32_t N, uint32_t max_steps) {
+    return march_counts_bytes(N) + (size_t)N * max_steps * sizeof(float);
+}
 
 // small N (a training batch) is latency-bound: one warp per CTA spreads the rays over all SMs
 static inline uint32_t march_block(uint32_t n) { return n <= (uint32_t)kNumSMs * 32u * 8u ? 32u : 128u; }
@@ -337,12 +360,16 @@ FOC_API int foc_march_rays_train(const float* rays_o, const float* rays_d, const
     if (C == 0 || C > 8 || H == 0 || H > 1024 || (uint64_t)C * H * H * H > (1ull << 24)) return FOC_ERR_UNSUPPORTED;  // fp32 cell index exact (H1)
     const MarchParams p = make_march_params(grid, bound, dt_gamma, max_steps, C, H);
     uint32_t* counts = static_cast<uint32_t*>(scratch);
-    const uint32_t bs = march_block(N);
-    k_march_count<<<ceil_div(N, bs), bs, 0, S(stream)>>>(rays_o, rays_d, nears, fars, noises, N, max_steps, p, counts);
+    float* tbuf = reinterpret_cast<float*>(static_cast<uint8_t*>(scratch) + march_counts_bytes(N));
+    // small batches: 4 rays per warp (see ray_of_thread); large ones: every lane carries a ray
+    if (N <= (uint32_t)kNumSMs * 32u * 8u)
+        k_march_record<4><<<ceil_div(ceil_div(N, 4) * 32, 128), 128, 0, S(stream)>>>(rays_o, rays_d, nears, fars, noises, N, max_steps, p, counts, tbuf);
+    else
+        k_march_record<32><<<ceil_div(N, 128), 128, 0, S(stream)>>>(rays_o, rays_d, nears, fars, noises, N, max_steps, p, counts, tbuf);
     FOC_LAUNCH_CHECK();
     k_march_scan<<<1, 1024, 0, S(stream)>>>(counts, N, rays, counter);
     FOC_LAUNCH_CHECK();
-    k_march_write<<<ceil_div(N, bs), bs, 0, S(stream)>>>(rays_o, rays_d, nears, fars, noises, N, M, p, rays, xyzs, dirs, deltas);
+    k_march_expand<<<ceil_div(N, 4), 128, 0, S(stream)>>>(rays_o, rays_d, nears, noises, N, M, max_steps, p, rays, tbuf, xyzs, dirs, deltas);
     FOC_LAUNCH_CHECK(); return 0;
 }
 

@@ -43,7 +43,7 @@ class _Backend:
     def march_rays_train(rays_o, rays_d, grid, bound, dt_gamma, max_steps, N, C, H, M, nears, fars, xyzs, dirs, deltas,
                          rays, counter, noises):
         require_cuda(rays_o, rays_d, grid, nears, fars, xyzs, dirs, deltas, rays, counter, noises)
-        scratch = torch.empty(max(1, lib().foc_march_rays_train_scratch_bytes(N)), dtype=torch.uint8, device=rays_o.device)
+        scratch = torch.empty(max(1, lib().foc_march_rays_train_scratch_bytes(N, max_steps)), dtype=torch.uint8, device=rays_o.device)
         check(lib().foc_march_rays_train(ptr(rays_o), ptr(rays_d), ptr(grid), bound, dt_gamma, max_steps, N, C, H, M,
                                          ptr(nears), ptr(fars), ptr(xyzs), ptr(dirs), ptr(deltas), ptr(rays), ptr(counter),
                                          ptr(noises), ptr(scratch), stream()), "march_rays_train")

@@ -13,7 +13,7 @@ from .network import NeRFNetwork
 
 class Trainer:
     def __init__(self, bound=1.0, density_grid=None, density_thresh=10.0, min_near=0.2, dt_gamma=0.0, max_steps=1024,
-                 lr=1e-2, fp16=True, device="cuda", grid_size=128, seed=0):
+                 lr=1e-2, fp16=True, device="cuda", grid_size=128, seed=0, fused=True, use_graph=False):
         if not torch.cuda.is_available():
             raise RuntimeError("focnerf_b200.Trainer needs a CUDA device (there is no CPU path)")
         import math
@@ -30,7 +30,12 @@ class Trainer:
         self.step_counter = torch.zeros(16, 2, dtype=torch.int32, device=self.device)     # renderer.py:96-98
         self.mean_count, self.local_step = 0, 0
         self.grad_sync = None
-        self.optimizer = torch.optim.Adam(self.model.get_params(lr), betas=(0.9, 0.99), eps=1e-15, fused=True)
+        # fused: field-network wiring through field_glue.cu (same function, ~25 fewer launches per step)
+        # use_graph: replay the whole optimisation step as ONE CUDA graph once the sample-buffer size has settled
+        self.fused, self.use_graph = fused, use_graph
+        self._graph = None
+        self.optimizer = torch.optim.Adam(self.model.get_params(lr), betas=(0.9, 0.99), eps=1e-15, fused=True,
+                                          capturable=use_graph)
         self.scaler = torch.amp.GradScaler("cuda", enabled=fp16)
 
     def set_density_grid(self, density_grid, density_thresh=10.0):
@@ -40,27 +45,26 @@ class Trainer:
         raymarching.packbits(g, thresh, self.density_bitfield)
 
     # ------------------------------------------------------------------------------------------------ training
-    def render_train(self, rays_o, rays_d, bg_color=1.0, perturb=True, force_all_rays=False):
+    def render_train(self, rays_o, rays_d, bg_color=1.0, perturb=True, force_all_rays=False, counter=None, mean_count=None):
         """run_cuda, training branch (legacy/nerf/renderer.py:268-319)."""
         nears, fars = raymarching.near_far_from_aabb(rays_o, rays_d, self.aabb, self.min_near)
-        counter = self.step_counter[self.local_step % 16]
+        if counter is None:
+            counter = self.step_counter[self.local_step % 16]
+            self.local_step += 1
         counter.zero_()
-        self.local_step += 1
         xyzs, dirs, deltas, rays = raymarching.march_rays_train(
             rays_o, rays_d, self.bound, self.density_bitfield, self.cascade, self.grid_size, nears, fars, counter,
-            self.mean_count, perturb, 128, force_all_rays, self.dt_gamma, self.max_steps)
-        sigmas, rgbs = self.model(xyzs, dirs)
+            self.mean_count if mean_count is None else mean_count, perturb, 128, force_all_rays, self.dt_gamma, self.max_steps)
+        sigmas, rgbs = (self.model.forward_fused if self.fused else self.model)(xyzs, dirs)
         weights_sum, depth, image = raymarching.composite_rays_train(sigmas, rgbs, deltas, rays)
         image = image + (1 - weights_sum).unsqueeze(-1) * bg_color
         depth = torch.clamp(depth - nears, min=0) / (fars - nears)
         return image, depth, weights_sum
 
-    def train_step(self, rays_o, rays_d, gt_rgb, bg_color=1.0):
-        """One optimisation step on device-resident rays; returns the loss tensor (no host sync)."""
-        self.model.train()
+    def _step_body(self, rays_o, rays_d, gt_rgb, bg_color=1.0, counter=None, mean_count=None):
         self.optimizer.zero_grad(set_to_none=True)
         with torch.autocast("cuda", dtype=torch.float16, enabled=self.fp16):
-            image, _, _ = self.render_train(rays_o, rays_d, bg_color)
+            image, _, _ = self.render_train(rays_o, rays_d, bg_color, counter=counter, mean_count=mean_count)
             loss = torch.nn.functional.mse_loss(image, gt_rgb)
         self.scaler.scale(loss).backward()
         if self.grad_sync is not None:                 # data-parallel: all-reduce the (scaled) gradients over NCCL
@@ -68,6 +72,46 @@ class Trainer:
         self.scaler.step(self.optimizer)
         self.scaler.update()
         return loss
+
+    def train_step(self, rays_o, rays_d, gt_rgb, bg_color=1.0):
+        """One optimisation step on device-resident rays; returns the loss tensor (no host sync)."""
+        self.model.train()
+        if self.use_graph and self.mean_count > 0:
+            return self._graph_step(rays_o, rays_d, gt_rgb, bg_color)
+        return self._step_body(rays_o, rays_d, gt_rgb, bg_color)
+
+    # ---- CUDA-graph replay of the step -------------------------------------------------------------------------------
+    GRAPH_QUANTUM = 16384          # sample-buffer sizes are rounded up to this, so the captured shapes rarely change
+
+    def _graph_step(self, rays_o, rays_d, gt_rgb, bg_color):
+        """The step is ~90 small launches for 4096 rays; replaying it as one graph removes the launch gaps.  Shapes must
+        be static: the sample buffers are sized by the reference's own `mean_count` rule (raymarching.py:198-203), here
+        rounded up to GRAPH_QUANTUM so that the 16-step refresh of mean_count only re-captures when it moves by > 16k."""
+        q = self.GRAPH_QUANTUM
+        m_q = ((self.mean_count + q - 1) // q) * q
+        if self._graph is not None and m_q <= self._graph[0][0] <= m_q + q:       # hysteresis: keep a slightly larger buffer
+            m_q = self._graph[0][0]
+        key = (m_q, tuple(rays_o.shape), float(bg_color))
+        if self._graph is None or self._graph[0] != key:
+            self._graph = None                                                     # frees the old graph's pool first
+            g_in = [torch.empty_like(rays_o), torch.empty_like(rays_d), torch.empty_like(gt_rgb)]
+            for dst, src in zip(g_in, (rays_o, rays_d, gt_rgb)):
+                dst.copy_(src)
+            g_counter = torch.zeros(2, dtype=torch.int32, device=rays_o.device)
+            torch.cuda.synchronize()
+            graph = torch.cuda.CUDAGraph()
+            self.optimizer.zero_grad(set_to_none=True)
+            with torch.cuda.graph(graph):
+                g_loss = self._step_body(g_in[0], g_in[1], g_in[2], bg_color, counter=g_counter, mean_count=m_q)
+            self._graph = (key, graph, g_in, g_counter, g_loss)
+        _, graph, g_in, g_counter, g_loss = self._graph
+        for dst, src in zip(g_in, (rays_o, rays_d, gt_rgb)):
+            if dst.data_ptr() != src.data_ptr():
+                dst.copy_(src, non_blocking=True)
+        graph.replay()
+        self.step_counter[self.local_step % 16].copy_(g_counter)
+        self.local_step += 1
+        return g_loss
 
     def train_step_host(self, rays_o_h, rays_d_h, gt_rgb_h, stage):
         """End-to-end step from PINNED HOST buffers: H2D copies of the batch, the step, D2H read of the loss."""

@@ -42,8 +42,9 @@ int foc_packbits(const float *grid, uint32_t N, float density_thresh, uint8_t *b
 /* replaces march_rays_train, raymarching.h:13 (raymarching.cu:312-480).
  * Same outputs; slots are handed out by an exclusive prefix scan in ray order instead of arrival-order
  * atomics, so rays[n] = (n, offset, count) is deterministic.  counter[0] += total samples, counter[1] += N.
- * scratch: foc_march_rays_train_scratch_bytes(N) bytes of device memory (contents irrelevant). */
-size_t foc_march_rays_train_scratch_bytes(uint32_t N);
+ * scratch: foc_march_rays_train_scratch_bytes(N, max_steps) bytes of device memory (contents irrelevant): per-ray counts plus
+ * the recorded sample parameters of the single serial pass, which a second, data-parallel kernel expands. */
+size_t foc_march_rays_train_scratch_bytes(uint32_t N, uint32_t max_steps);
 int foc_march_rays_train(const float *rays_o, const float *rays_d, const uint8_t *grid, float bound, float dt_gamma,
                          uint32_t max_steps, uint32_t N, uint32_t C, uint32_t H, uint32_t M, const float *nears,
                          const float *fars, float *xyzs, float *dirs, float *deltas, int32_t *rays, int32_t *counter,
@@ -147,6 +148,19 @@ int foc_free_splitk(void);
 int foc_freq_encode_forward(const float *inputs, uint32_t B, uint32_t D, uint32_t deg, uint32_t C, float *outputs, void *stream);
 int foc_freq_encode_backward(const float *grad, const float *outputs, uint32_t B, uint32_t D, uint32_t deg, uint32_t C,
                              float *grad_inputs, void *stream);
+
+/* ---------------------------------------------------------------- field-network wiring (nerf/network_ff.py:51-74), fused
+ * Elementwise glue between the encoders and the two MLPs, one pass per direction instead of ~25 PyTorch kernels per step.
+ * forward : h [B,16] f16 (sigma-net output), dirs [B,3] f32 -> sigma [B] f32 = exp(float(h[:,0])) (activation.py:5-18),
+ *           cin [B,32] f16 = [SH4(dirs) | h[:,1:16] | 0]  (network_ff.py:63-68).
+ * backward: grad_h[:,0] = grad_sigma * exp(clamp(h0,-15,15)); grad_h[:,1:16] = grad_cin[:,16:31]; grad_sigma may be NULL. */
+int foc_field_mid_forward(const float *dirs, const uint16_t *h, uint32_t B, float *sigma, uint16_t *cin, void *stream);
+int foc_field_mid_backward(const float *grad_sigma, const uint16_t *grad_cin, const uint16_t *h, uint32_t B, uint16_t *grad_h,
+                           void *stream);
+/* rgb [B,3] f32 = sigmoid(hc[:, :3]) rounded through f16 as torch.sigmoid on the half tensor does (network_ff.py:72);
+ * backward: grad_hc [B,16] f16 = grad * y * (1 - y) in columns 0..2, zero elsewhere. */
+int foc_rgb_sigmoid_forward(const uint16_t *hc, uint32_t B, float *rgb, void *stream);
+int foc_rgb_sigmoid_backward(const float *grad_rgb, const float *rgb, uint32_t B, uint16_t *grad_hc, void *stream);
 
 /* degree <= 4 real spherical-harmonics direction encoding (`shencoder`, imported by nerf/network_ff.py:5 but ABSENT
  * from the reference tree: closed form, parity unpinned).  dirs [B,3] -> outputs [B, degree^2] f32. */

@@ -22,6 +22,7 @@ def test_header_prototypes_parse_to_ctypes(built_lib):
     ret, args = protos["foc_march_rays_train"]
     assert ret is ctypes.c_int and len(args) == 20 and args[3] is ctypes.c_float and args[5] is ctypes.c_uint32
     assert protos["foc_ffmlp_backward_scratch_bytes"][0] is ctypes.c_size_t
+    assert len(protos["foc_march_rays_train_scratch_bytes"][1]) == 2
 
 
 def test_sass_contains_blackwell_tensor_path(built_lib):

@@ -39,3 +39,58 @@ def test_render_loop_compaction_equivalence():
     b = tr.render(o, d, device_compaction=False)
     for x, y in zip(a, b):
         assert torch.equal(torch.nan_to_num(x), torch.nan_to_num(y))
+
+
+def test_forward_fused_matches_forward():
+    """field_glue.cu path == the module-by-module wiring of network_ff.py:51-74, values and parameter gradients."""
+    from focnerf_b200.network import NeRFNetwork
+    torch.manual_seed(3)
+    net = NeRFNetwork(bound=1.0).cuda()
+    with torch.no_grad():
+        net.encoder.embeddings.uniform_(-0.5, 0.5)         # the 1e-4 init leaves the MLP outputs degenerate
+    B = 128 * 37
+    g = torch.Generator(device="cuda").manual_seed(5)
+    x = torch.rand(B, 3, device="cuda", generator=g) * 2 - 1
+    d = torch.nn.functional.normalize(torch.randn(B, 3, device="cuda", generator=g), dim=-1)
+    ws, wc = torch.randn(B, device="cuda", generator=g), torch.randn(B, 3, device="cuda", generator=g)
+    grads, outs = [], []
+    for fn in (net.forward, net.forward_fused):
+        net.zero_grad(set_to_none=True)
+        with torch.autocast("cuda", dtype=torch.float16):
+            sigma, rgb = fn(x, d)
+        ((sigma.float() * ws).sum() * 1e-2 + (rgb.float() * wc).sum()).backward()
+        outs.append((sigma.detach().float(), rgb.detach().float()))
+        grads.append([p.grad.detach().float().clone() for p in net.parameters()])
+    assert outs[1][0].dtype == torch.float32 and outs[1][1].shape == (B, 3)
+    assert torch.allclose(outs[0][0], outs[1][0], rtol=1e-5, atol=1e-7)
+    assert torch.allclose(outs[0][1], outs[1][1], rtol=0, atol=1e-3)
+    for a, b in zip(*grads):
+        rel = float((a - b).norm() / (a.norm() + 1e-20))
+        assert rel < 2e-2, rel                              # fp16 gradient rounding (different add order in the unfused cat/slice)
+
+
+def test_graph_step_trains_and_tracks_counter():
+    """use_graph=True: the step replayed as one CUDA graph still trains, keeps the step_counter ring current, and
+    re-captures when the sample-buffer quantum changes."""
+    from focnerf_b200.trainer import Trainer
+    scene, cascade, grid, bits, thresh = cases.scene_bitfield(1.0)
+    tr = Trainer(bound=1.0, density_grid=torch.from_numpy(grid), use_graph=True)
+    losses, captured = [], set()
+    for it in range(80):
+        o, d = cases.camera_rays(4096, 100 + it)
+        o, d = torch.from_numpy(o).cuda(), torch.from_numpy(d).cuda()
+        gt = scene.render_gt(o, d)
+        losses.append(float(tr.train_step(o, d, gt)))
+        if tr._graph is not None:
+            captured.add(tr._graph[0][0])
+        if (it + 1) % 16 == 0:
+            tr.update_mean_count()
+    assert tr._graph is not None and len(captured) >= 1
+    assert all(np.isfinite(losses)), losses
+    assert np.mean(losses[-10:]) < 0.5 * np.mean(losses[:5]), (losses[:5], losses[-10:])
+    cnt = tr.step_counter[:, 0].cpu().numpy()
+    assert (cnt > 0).all()
+    # a forced quantum change re-captures
+    tr.mean_count = max(captured) + 3 * Trainer.GRAPH_QUANTUM
+    tr.train_step(o, d, gt)
+    assert tr._graph[0][0] > max(captured)
