@@ -6,9 +6,10 @@
 // the FMA contractions nvcc makes for the reference source (verified against the SASS of oracle/_ref).
 //
 // Training march = three launches, no spin-waits, no atomics:
-//   count  : 1 thread / ray walks the bitfield and counts occupied steps          -> scratch counts[N]
+//   record : walk each ray once, recording the parameter t of every occupied step -> scratch counts[N], tbuf[N,max_steps]
+//            (constant step: warp per ray, probes in parallel -- k_march_record_const; dt_gamma > 0: serial walk)
 //   scan   : 1 CTA, warp-shuffle exclusive prefix scan over counts                 -> rays[N,3], counter[2]
-//   write  : 1 thread / ray re-walks and writes its slice (slots are ray-ordered and deterministic; the
+//   expand : warp per ray turns the recorded t's into samples, coalesced (slots are ray-ordered and deterministic; the
 //            reference hands them out in atomic arrival order, raymarching.cu:405-406)
 #include "common.cuh"
 
@@ -54,10 +55,9 @@ __device__ __forceinline__ int mip_level(float mx, int C) {
     return min(C - 1, max(0, e));
 }
 
-// One probe at parameter t: returns true when the cell is occupied (x,y,z,dt filled);
-// otherwise advances t past the empty cell (raymarching.cu:360-399).
-__device__ __forceinline__ bool probe(const MarchParams& p, const Ray& r, float& t, float& x, float& y, float& z, float& dt) {
-    const float tc = t;
+// The cell test at parameter t (raymarching.cu:360-392): fills x,y,z,dt; returns true when the cell is occupied, else
+// sets tt = the parameter at which the ray leaves the (empty) cell.
+__device__ __forceinline__ bool probe_cell(const MarchParams& p, const Ray& r, float tc, float& x, float& y, float& z, float& dt, float& tt) {
     x = clampf(ffma(tc, r.dx, r.ox), -p.bound, p.bound);
     y = clampf(ffma(tc, r.dy, r.oy), -p.bound, p.bound);
     z = clampf(ffma(tc, r.dz, r.oz), -p.bound, p.bound);
@@ -83,8 +83,16 @@ __device__ __forceinline__ bool probe(const MarchParams& p, const Ray& r, float&
     const float tx = fmul(ffma(mip_bound, ffma(fmul(fadd(fadd((float)nx, 0.5f), r.sx), p.rH), 2.0f, -1.0f), -x), r.rdx);
     const float ty = fmul(ffma(mip_bound, ffma(fmul(fadd(fadd((float)ny, 0.5f), r.sy), p.rH), 2.0f, -1.0f), -y), r.rdy);
     const float tz = fmul(ffma(mip_bound, ffma(fmul(fadd(fadd((float)nz, 0.5f), r.sz), p.rH), 2.0f, -1.0f), -z), r.rdz);
-    const float tt = fadd(tc, fmaxf(0.0f, fminf(tx, fminf(ty, tz))));
-    float tn = tc;
+    tt = fadd(tc, fmaxf(0.0f, fminf(tx, fminf(ty, tz))));
+    return false;
+}
+
+// One probe at parameter t: returns true when the cell is occupied (x,y,z,dt filled);
+// otherwise advances t past the empty cell (raymarching.cu:393-399).
+__device__ __forceinline__ bool probe(const MarchParams& p, const Ray& r, float& t, float& x, float& y, float& z, float& dt) {
+    float tt;
+    if (probe_cell(p, r, t, x, y, z, dt, tt)) return true;
+    float tn = t;
     do { tn = fadd(tn, step_dt(p, tn)); } while (tn < tt);
     t = tn;
     return false;
@@ -216,6 +224,107 @@ __global__ void __launch_bounds__(128) k_march_record(const float* __restrict__ 
         if (probe(p, r, t, x, y, z, dt)) { tb[num++] = tc; t = fadd(tc, dt); }
     }
     counts[n] = num;
+}
+
+// pass 1, constant step (dt_gamma == 0, the setting of bound-1 scenes): ONE WARP PER RAY, data-parallel.
+//
+// With a constant step d the serial walk only ever visits parameters of ONE fixed sequence t_0, t_{k+1} = fl(t_k + d):
+// an occupied cell advances by one element, an empty cell skips to the first element >= tt (raymarching.cu:393-399 adds
+// d repeatedly).  So the walk splits into
+//   A  generate 1024 elements of the sequence: every lane runs a 32-add chain from a speculated seed
+//      (bits(t_s) + 32*lane*c, c = the per-step bit increment inside one binade); a chain is accepted only when its
+//      last value equals the next lane's seed BITWISE, otherwise the first unverified lane restarts from the exact
+//      value -- the result is the sequential sum by induction, no assumption about rounding survives unverified;
+//   B  probe all elements < far in parallel (the global bitfield loads overlap instead of serialising), and resolve
+//      each element's successor: k+1 when occupied, else the first later element >= tt;
+//   C  follow the successor links from element 0 (one shared-memory load per visited cell), recording occupied ones.
+// Same probes, same floats, same order of recorded samples as the serial walk.
+constexpr int kSeqChunk = 1024;
+struct MarchSeq {
+    float t[kSeqChunk + 32];             // element k at k + (k >> 5): both the per-lane chains and strided reads are conflict-free
+    uint16_t next[kSeqChunk];            // bit 15: occupied; low bits: successor index (kSeqChunk = beyond this chunk)
+};
+__device__ __forceinline__ int seq_pos(int k) { return k + (k >> 5); }
+
+__global__ void __launch_bounds__(128) k_march_record_const(const float* __restrict__ rays_o, const float* __restrict__ rays_d,
+                                                            const float* __restrict__ nears, const float* __restrict__ fars,
+                                                            const float* __restrict__ noises, uint32_t N, uint32_t max_steps,
+                                                            MarchParams p, uint32_t* __restrict__ counts, float* __restrict__ tbuf) {
+    __shared__ MarchSeq seq[4];
+    const uint32_t lane = threadIdx.x & 31u, n = blockIdx.x * 4u + (threadIdx.x >> 5);
+    if (n >= N) return;                                              // warp-uniform
+    MarchSeq& w = seq[threadIdx.x >> 5];
+    const uint32_t full = 0xffffffffu;
+    const Ray r = load_ray(rays_o, rays_d, n, __ldg(fars + n));
+    const float near = __ldg(nears + n);
+    const float d = step_dt(p, 1.0f);                                // clamp(t * 0) for every finite t
+    float t_start = ffma(d, __ldg(noises + n), near);
+    float* tb = tbuf + (size_t)n * max_steps;
+    uint32_t num = 0;
+    float pending = -1.0f;                                           // tt of a skip that ran past the previous chunk (t >= 0)
+    bool have_pending = false;
+    for (int chunk = 0; chunk < 4096 && t_start < r.far && num < max_steps; ++chunk) {
+        // ---- A: t[0..1023] (+ t_next), exact
+        uint32_t first = 0, below = 0;
+        float exact = t_start, seed = t_start, v = t_start;
+        while (true) {
+            const uint32_t c = __float_as_uint(fadd(exact, d)) - __float_as_uint(exact);
+            if (lane >= first) {
+                seed = __uint_as_float(__float_as_uint(exact) + (lane - first) * 32u * c);
+                v = seed; below = 0;
+                float* row = w.t + lane * 33u;
+                #pragma unroll 8
+                for (int i = 0; i < 32; ++i) { row[i] = v; below += (v < r.far) ? 1u : 0u; v = fadd(v, d); }
+            }
+            const float nxt = __shfl_down_sync(full, seed, 1);
+            const bool bad = lane >= first && lane < 31u && __float_as_uint(v) != __float_as_uint(nxt);
+            const uint32_t m = __ballot_sync(full, bad);
+            if (m == 0) break;
+            const int l = __ffs((int)m) - 1;
+            first = (uint32_t)l + 1u;
+            exact = __shfl_sync(full, v, l);
+        }
+        const float t_next = __shfl_sync(full, v, 31);
+        const int Kc = (int)__reduce_add_sync(full, below);         // elements of this chunk with t < far (a prefix: t is monotone)
+        __syncwarp();
+        // ---- B: probe + successor
+        for (int k = (int)lane; k < Kc; k += 32) {
+            float x, y, z, dt, tt;
+            uint32_t j;
+            if (probe_cell(p, r, w.t[seq_pos(k)], x, y, z, dt, tt)) j = 0x8000u | (uint32_t)(k + 1);
+            else {
+                int q = k + 1;
+                while (q < kSeqChunk && w.t[seq_pos(q)] < tt) ++q;
+                j = (uint32_t)q;
+            }
+            w.next[k] = (uint16_t)j;
+        }
+        __syncwarp();
+        // ---- C: follow the links (uniform over the warp; lane 0 stores)
+        int k = 0;
+        if (have_pending) {
+            while (k < kSeqChunk && w.t[seq_pos(k)] < pending) ++k;
+            have_pending = (k == kSeqChunk);
+        }
+        while (k < Kc && num < max_steps) {
+            const uint32_t j = w.next[k];
+            if (j & 0x8000u) {
+                if (lane == 0) tb[num] = w.t[seq_pos(k)];
+                ++num; ++k;
+            } else {
+                if (j == (uint32_t)kSeqChunk) {                      // the skip leaves this chunk: carry its target
+                    float x, y, z, dt;
+                    probe_cell(p, r, w.t[seq_pos(k)], x, y, z, dt, pending);
+                    have_pending = true;
+                }
+                k = (int)j;
+            }
+        }
+        if (Kc < kSeqChunk) break;                                   // the sequence passed `far` inside this chunk
+        t_start = t_next;
+        __syncwarp();
+    }
+    if (lane == 0) counts[n] = num;
 }
 
 // exclusive prefix scan of counts in ray order by ONE CTA of 1024 threads (N is a few thousand in training; at
@@ -361,8 +470,10 @@ FOC_API int foc_march_rays_train(const float* rays_o, const float* rays_d, const
     const MarchParams p = make_march_params(grid, bound, dt_gamma, max_steps, C, H);
     uint32_t* counts = static_cast<uint32_t*>(scratch);
     float* tbuf = reinterpret_cast<float*>(static_cast<uint8_t*>(scratch) + march_counts_bytes(N));
-    // small batches: 4 rays per warp (see ray_of_thread); large ones: every lane carries a ray
-    if (N <= (uint32_t)kNumSMs * 32u * 8u)
+    // constant step: warp-per-ray parallel walk; else serial walk, 4 rays per warp for small batches (see ray_of_thread)
+    if (dt_gamma == 0.0f)
+        k_march_record_const<<<ceil_div(N, 4), 128, 0, S(stream)>>>(rays_o, rays_d, nears, fars, noises, N, max_steps, p, counts, tbuf);
+    else if (N <= (uint32_t)kNumSMs * 32u * 8u)
         k_march_record<4><<<ceil_div(ceil_div(N, 4) * 32, 128), 128, 0, S(stream)>>>(rays_o, rays_d, nears, fars, noises, N, max_steps, p, counts, tbuf);
     else
         k_march_record<32><<<ceil_div(N, 128), 128, 0, S(stream)>>>(rays_o, rays_d, nears, fars, noises, N, max_steps, p, counts, tbuf);

@@ -35,7 +35,8 @@ def _assert_march_equal(a, b):
         assert np.array_equal(a[k].view(np.uint32), b[k].view(np.uint32)), f"{k} not bit-exact"
 
 
-@pytest.mark.parametrize("bound,dt_gamma", [(1.0, 0.0), (2.0, 1.0 / 128), (1.0, 1.0 / 128)])
+# dt_gamma == 0 takes the warp-per-ray constant-step walk; bound 2 / 4 make it span several 1024-element chunks
+@pytest.mark.parametrize("bound,dt_gamma", [(1.0, 0.0), (2.0, 1.0 / 128), (1.0, 1.0 / 128), (2.0, 0.0), (4.0, 0.0)])
 def test_march_train_vs_oracle(bound, dt_gamma):
     c = cases.march_case(512, 1, bound, dt_gamma)
     got = runners.march_train(ours(), c)
@@ -44,7 +45,7 @@ def test_march_train_vs_oracle(bound, dt_gamma):
     assert np.array_equal(got["offsets"], np.concatenate([[0], np.cumsum(got["counts"])[:-1]]))
 
 
-@pytest.mark.parametrize("bound,dt_gamma", [(1.0, 0.0), (2.0, 1.0 / 128)])
+@pytest.mark.parametrize("bound,dt_gamma", [(1.0, 0.0), (2.0, 1.0 / 128), (2.0, 0.0), (4.0, 0.0)])
 def test_march_train_vs_reference(bound, dt_gamma):
     ref = ref_ext.load("raymarching")
     if ref is None:
