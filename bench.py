@@ -132,12 +132,13 @@ def run_ours(args):
     dev = torch.device("cuda", local)
     scene, cascade, grid, bits, thresh = cases.scene_bitfield(1.0)
     use_graph = (not args.no_graph) and (world == 1 or os.environ.get("FOC_GRAPH_DP", "1") == "1")
-    tr = Trainer(bound=1.0, density_grid=torch.from_numpy(grid), device=dev, seed=0, fused=not args.no_fused, use_graph=use_graph)
+    tr = Trainer(bound=1.0, density_grid=torch.from_numpy(grid), device=dev, seed=0, fused=not args.no_fused, use_graph=use_graph,
+                 optimizer="torch" if args.torch_optim else "fused")
     params = [p for p in tr.model.parameters()]
     if world > 1:                                   # data-parallel: identical replicas, gradients all-reduced every step
         for p in params:
             dist.broadcast(p.data, 0)
-        tr.grad_sync = lambda: [dist.all_reduce(p.grad, op=dist.ReduceOp.AVG) for p in params if p.grad is not None]
+        tr.grad_sync = lambda: [dist.all_reduce(g, op=dist.ReduceOp.AVG) for g in tr.grad_tensors()]
     pool_dev, pool_host = make_pool(scene, POOL, RAYS_PER_GPU, 1000 + 7919 * rank, dev)
     stage = [torch.empty_like(t) for t in pool_dev[0]]
 
@@ -234,7 +235,7 @@ def run_ours(args):
         "config": {"workload": "configs[1]: single-object hash-grid NeRF train step (16 levels, 2^19 table, F=2, 64-wide FFMLPs, "
                                "4096 rays/batch per GPU, cuda_ray, fp16, Adam)", "rays_per_gpu": RAYS_PER_GPU,
                    "samples_per_step": samples, "parallelism": f"dp{world}" if world > 1 else "single",
-                   "cuda_graph": use_graph, "fused_glue": not args.no_fused,
+                   "cuda_graph": use_graph, "fused_glue": not args.no_fused, "optimizer": "torch" if args.torch_optim else "fused ScaledAdam",
                    "l2": "fresh ray batch every step; step working set (fp32 table + Adam moments + fp16 copy + grads ~ 260 MB) exceeds the 126 MB L2"},
         "clocks": clk,
         "e2e": {"value": total_rays / (ms_e2e * 1e-3), "unit": "rays/s", "ms_per_step": ms_e2e / args.steps,
@@ -277,6 +278,7 @@ if __name__ == "__main__":
     ap.add_argument("--warmup", type=int, default=8)
     ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
     ap.add_argument("--no-graph", action="store_true", help="launch the step eagerly instead of replaying a CUDA graph")
+    ap.add_argument("--torch-optim", action="store_true", help="torch.optim.Adam + GradScaler instead of the fused ScaledAdam")
     ap.add_argument("--no-fused", action="store_true", help="field network through the unfused operator modules")
     a = ap.parse_args()
     (run_reference if a.impl == "reference" else run_ours)(a)

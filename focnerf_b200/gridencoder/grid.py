@@ -86,7 +86,7 @@ class _grid_encode(Function):
     @staticmethod
     @custom_fwd(device_type="cuda")
     def forward(ctx, inputs, embeddings, offsets, per_level_scale, base_resolution, calc_grad_inputs=False, gridtype=0,
-                align_corners=False, interpolation=0):
+                align_corners=False, interpolation=0, shadow16=None, grad16=None):
         require_cuda(inputs, embeddings, offsets)
         inputs = inputs.contiguous()
         B, D = inputs.shape
@@ -94,8 +94,12 @@ class _grid_encode(Function):
         C = embeddings.shape[1]
         S = np.log2(per_level_scale)        # float64 here, narrowed to float at the ABI like the reference's pybind call
         H = base_resolution
+        ctx.grad16 = None
         if torch.is_autocast_enabled() and C % 2 == 0:
-            embeddings = embeddings.to(torch.half)
+            # fp16 side buffers (GridEncoder.enable_fp16_side_buffers): read the shadow the optimiser keeps current instead
+            # of casting the fp32 table every step, and scatter the gradient into the persistent fp16 buffer.
+            embeddings = shadow16 if shadow16 is not None else embeddings.to(torch.half)
+            ctx.grad16 = grad16
         outputs = torch.empty(B, L * C, device=inputs.device, dtype=embeddings.dtype)
         dy_dx = torch.empty(B, L * D * C, device=inputs.device, dtype=embeddings.dtype) if calc_grad_inputs else None
         _backend.grid_encode_forward(inputs, embeddings, offsets, outputs, B, D, C, L, S, H, dy_dx, gridtype, align_corners,
@@ -113,13 +117,14 @@ class _grid_encode(Function):
         grad = grad.contiguous()                                   # [B, L*C] read in place (layout FOC_BLC)
         if grad.dtype != embeddings.dtype:
             grad = grad.to(embeddings.dtype)
-        grad_embeddings = torch.zeros_like(embeddings)
+        side = ctx.grad16 is not None
+        grad_embeddings = ctx.grad16 if side else torch.zeros_like(embeddings)      # the side buffer accumulates, like .grad
         grad_inputs = torch.zeros_like(inputs, dtype=embeddings.dtype) if dy_dx is not None else None
         _backend.grid_encode_backward(grad, inputs, embeddings, offsets, grad_embeddings, B, D, C, L, S, H, dy_dx, grad_inputs,
                                       gridtype, ctx.align_corners, interpolation, FOC_BLC)
         if dy_dx is not None:
             grad_inputs = grad_inputs.to(inputs.dtype)
-        return grad_inputs, grad_embeddings, None, None, None, None, None, None, None
+        return grad_inputs, (None if side else grad_embeddings), None, None, None, None, None, None, None, None, None
 
 
 grid_encode = _grid_encode.apply
@@ -157,11 +162,24 @@ class GridEncoder(nn.Module):
         self.register_buffer('offsets', torch.from_numpy(np.array(offsets, dtype=np.int32)))
         self.n_params = offsets[-1] * level_dim
         self.embeddings = nn.Parameter(torch.empty(offset, level_dim))
+        self._shadow16, self._grad16 = None, None                  # see enable_fp16_side_buffers
         self.reset_parameters()
 
     def reset_parameters(self):
         std = 1e-4
         self.embeddings.data.uniform_(-std, std)
+
+    def enable_fp16_side_buffers(self):
+        """Not in the reference.  Allocates (grad16, shadow16), both [offset, C] half: under fp16 autocast the forward then
+        gathers from `shadow16` (no per-step `.to(half)` of the 49 MB table) and the backward scatters into `grad16`
+        (no per-step zeros_like + half->float copy); `embeddings.grad` stays None.  The owner of the buffers -- an
+        optimiser such as focnerf_b200.optim.ScaledAdam -- must refresh shadow16 after every parameter update and zero
+        grad16 after consuming it."""
+        if self.level_dim % 2 != 0:
+            raise RuntimeError("fp16 side buffers need an even level_dim (the fp16 path of the encoder, grid.py:43)")
+        self._shadow16 = self.embeddings.detach().to(torch.half).contiguous()
+        self._grad16 = torch.zeros_like(self._shadow16)
+        return self._grad16, self._shadow16
 
     def __repr__(self):
         return (f"GridEncoder: input_dim={self.input_dim} num_levels={self.num_levels} level_dim={self.level_dim} "
@@ -174,7 +192,7 @@ class GridEncoder(nn.Module):
         prefix_shape = list(inputs.shape[:-1])
         inputs = inputs.view(-1, self.input_dim)
         outputs = grid_encode(inputs, self.embeddings, self.offsets, self.per_level_scale, self.base_resolution,
-                              inputs.requires_grad, self.gridtype_id, self.align_corners, self.interp_id)
+                              inputs.requires_grad, self.gridtype_id, self.align_corners, self.interp_id, self._shadow16, self._grad16)
         return outputs.view(prefix_shape + [self.output_dim])
 
     @torch.amp.autocast("cuda", enabled=False)                     # always fp32 (grid.py:164)

@@ -13,7 +13,7 @@ from .network import NeRFNetwork
 
 class Trainer:
     def __init__(self, bound=1.0, density_grid=None, density_thresh=10.0, min_near=0.2, dt_gamma=0.0, max_steps=1024,
-                 lr=1e-2, fp16=True, device="cuda", grid_size=128, seed=0, fused=True, use_graph=False):
+                 lr=1e-2, fp16=True, device="cuda", grid_size=128, seed=0, fused=True, use_graph=False, optimizer="fused"):
         if not torch.cuda.is_available():
             raise RuntimeError("focnerf_b200.Trainer needs a CUDA device (there is no CPU path)")
         import math
@@ -34,9 +34,18 @@ class Trainer:
         # use_graph: replay the whole optimisation step as ONE CUDA graph once the sample-buffer size has settled
         self.fused, self.use_graph = fused, use_graph
         self._graph = None
-        self.optimizer = torch.optim.Adam(self.model.get_params(lr), betas=(0.9, 0.99), eps=1e-15, fused=True,
-                                          capturable=use_graph)
-        self.scaler = torch.amp.GradScaler("cuda", enabled=fp16)
+        # optimizer="fused": ScaledAdam (csrc/optim.cu) with the encoder's fp16 side buffers; "torch": the reference's
+        # torch.optim.Adam + torch.amp.GradScaler pair, kept for A/B checks
+        if optimizer == "fused":
+            from .optim import ScaledAdam
+            self.optimizer = ScaledAdam(self.model.parameters(), lr=lr, betas=(0.9, 0.99), eps=1e-15, loss_scaling=fp16)
+            if fp16:
+                g16, s16 = self.model.encoder.enable_fp16_side_buffers()
+                self.optimizer.attach(self.model.encoder.embeddings, grad16=g16, shadow16=s16)
+            self.scaler = None
+        else:
+            self.optimizer = torch.optim.Adam(self.model.get_params(lr), betas=(0.9, 0.99), eps=1e-15, fused=True, capturable=use_graph)
+            self.scaler = torch.amp.GradScaler("cuda", enabled=fp16)
 
     def set_density_grid(self, density_grid, density_thresh=10.0):
         """density_grid [cascade, H^3] (Morton order) -> bitfield, as update_extra_state does (renderer.py:529-531)."""
@@ -66,12 +75,24 @@ class Trainer:
         with torch.autocast("cuda", dtype=torch.float16, enabled=self.fp16):
             image, _, _ = self.render_train(rays_o, rays_d, bg_color, counter=counter, mean_count=mean_count)
             loss = torch.nn.functional.mse_loss(image, gt_rgb)
+        if self.scaler is None:
+            self.optimizer.scale_loss(loss).backward()
+            if self.grad_sync is not None:             # data-parallel: all-reduce the (scaled) gradients over NCCL
+                self.grad_sync()
+            self.optimizer.step()
+            return loss
         self.scaler.scale(loss).backward()
-        if self.grad_sync is not None:                 # data-parallel: all-reduce the (scaled) gradients over NCCL
+        if self.grad_sync is not None:
             self.grad_sync()
         self.scaler.step(self.optimizer)
         self.scaler.update()
         return loss
+
+    def grad_tensors(self):
+        """Gradient tensors a data-parallel all-reduce must average between backward and the optimiser step."""
+        if self.scaler is None:
+            return self.optimizer.grad_tensors()
+        return [p.grad for p in self.model.parameters() if p.grad is not None]
 
     def train_step(self, rays_o, rays_d, gt_rgb, bg_color=1.0):
         """One optimisation step on device-resident rays; returns the loss tensor (no host sync)."""

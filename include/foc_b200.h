@@ -166,6 +166,33 @@ int foc_rgb_sigmoid_backward(const float *grad_rgb, const float *rgb, uint32_t B
  * from the reference tree: closed form, parity unpinned).  dirs [B,3] -> outputs [B, degree^2] f32. */
 int foc_sh_encode_forward(const float *dirs, uint32_t B, uint32_t degree, float *outputs, void *stream);
 
+/* ---------------------------------------------------------------- optimiser step of the path
+ * Dense Adam + dynamic loss scaling, replacing torch.optim.Adam(betas, eps) + torch.amp.GradScaler as the reference's
+ * train step uses them (main_nerf.py:211,472; nerf/utils.py:866-868), with torch's arithmetic (torch/optim/adam.py,
+ * amsgrad = False, weight_decay = 0) and GradScaler.update()'s scale rule.  One sweep over the parameters also writes
+ * the fp16 copy the next forward reads (`shadow16`) and zeroes the gradient in place (`zero_grad`).
+ * All scalars that change between steps (lr, scale, found_inf, step, growth_tracker) are DEVICE scalars: no host sync,
+ * CUDA-graph capturable.  Up to 8 tensors per call; pointers 16-byte aligned. */
+typedef struct FocAdamTensor {
+    float *param;        /* [n] fp32 master parameters */
+    float *exp_avg;      /* [n] first moment */
+    float *exp_avg_sq;   /* [n] second moment */
+    void *grad;          /* [n] gradient of (loss * scale), f32 or f16 per grad_dtype; NULL = tensor is skipped */
+    uint16_t *shadow16;  /* [n] optional fp16 copy of the updated parameters, NULL = none */
+    uint64_t n;
+    int32_t grad_dtype;  /* 0 = f32, 1 = f16 */
+    int32_t zero_grad;   /* != 0: the gradient is zeroed after use (also on a skipped step) */
+} FocAdamTensor;
+/* *found_inf = 1.0f when any gradient element is inf / nan (GradScaler._unscale_grads_' check); never cleared here */
+int foc_adam_nonfinite(const FocAdamTensor *tensors, int count, float *found_inf, void *stream);
+/* t = *step + 1; skipped entirely when *found_inf != 0.  scale / found_inf may be NULL (no loss scaling). */
+int foc_adam_step(const FocAdamTensor *tensors, int count, const float *lr, float beta1, float beta2, float eps,
+                  const float *scale, const float *found_inf, const int32_t *step, void *stream);
+/* GradScaler.update(): found_inf -> scale *= backoff, tracker = 0; else tracker += 1 and every growth_interval clean
+ * steps scale *= growth.  Also *step += 1 on a clean step, and *found_inf = 0.  scale may be NULL (step counter only). */
+int foc_scaler_update(float *scale, int32_t *growth_tracker, float *found_inf, int32_t *step, float growth_factor,
+                      float backoff_factor, int32_t growth_interval, void *stream);
+
 #ifdef __cplusplus
 }
 #endif

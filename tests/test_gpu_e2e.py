@@ -9,16 +9,17 @@ import cases
 pytestmark = pytest.mark.gpu
 
 
-def _trainer(bound=1.0):
+def _trainer(bound=1.0, **kw):
     from focnerf_b200.trainer import Trainer
     scene, cascade, grid, bits, thresh = cases.scene_bitfield(bound)
-    tr = Trainer(bound=bound, density_grid=torch.from_numpy(grid))
+    tr = Trainer(bound=bound, density_grid=torch.from_numpy(grid), **kw)
     assert np.array_equal(tr.density_bitfield.cpu().numpy(), bits)
     return scene, tr
 
 
-def test_train_steps_reduce_loss():
-    scene, tr = _trainer()
+@pytest.mark.parametrize("optimizer", ["fused", "torch"])
+def test_train_steps_reduce_loss(optimizer):
+    scene, tr = _trainer(optimizer=optimizer)
     losses = []
     for it in range(60):
         o, d = cases.camera_rays(4096, 100 + it)
