@@ -231,27 +231,33 @@ __global__ void __launch_bounds__(128) k_march_record(const float* __restrict__ 
 // With a constant step d the serial walk only ever visits parameters of ONE fixed sequence t_0, t_{k+1} = fl(t_k + d):
 // an occupied cell advances by one element, an empty cell skips to the first element >= tt (raymarching.cu:393-399 adds
 // d repeatedly).  So the walk splits into
-//   A  generate 1024 elements of the sequence: every lane runs a 32-add chain from a speculated seed
-//      (bits(t_s) + 32*lane*c, c = the per-step bit increment inside one binade); a chain is accepted only when its
+//   A  generate a chunk of 512 elements of the sequence: every lane runs a 16-add chain from a speculated seed
+//      (bits(t_s) + 16*lane*c, c = the per-step bit increment inside one binade); a chain is accepted only when its
 //      last value equals the next lane's seed BITWISE, otherwise the first unverified lane restarts from the exact
 //      value -- the result is the sequential sum by induction, no assumption about rounding survives unverified;
 //   B  probe all elements < far in parallel (the global bitfield loads overlap instead of serialising), and resolve
 //      each element's successor: k+1 when occupied, else the first later element >= tt;
 //   C  follow the successor links from element 0 (one shared-memory load per visited cell), recording occupied ones.
 // Same probes, same floats, same order of recorded samples as the serial walk.
-constexpr int kSeqChunk = 1024;
+constexpr int kSeqChunk = 512, kSeqPerLane = kSeqChunk / 32, kSeqShift = 4;      // 2^kSeqShift == kSeqPerLane
+constexpr int kSeqWarps = 1;                 // warps (= rays) per CTA: 5.2 KB of shared memory per ray, so a 4096-ray batch
+                                             // (28 rays per SM) is resident in ONE wave
 struct MarchSeq {
-    float t[kSeqChunk + 32];             // element k at k + (k >> 5): both the per-lane chains and strided reads are conflict-free
+    float t[kSeqChunk + 32];             // element k at k + (k >> kSeqShift): per-lane chains and strided reads are conflict-free
     uint16_t next[kSeqChunk];            // bit 15: occupied; low bits: successor index (kSeqChunk = beyond this chunk)
+    union {
+        float tt[kSeqChunk];             // B: exit parameter of an empty cell, -1 for an occupied one
+        uint16_t samp[kSeqChunk];        // C: indices of the occupied cells the walk visited, in order
+    };
 };
-__device__ __forceinline__ int seq_pos(int k) { return k + (k >> 5); }
+__device__ __forceinline__ int seq_pos(int k) { return k + (k >> kSeqShift); }
 
-__global__ void __launch_bounds__(128) k_march_record_const(const float* __restrict__ rays_o, const float* __restrict__ rays_d,
+__global__ void __launch_bounds__(32 * kSeqWarps) k_march_record_const(const float* __restrict__ rays_o, const float* __restrict__ rays_d,
                                                             const float* __restrict__ nears, const float* __restrict__ fars,
                                                             const float* __restrict__ noises, uint32_t N, uint32_t max_steps,
                                                             MarchParams p, uint32_t* __restrict__ counts, float* __restrict__ tbuf) {
-    __shared__ MarchSeq seq[4];
-    const uint32_t lane = threadIdx.x & 31u, n = blockIdx.x * 4u + (threadIdx.x >> 5);
+    __shared__ MarchSeq seq[kSeqWarps];
+    const uint32_t lane = threadIdx.x & 31u, n = blockIdx.x * (uint32_t)kSeqWarps + (threadIdx.x >> 5);
     if (n >= N) return;                                              // warp-uniform
     MarchSeq& w = seq[threadIdx.x >> 5];
     const uint32_t full = 0xffffffffu;
@@ -270,11 +276,11 @@ __global__ void __launch_bounds__(128) k_march_record_const(const float* __restr
         while (true) {
             const uint32_t c = __float_as_uint(fadd(exact, d)) - __float_as_uint(exact);
             if (lane >= first) {
-                seed = __uint_as_float(__float_as_uint(exact) + (lane - first) * 32u * c);
+                seed = __uint_as_float(__float_as_uint(exact) + (lane - first) * (uint32_t)kSeqPerLane * c);
                 v = seed; below = 0;
-                float* row = w.t + lane * 33u;
+                float* row = w.t + lane * (uint32_t)(kSeqPerLane + 1);
                 #pragma unroll 8
-                for (int i = 0; i < 32; ++i) { row[i] = v; below += (v < r.far) ? 1u : 0u; v = fadd(v, d); }
+                for (int i = 0; i < kSeqPerLane; ++i) { row[i] = v; below += (v < r.far) ? 1u : 0u; v = fadd(v, d); }
             }
             const float nxt = __shfl_down_sync(full, seed, 1);
             const bool bad = lane >= first && lane < 31u && __float_as_uint(v) != __float_as_uint(nxt);
@@ -287,39 +293,70 @@ __global__ void __launch_bounds__(128) k_march_record_const(const float* __restr
         const float t_next = __shfl_sync(full, v, 31);
         const int Kc = (int)__reduce_add_sync(full, below);         // elements of this chunk with t < far (a prefix: t is monotone)
         __syncwarp();
-        // ---- B: probe + successor
+        // ---- B1: probe every element (straight-line body, unrolled: the bitfield loads of several elements are in flight
+        // together);  B2: successor = k+1 when occupied, else the first later element >= tt
+        #pragma unroll 4
         for (int k = (int)lane; k < Kc; k += 32) {
             float x, y, z, dt, tt;
-            uint32_t j;
-            if (probe_cell(p, r, w.t[seq_pos(k)], x, y, z, dt, tt)) j = 0x8000u | (uint32_t)(k + 1);
-            else {
-                int q = k + 1;
+            const bool occ = probe_cell(p, r, w.t[seq_pos(k)], x, y, z, dt, tt);
+            w.tt[k] = occ ? -1.0f : tt;                              // tt >= t >= 0 for an empty cell
+        }
+        __syncwarp();
+        const float rd = __frcp_rn(d);
+        for (int k = (int)lane; k < Kc; k += 32) {
+            const float tt = w.tt[k];
+            uint32_t j = 0x8000u | (uint32_t)(k + 1);
+            if (tt >= 0.0f) {
+                // first q > k with t[q] >= tt: guess from the spacing, then correct against the exact sequence
+                int q = k + max(1, (int)fminf(ceilf((tt - w.t[seq_pos(k)]) * rd), 2048.0f));
+                q = min(q, kSeqChunk);
+                while (q > k + 1 && w.t[seq_pos(q - 1)] >= tt) --q;
                 while (q < kSeqChunk && w.t[seq_pos(q)] < tt) ++q;
                 j = (uint32_t)q;
             }
             w.next[k] = (uint16_t)j;
         }
         __syncwarp();
-        // ---- C: follow the links (uniform over the warp; lane 0 stores)
+        // B3: shorten runs of empty cells.  An empty cell records nothing, so its link may point past any number of further
+        // empty cells (pointer doubling, 3 rounds: runs shrink 8x).  Links that leave the chunk are kept: the walk must end on
+        // the cell whose own skip crosses the boundary, its tt is what carries over.  Lanes may read a link another lane is
+        // rewriting -- old and new value are both valid targets.
+        #pragma unroll 1
+        for (int round = 0; round < 3; ++round) {
+            for (int k = (int)lane; k < Kc; k += 32) {
+                const uint32_t j = w.next[k];
+                if (j < (uint32_t)Kc) {                               // k empty (bit 15 clear), j inside the probed range
+                    const uint32_t j2 = w.next[j];
+                    if (j2 < (uint32_t)kSeqChunk) w.next[k] = (uint16_t)j2;   // j empty too, and its skip stays in the chunk
+                }
+            }
+            __syncwarp();
+        }
+        // ---- C: follow the links.  This is the only serial part (one dependent shared-memory load per visited cell), so
+        // the loop body is kept branch-free: the index is stored unconditionally and the count advances on occupied cells.
         int k = 0;
         if (have_pending) {
             while (k < kSeqChunk && w.t[seq_pos(k)] < pending) ++k;
             have_pending = (k == kSeqChunk);
         }
+        const uint32_t num0 = num;
+        int last_k = -1;
+        uint32_t last_j = 0x8000u;
         while (k < Kc && num < max_steps) {
             const uint32_t j = w.next[k];
-            if (j & 0x8000u) {
-                if (lane == 0) tb[num] = w.t[seq_pos(k)];
-                ++num; ++k;
-            } else {
-                if (j == (uint32_t)kSeqChunk) {                      // the skip leaves this chunk: carry its target
-                    float x, y, z, dt;
-                    probe_cell(p, r, w.t[seq_pos(k)], x, y, z, dt, pending);
-                    have_pending = true;
-                }
-                k = (int)j;
-            }
+            const uint32_t occ = j >> 15;
+            w.samp[num - num0] = (uint16_t)k;                        // kept only when occ (num advances past it)
+            num += occ;
+            last_k = k; last_j = j;
+            k = (int)(j & 0x7fffu);
         }
+        if (last_j == (uint32_t)kSeqChunk) {                          // an empty cell whose skip leaves this chunk: carry its target
+            float x, y, z, dt;
+            probe_cell(p, r, w.t[seq_pos(last_k)], x, y, z, dt, pending);
+            have_pending = true;
+        }
+        __syncwarp();
+        for (uint32_t s = lane; s < num - num0; s += 32) tb[num0 + s] = w.t[seq_pos(w.samp[s])];
         if (Kc < kSeqChunk) break;                                   // the sequence passed `far` inside this chunk
         t_start = t_next;
         __syncwarp();
@@ -472,7 +509,7 @@ FOC_API int foc_march_rays_train(const float* rays_o, const float* rays_d, const
     float* tbuf = reinterpret_cast<float*>(static_cast<uint8_t*>(scratch) + march_counts_bytes(N));
     // constant step: warp-per-ray parallel walk; else serial walk, 4 rays per warp for small batches (see ray_of_thread)
     if (dt_gamma == 0.0f)
-        k_march_record_const<<<ceil_div(N, 4), 128, 0, S(stream)>>>(rays_o, rays_d, nears, fars, noises, N, max_steps, p, counts, tbuf);
+        k_march_record_const<<<ceil_div(N, (uint32_t)kSeqWarps), 32 * kSeqWarps, 0, S(stream)>>>(rays_o, rays_d, nears, fars, noises, N, max_steps, p, counts, tbuf);
     else if (N <= (uint32_t)kNumSMs * 32u * 8u)
         k_march_record<4><<<ceil_div(ceil_div(N, 4) * 32, 128), 128, 0, S(stream)>>>(rays_o, rays_d, nears, fars, noises, N, max_steps, p, counts, tbuf);
     else
