@@ -136,9 +136,10 @@ def run_ours(args):
                  optimizer="torch" if args.torch_optim else "fused")
     params = [p for p in tr.model.parameters()]
     if world > 1:                                   # data-parallel: identical replicas, gradients all-reduced every step
-        for p in params:
-            dist.broadcast(p.data, 0)
-        tr.grad_sync = lambda: [dist.all_reduce(g, op=dist.ReduceOp.AVG) for g in tr.grad_tensors()]
+        from focnerf_b200 import dist as fdist
+        fdist.broadcast_parameters(params)
+        tr.optimizer.refresh_shadows() if hasattr(tr.optimizer, "refresh_shadows") else None
+        tr.grad_sync = lambda: fdist.all_reduce_mean(tr.grad_tensors())
     pool_dev, pool_host = make_pool(scene, POOL, RAYS_PER_GPU, 1000 + 7919 * rank, dev)
     stage = [torch.empty_like(t) for t in pool_dev[0]]
 
