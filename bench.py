@@ -117,6 +117,45 @@ def cpu_baseline(scene, bits, cascade, rays=1024):
             "sample": f"1 train step (fwd+bwd+Adam) on {rays} rays of the same scene, oracle C port with OpenMP, {dt:.1f} s"}
 
 
+def render_bench(render_fn, dev, rank, world, frames=3, H=800, W=800):
+    """configs[2]: 800x800 inference render (march_rays / composite_rays loop with early termination), ray tiles sharded
+    over the ranks, tiles gathered once per frame.  -> {"value": Mrays/s whole job, ...} (same dict on every rank)."""
+    import torch
+    import torch.distributed as dist
+    from focnerf_b200 import synthetic
+    from focnerf_b200.dist import gather_tiles, ray_tile
+    pose = synthetic.ring_poses(8, radius=2.2, seed=123)[3]
+    o, d = synthetic.get_rays(pose, synthetic.intrinsics(H, W), H, W)
+    n = H * W
+    s, e = ray_tile(n, rank, world)
+    o, d = o[s:e].contiguous().to(dev), d[s:e].contiguous().to(dev)
+
+    def frame():
+        image, depth, ws = render_fn(o, d)
+        out = torch.cat([image, depth.unsqueeze(-1), ws.unsqueeze(-1)], -1)
+        return gather_tiles(out, n) if world > 1 else out
+
+    frame()                                          # warm-up (allocator, autotune-free: just first-touch)
+    if world > 1:
+        dist.barrier()
+    torch.cuda.synchronize()
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    e0.record()
+    for _ in range(frames):
+        out = frame()
+    e1.record()
+    if world > 1:
+        dist.barrier()
+    torch.cuda.synchronize()
+    ms = torch.tensor([e0.elapsed_time(e1)], device=dev)
+    if world > 1:
+        dist.all_reduce(ms, op=dist.ReduceOp.MAX)
+    ms = float(ms.item()) / frames
+    return {"metric": "800x800 render Mrays/s", "value": n / (ms * 1e-3) / 1e6, "unit": "Mrays/s", "ms_per_frame": ms, "frames": frames,
+            "rays": n, "scaling": "strong", "coverage": float((out[:, 4] > 0.5).float().mean().item()),
+            "workload": "configs[2]: one 800x800 test pose of the synthetic scene, T_thresh 1e-4, max_steps 1024, model as trained by the timed steps"}
+
+
 def run_ours(args):
     import numpy as np
     import torch
@@ -128,6 +167,8 @@ def run_ours(args):
     world, rank, local = int(os.environ.get("WORLD_SIZE", 1)), int(os.environ.get("RANK", 0)), int(os.environ.get("LOCAL_RANK", 0))
     torch.cuda.set_device(local)
     if world > 1:
+        if os.environ.get("FOC_KEEP_NCCL_DEBUG") != "1":
+            os.environ.pop("NCCL_DEBUG", None)      # NCCL_DEBUG=VERSION/WARN prints a banner on stdout; stdout carries ONE JSON line
         dist.init_process_group("nccl")
     dev = torch.device("cuda", local)
     scene, cascade, grid, bits, thresh = cases.scene_bitfield(1.0)
@@ -205,9 +246,24 @@ def run_ours(args):
         sync_all()
     tr.use_graph = use_graph
 
+    render = render_bench(tr.render, dev, rank, world, frames=args.frames) if args.frames > 0 else None
+
+    def shutdown():
+        """Captured graphs hold NCCL work: drop them before the communicator goes, and never let teardown hang the job."""
+        if world == 1:
+            return
+        sys.stdout.flush()
+        threading.Timer(30.0, lambda: os._exit(0)).start()
+        tr._graph = None
+        import gc
+        gc.collect()
+        torch.cuda.synchronize()
+        dist.barrier()
+        dist.destroy_process_group()
+        os._exit(0)
+
     if rank != 0:
-        if world > 1:
-            dist.destroy_process_group()
+        shutdown()
         return
     total_rays = world * RAYS_PER_GPU * args.steps
     hbm, how = peaks()
@@ -242,13 +298,13 @@ def run_ours(args):
         "e2e": {"value": total_rays / (ms_e2e * 1e-3), "unit": "rays/s", "ms_per_step": ms_e2e / args.steps,
                 "h2d_bytes_per_step": world * RAYS_PER_GPU * 9 * 4, "d2h_bytes_per_step": world * 4},
         "gpu_launches": int(round(kt.kernel_launches() / n_prof * args.steps)),
+        "render": render,
         "roofline": roof,
     }
     if world == 1:
         out["cpu_baseline"] = cpu_baseline(scene, bits, cascade)
     print(json.dumps(out))
-    if world > 1:
-        dist.destroy_process_group()
+    shutdown()
 
 
 def run_reference(args):
@@ -275,7 +331,8 @@ def run_reference(args):
 if __name__ == "__main__":
     ap = argparse.ArgumentParser()
     ap.add_argument("--gpus", type=int, default=1)
-    ap.add_argument("--steps", type=int, default=64)
+    ap.add_argument("--steps", type=int, default=256)
+    ap.add_argument("--frames", type=int, default=3, help="800x800 frames of the render workload (0 = skip)")
     ap.add_argument("--warmup", type=int, default=8)
     ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
     ap.add_argument("--no-graph", action="store_true", help="launch the step eagerly instead of replaying a CUDA graph")

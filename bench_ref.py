@@ -218,6 +218,36 @@ class RefTrainer:
         total = min(self.local_step, 16)
         self.mean_count = int(self.step_counter[:total, 0].sum().item() / total)
 
+    @torch.no_grad()
+    def render(self, rays_o, rays_d, T_thresh=1e-4):
+        """run_cuda, inference branch (legacy/nerf/renderer.py:331-372) on the reference extensions."""
+        N, dev = rays_o.shape[0], rays_o.device
+        nears, fars = torch.empty(N, device=dev), torch.empty(N, device=dev)
+        _rm.near_far_from_aabb(rays_o, rays_d, self.aabb, N, 0.2, nears, fars)
+        ws, depth, image = torch.zeros(N, device=dev), torch.zeros(N, device=dev), torch.zeros(N, 3, device=dev)
+        n_alive = N
+        rays_alive = torch.arange(n_alive, dtype=torch.int32, device=dev)
+        rays_t = nears.clone()
+        step = 0
+        with torch.autocast("cuda", dtype=torch.float16):
+            while step < 1024:
+                n_alive = rays_alive.shape[0]
+                if n_alive <= 0:
+                    break
+                n_step = max(min(N // n_alive, 8), 1)
+                M = n_alive * n_step
+                M += 128 - M % 128 if M % 128 else 0
+                xyzs, dirs, deltas = torch.zeros(M, 3, device=dev), torch.zeros(M, 3, device=dev), torch.zeros(M, 2, device=dev)
+                noises = torch.zeros(n_alive, device=dev)
+                _rm.march_rays(n_alive, n_step, rays_alive, rays_t, rays_o, rays_d, self.bound, 0.0, 1024, self.cascade, 128, self.bitfield,
+                               nears, fars, xyzs, dirs, deltas, noises)
+                sigmas, rgbs = self.model(xyzs, dirs)
+                _rm.composite_rays(n_alive, n_step, T_thresh, rays_alive, rays_t, sigmas.float().contiguous(), rgbs.float().contiguous(),
+                                   deltas, ws, depth, image)
+                rays_alive = rays_alive[rays_alive >= 0]
+                step += n_step
+        return image + (1 - ws).unsqueeze(-1), depth, ws
+
 
 def run(args):
     """-> the JSON dict for `bench.py --impl reference` (rank 0, one GPU: the reference has no multi-GPU path)."""
@@ -269,6 +299,7 @@ def run(args):
     ms_e2e = t0.elapsed_time(t1)
     rays = bench.RAYS_PER_GPU * args.steps
     val, val_e2e = rays / (ms * 1e-3), rays / (ms_e2e * 1e-3)
+    render = bench.render_bench(tr.render, dev, 0, 1, frames=args.frames) if args.frames > 0 else None
     return {
         "impl": "reference", "metric": "train rays/s", "value": val, "unit": "rays/s", "n_gpus": 1, "steps": args.steps, "warmup": warm,
         "ms_per_step": ms / args.steps, "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "f16", "data": "synthetic",
@@ -277,7 +308,7 @@ def run(args):
                    "note": "the reference's own CUDA extensions (raymarching, gridencoder, ffmlp: unmodified sources compiled for sm_100a) on the "
                            "same B200; the reference has no CPU implementation of this path and no multi-GPU path, so this arm always runs on "
                            "one GPU"},
-        "clocks": clk,
+        "clocks": clk, "render": render,
         "cpu_baseline": {"value": val, "unit": "rays/s", "cores": 0, "kind": "reference",
                          "sample": f"{args.steps} full train steps of 4096 rays on the reference CUDA extensions (GPU; the reference has no CPU path)"},
         "e2e": {"value": val_e2e, "unit": "rays/s", "ms_per_step": ms_e2e / args.steps, "h2d_bytes_per_step": bench.RAYS_PER_GPU * 36,

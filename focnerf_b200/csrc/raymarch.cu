@@ -498,10 +498,10 @@ FOC_API size_t foc_march_rays_train_scratch_bytes(uint32_t N, uint32_t max_steps
 // small N (a training batch) is latency-bound: one warp per CTA spreads the rays over all SMs
 static inline uint32_t march_block(uint32_t n) { return n <= (uint32_t)kNumSMs * 32u * 8u ? 32u : 128u; }
 
-FOC_API int foc_march_rays_train(const float* rays_o, const float* rays_d, const uint8_t* grid, float bound, float dt_gamma,
-                                 uint32_t max_steps, uint32_t N, uint32_t C, uint32_t H, uint32_t M, const float* nears,
-                                 const float* fars, float* xyzs, float* dirs, float* deltas, int32_t* rays, int32_t* counter,
-                                 const float* noises, void* scratch, void* stream) {
+// record + scan: rays[n] = (n, offset, count), counter[0] += total, counter[1] += N; the recorded parameters stay in `scratch`
+FOC_API int foc_march_rays_count(const float* rays_o, const float* rays_d, const uint8_t* grid, float bound, float dt_gamma,
+                                 uint32_t max_steps, uint32_t N, uint32_t C, uint32_t H, const float* nears, const float* fars,
+                                 int32_t* rays, int32_t* counter, const float* noises, void* scratch, void* stream) {
     if (N == 0) return 0;
     if (C == 0 || C > 8 || H == 0 || H > 1024 || (uint64_t)C * H * H * H > (1ull << 24)) return FOC_ERR_UNSUPPORTED;  // fp32 cell index exact (H1)
     const MarchParams p = make_march_params(grid, bound, dt_gamma, max_steps, C, H);
@@ -516,9 +516,27 @@ FOC_API int foc_march_rays_train(const float* rays_o, const float* rays_d, const
         k_march_record<32><<<ceil_div(N, 128), 128, 0, S(stream)>>>(rays_o, rays_d, nears, fars, noises, N, max_steps, p, counts, tbuf);
     FOC_LAUNCH_CHECK();
     k_march_scan<<<1, 1024, 0, S(stream)>>>(counts, N, rays, counter);
-    FOC_LAUNCH_CHECK();
+    FOC_LAUNCH_CHECK(); return 0;
+}
+
+// expand the records of foc_march_rays_count (same scratch, same rays) into samples; rays whose slice would pass M write nothing
+FOC_API int foc_march_rays_expand(const float* rays_o, const float* rays_d, float bound, float dt_gamma, uint32_t max_steps, uint32_t N,
+                                  uint32_t C, uint32_t H, uint32_t M, const float* nears, const int32_t* rays, const float* noises,
+                                  const void* scratch, float* xyzs, float* dirs, float* deltas, void* stream) {
+    if (N == 0) return 0;
+    if (C == 0 || C > 8 || H == 0 || H > 1024) return FOC_ERR_UNSUPPORTED;
+    const MarchParams p = make_march_params(nullptr, bound, dt_gamma, max_steps, C, H);
+    const float* tbuf = reinterpret_cast<const float*>(static_cast<const uint8_t*>(scratch) + march_counts_bytes(N));
     k_march_expand<<<ceil_div(N, 4), 128, 0, S(stream)>>>(rays_o, rays_d, nears, noises, N, M, max_steps, p, rays, tbuf, xyzs, dirs, deltas);
     FOC_LAUNCH_CHECK(); return 0;
+}
+
+FOC_API int foc_march_rays_train(const float* rays_o, const float* rays_d, const uint8_t* grid, float bound, float dt_gamma,
+                                 uint32_t max_steps, uint32_t N, uint32_t C, uint32_t H, uint32_t M, const float* nears,
+                                 const float* fars, float* xyzs, float* dirs, float* deltas, int32_t* rays, int32_t* counter,
+                                 const float* noises, void* scratch, void* stream) {
+    if (int rc = foc_march_rays_count(rays_o, rays_d, grid, bound, dt_gamma, max_steps, N, C, H, nears, fars, rays, counter, noises, scratch, stream)) return rc;
+    return foc_march_rays_expand(rays_o, rays_d, bound, dt_gamma, max_steps, N, C, H, M, nears, rays, noises, scratch, xyzs, dirs, deltas, stream);
 }
 
 FOC_API int foc_march_rays(uint32_t n_alive, uint32_t n_step, const int32_t* rays_alive, const float* rays_t,

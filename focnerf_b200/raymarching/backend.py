@@ -80,6 +80,18 @@ class _Backend:
 
     # ---- new entry points (no reference counterpart) ---------------------------------------------------------------
     @staticmethod
+    def march_rays_count(rays_o, rays_d, grid, bound, dt_gamma, max_steps, N, C, H, nears, fars, rays, counter, noises, scratch):
+        require_cuda(rays_o, rays_d, grid, nears, fars, rays, counter, noises, scratch)
+        check(lib().foc_march_rays_count(ptr(rays_o), ptr(rays_d), ptr(grid), bound, dt_gamma, max_steps, N, C, H, ptr(nears), ptr(fars),
+                                         ptr(rays), ptr(counter), ptr(noises), ptr(scratch), stream()), "march_rays_count")
+
+    @staticmethod
+    def march_rays_expand(rays_o, rays_d, bound, dt_gamma, max_steps, N, C, H, M, nears, rays, noises, scratch, xyzs, dirs, deltas):
+        require_cuda(rays_o, rays_d, nears, rays, noises, scratch, xyzs, dirs, deltas)
+        check(lib().foc_march_rays_expand(ptr(rays_o), ptr(rays_d), bound, dt_gamma, max_steps, N, C, H, M, ptr(nears), ptr(rays),
+                                          ptr(noises), ptr(scratch), ptr(xyzs), ptr(dirs), ptr(deltas), stream()), "march_rays_expand")
+
+    @staticmethod
     def compact_alive(rays_alive, n, out, n_out):
         require_cuda(rays_alive, out, n_out)
         scratch = torch.empty(max(4, lib().foc_compact_alive_scratch_bytes(n)), dtype=torch.uint8, device=rays_alive.device)

@@ -192,6 +192,30 @@ class _composite_rays(Function):
 composite_rays = _composite_rays.apply
 
 
+@torch.no_grad()
+def march_rays_all(rays_o, rays_d, bound, density_bitfield, C, H, nears, fars, align=128, dt_gamma=0, max_steps=1024):
+    """Not in the reference: every sample of every ray (what march_rays_train(force_all_rays=True, perturb=False) returns),
+    but with the sample buffers sized EXACTLY -- walk + scan first, one 4-byte D2H read of the total, then the expansion --
+    instead of the reference's N * max_steps worst case (raymarching.py:196), which is 21 GB for an 800x800 frame.
+    Returns xyzs [M,3], dirs [M,3], deltas [M,2], rays [N,3] with M the total rounded up to `align`."""
+    rays_o, rays_d = _cuda(rays_o).float().contiguous().view(-1, 3), _cuda(rays_d).float().contiguous().view(-1, 3)
+    density_bitfield = _cuda(density_bitfield).contiguous()
+    N, dev = rays_o.shape[0], rays_o.device
+    from .._lib import lib
+    scratch = torch.empty(max(1, lib().foc_march_rays_train_scratch_bytes(N, max_steps)), dtype=torch.uint8, device=dev)
+    rays = torch.empty(N, 3, dtype=torch.int32, device=dev)
+    counter = torch.zeros(2, dtype=torch.int32, device=dev)
+    noises = torch.zeros(N, dtype=torch.float32, device=dev)
+    _backend.march_rays_count(rays_o, rays_d, density_bitfield, bound, dt_gamma, max_steps, N, C, H, nears, fars, rays, counter,
+                              noises, scratch)
+    M = _pad_up(max(int(counter[0].item()), 1), align)
+    xyzs = torch.zeros(M, 3, dtype=torch.float32, device=dev)
+    dirs = torch.zeros(M, 3, dtype=torch.float32, device=dev)
+    deltas = torch.zeros(M, 2, dtype=torch.float32, device=dev)
+    _backend.march_rays_expand(rays_o, rays_d, bound, dt_gamma, max_steps, N, C, H, M, nears, rays, noises, scratch, xyzs, dirs, deltas)
+    return xyzs, dirs, deltas, rays
+
+
 def compact_alive(rays_alive, n_alive=None):
     """Device-side replacement for `rays_alive[rays_alive >= 0]` (legacy/nerf/renderer.py:363).
 

@@ -150,14 +150,33 @@ class Trainer:
 
     # ------------------------------------------------------------------------------------------------ inference
     @torch.no_grad()
-    def render(self, rays_o, rays_d, bg_color=1.0, T_thresh=1e-4, device_compaction=True):
-        """run_cuda, inference branch (legacy/nerf/renderer.py:331-372).  device_compaction=True swaps the reference's
-        boolean-mask indexing for raymarching.compact_alive; the alive count is still read once per iteration because
-        the caller-owned loop sizes its launches with it."""
+    def render(self, rays_o, rays_d, bg_color=1.0, T_thresh=1e-4, device_compaction=True, mode="single_pass"):
+        """run_cuda, inference branch (legacy/nerf/renderer.py:331-372).
+
+        mode="loop": the reference's caller-owned loop (march_rays -> field -> composite_rays, n_step = min(N // n_alive, 8)).
+          One host read of the alive count per iteration (it sizes the next launches): ~45 iterations of ~15
+          launches for an 800x800 frame, host-bound on B200.  device_compaction=True swaps the boolean-mask indexing for
+          raymarching.compact_alive.
+        mode="single_pass" (default): the same samples and the same front-to-back recurrence, but marched for all rays at once
+          into exactly-sized ray-ordered buffers (march_rays_all: one 4-byte host read per frame), one field evaluation, one
+          compositor launch with the same early termination.  Samples behind the termination point are evaluated and
+          discarded -- the tensor pipe and HBM are far from saturated, the launch/sync chain was the bound."""
         self.model.eval()
         rays_o, rays_d = rays_o.contiguous().view(-1, 3), rays_d.contiguous().view(-1, 3)
         N, dev = rays_o.shape[0], rays_o.device
         nears, fars = raymarching.near_far_from_aabb(rays_o, rays_d, self.aabb, self.min_near)
+        if mode == "single_pass":
+            xyzs, dirs, deltas, rays = raymarching.march_rays_all(rays_o, rays_d, self.bound, self.density_bitfield, self.cascade,
+                                                                  self.grid_size, nears, fars, 128, self.dt_gamma, self.max_steps)
+            with torch.autocast("cuda", dtype=torch.float16, enabled=self.fp16):
+                sigmas, rgbs = (self.model.forward_fused if self.fused and self.fp16 else self.model)(xyzs, dirs)
+                weights_sum, depth, image = raymarching.composite_rays_train(sigmas, rgbs, deltas, rays, T_thresh)
+            image = image + (1 - weights_sum).unsqueeze(-1) * bg_color
+            # the training compositor measures depth from the first sample's start (raymarching.cu:545 starts t at 0), the
+            # inference one from the ray origin (raymarching.cu:858 starts at rays_t): add the offset sum_i w_i * near
+            depth = depth + torch.where(weights_sum > 0, nears, torch.zeros_like(nears)) * weights_sum
+            depth = torch.clamp(depth - nears, min=0) / (fars - nears)
+            return image, depth, weights_sum
         weights_sum = torch.zeros(N, dtype=torch.float32, device=dev)
         depth = torch.zeros(N, dtype=torch.float32, device=dev)
         image = torch.zeros(N, 3, dtype=torch.float32, device=dev)

@@ -49,6 +49,15 @@ int foc_march_rays_train(const float *rays_o, const float *rays_d, const uint8_t
                          uint32_t max_steps, uint32_t N, uint32_t C, uint32_t H, uint32_t M, const float *nears,
                          const float *fars, float *xyzs, float *dirs, float *deltas, int32_t *rays, int32_t *counter,
                          const float *noises, void *scratch, void *stream);
+/* The two halves of foc_march_rays_train, for callers that size the sample buffers exactly (no reference counterpart):
+ * count  = walk + exclusive scan: rays [N,3] = (ray, offset, count), counter[0] += total samples, counter[1] += N;
+ * expand = write xyzs/dirs/deltas [M,*] from the parameters recorded in `scratch` by the count call (same N, max_steps). */
+int foc_march_rays_count(const float *rays_o, const float *rays_d, const uint8_t *grid, float bound, float dt_gamma,
+                         uint32_t max_steps, uint32_t N, uint32_t C, uint32_t H, const float *nears, const float *fars,
+                         int32_t *rays, int32_t *counter, const float *noises, void *scratch, void *stream);
+int foc_march_rays_expand(const float *rays_o, const float *rays_d, float bound, float dt_gamma, uint32_t max_steps, uint32_t N,
+                          uint32_t C, uint32_t H, uint32_t M, const float *nears, const int32_t *rays, const float *noises,
+                          const void *scratch, float *xyzs, float *dirs, float *deltas, void *stream);
 
 /* replaces composite_rays_train_forward / _backward, raymarching.h:14-15 (raymarching.cu:501-577, 602-682) */
 int foc_composite_rays_train_forward(const float *sigmas, const float *rgbs, const float *deltas, const int32_t *rays,

@@ -36,10 +36,29 @@ def test_render_loop_compaction_equivalence():
     scene, tr = _trainer()
     o, d = cases.camera_rays(20000, 7)
     o, d = torch.from_numpy(o).cuda(), torch.from_numpy(d).cuda()
-    a = tr.render(o, d, device_compaction=True)
-    b = tr.render(o, d, device_compaction=False)
+    a = tr.render(o, d, device_compaction=True, mode="loop")
+    b = tr.render(o, d, device_compaction=False, mode="loop")
     for x, y in zip(a, b):
         assert torch.equal(torch.nan_to_num(x), torch.nan_to_num(y))
+
+
+def test_render_single_pass_matches_loop():
+    """The single-pass render (all samples marched at once, one compositor launch) reproduces the reference-style loop."""
+    scene, tr = _trainer()
+    for it in range(48):                                           # a partly trained field, so early termination is exercised
+        o, d = cases.camera_rays(4096, 300 + it)
+        o, d = torch.from_numpy(o).cuda(), torch.from_numpy(d).cuda()
+        tr.train_step(o, d, scene.render_gt(o, d))
+        if (it + 1) % 16 == 0:
+            tr.update_mean_count()
+    o, d = cases.camera_rays(30000, 9)
+    o, d = torch.from_numpy(o).cuda(), torch.from_numpy(d).cuda()
+    a = tr.render(o, d, mode="single_pass")
+    b = tr.render(o, d, mode="loop")
+    assert float(b[2].max()) > 0.5                                 # something was hit
+    for x, y, tol in zip(a, b, (2e-3, 2e-3, 2e-3)):
+        x, y = torch.nan_to_num(x), torch.nan_to_num(y)
+        assert torch.allclose(x, y, atol=tol, rtol=0), float((x - y).abs().max())
 
 
 def test_forward_fused_matches_forward():
