@@ -118,6 +118,132 @@ k_composite_train_bwd(const float* __restrict__ grad_weights_sum, const float* _
     }
 }
 
+// ---- loss head fused into the compositor (no reference kernel: legacy/nerf/renderer.py:313-316 + nerf/utils.py:535-545
+// run ~14 elementwise / reduction kernels for  pred = image + (1 - weights_sum) * bg;  loss = mean((pred - gt)^2) )
+//
+// forward : the K7 scan, then lane 0 also writes err[id] = sum_c (pred_c - gt_c)^2; k_mse_finish sums err in a fixed order.
+// backward: the K8 scan with  g_image = grad_loss * 2 (pred - gt) / (3N)  and  g_ws = -bg * sum_c g_image_c  formed in
+//           registers.  With `ordered` (slices in ascending ray order, what foc_march_rays_train produces) the kernel also
+//           zero-fills every gradient row it does not own a value for -- past the termination sample, the rows of dropped
+//           rays and the padding rows [total, M) -- so the caller need not pre-zero the buffers.
+__global__ void __launch_bounds__(32 * kCompWarpsPerCta)
+k_composite_mse_fwd(const float* __restrict__ sigmas, const float* __restrict__ rgbs, const float* __restrict__ deltas,
+                    const int32_t* __restrict__ rays, const float* __restrict__ gt, float bg, uint32_t M, uint32_t N, float T_thresh,
+                    float* __restrict__ weights_sum, float* __restrict__ depth, float* __restrict__ image, float* __restrict__ err) {
+    const int lane = threadIdx.x & 31;
+    const uint32_t n = blockIdx.x * kCompWarpsPerCta + (threadIdx.x >> 5);
+    if (n >= N) return;
+    const uint32_t id = (uint32_t)__ldg(rays + 3 * (size_t)n), off = (uint32_t)__ldg(rays + 3 * (size_t)n + 1),
+                   cnt = (uint32_t)__ldg(rays + 3 * (size_t)n + 2);
+    float r = 0.f, g = 0.f, b = 0.f, d = 0.f, ws = 0.f;
+    if (cnt != 0 && (uint64_t)off + cnt <= M) {
+        float T = 1.0f, t_base = 0.0f;
+        for (uint32_t base = 0; base < cnt; base += 32) {
+            const uint32_t s = base + lane;
+            const bool valid = s < cnt;
+            const size_t i = (size_t)off + (valid ? s : 0);
+            float alpha = 0.f, d1 = 0.f, cr = 0.f, cg = 0.f, cb = 0.f;
+            if (valid) {
+                const float2 dl = __ldg(reinterpret_cast<const float2*>(deltas) + i);
+                alpha = 1.0f - __expf(-__ldg(sigmas + i) * dl.x);
+                d1 = dl.y;
+                cr = __ldg(rgbs + 3 * i); cg = __ldg(rgbs + 3 * i + 1); cb = __ldg(rgbs + 3 * i + 2);
+            }
+            const float incl = warp_incl_prod(1.0f - alpha, lane);
+            const float w = alpha * (T * excl_from_incl_prod(incl, lane));
+            const float T_after = T * incl;
+            const float t = t_base + warp_incl_sum(d1, lane);
+            const uint32_t stop = __ballot_sync(0xffffffffu, valid && T_after < T_thresh);
+            const int last = stop ? (__ffs(stop) - 1) : 31;
+            if (valid && lane <= last) {
+                r = fmaf(w, cr, r); g = fmaf(w, cg, g); b = fmaf(w, cb, b);
+                d = fmaf(w, t, d); ws += w;
+            }
+            if (stop) break;
+            T = bcast_last(T_after); t_base = bcast_last(t);
+        }
+        r = warp_sum(r); g = warp_sum(g); b = warp_sum(b); d = warp_sum(d); ws = warp_sum(ws);
+    }
+    if (lane == 0) {
+        weights_sum[id] = ws; depth[id] = d;
+        image[3 * (size_t)id] = r; image[3 * (size_t)id + 1] = g; image[3 * (size_t)id + 2] = b;
+        const float mix = (1.0f - ws) * bg;
+        const float e0 = (r + mix) - __ldg(gt + 3 * (size_t)id), e1 = (g + mix) - __ldg(gt + 3 * (size_t)id + 1), e2 = (b + mix) - __ldg(gt + 3 * (size_t)id + 2);
+        err[id] = e0 * e0 + e1 * e1 + e2 * e2;
+    }
+}
+
+// loss[0] = sum(err[0..N)) / (3N), one CTA, fixed summation order
+__global__ void __launch_bounds__(1024) k_mse_finish(const float* __restrict__ err, uint32_t N, float* __restrict__ loss) {
+    __shared__ float part[32];
+    float acc = 0.f;
+    for (uint32_t i = threadIdx.x; i < N; i += 1024) acc += __ldg(err + i);
+    acc = warp_sum(acc);
+    if ((threadIdx.x & 31) == 0) part[threadIdx.x >> 5] = acc;
+    __syncthreads();
+    if (threadIdx.x < 32) {
+        const float t = warp_sum(part[threadIdx.x]);
+        if (threadIdx.x == 0) loss[0] = t / (3.0f * (float)N);
+    }
+}
+
+__global__ void __launch_bounds__(32 * kCompWarpsPerCta)
+k_composite_mse_bwd(const float* __restrict__ grad_loss, const float* __restrict__ gt, float bg,
+                    const float* __restrict__ sigmas, const float* __restrict__ rgbs, const float* __restrict__ deltas,
+                    const int32_t* __restrict__ rays, const float* __restrict__ weights_sum, const float* __restrict__ image,
+                    uint32_t M, uint32_t N, float T_thresh, int ordered, float* __restrict__ grad_sigmas, float* __restrict__ grad_rgbs) {
+    const int lane = threadIdx.x & 31;
+    const uint32_t n = blockIdx.x * kCompWarpsPerCta + (threadIdx.x >> 5);
+    if (n >= N) return;
+    const uint32_t id = (uint32_t)__ldg(rays + 3 * (size_t)n), off = (uint32_t)__ldg(rays + 3 * (size_t)n + 1),
+                   cnt = (uint32_t)__ldg(rays + 3 * (size_t)n + 2);
+    auto zero_rows = [&](uint64_t lo, uint64_t hi) {                  // rows [lo, hi) of both gradient arrays
+        for (uint64_t i = lo + lane; i < hi; i += 32) {
+            grad_sigmas[i] = 0.f; grad_rgbs[3 * i] = 0.f; grad_rgbs[3 * i + 1] = 0.f; grad_rgbs[3 * i + 2] = 0.f;
+        }
+    };
+    const bool kept = (uint64_t)off + cnt <= M;
+    if (ordered) {
+        if (!kept && off < M) zero_rows(off, M);                       // the FIRST dropped ray (off <= M < off + cnt) owns the rest
+        if (kept && n == N - 1) zero_rows((uint64_t)off + cnt, M);     // nothing dropped: the last ray owns the padding rows
+    }
+    if (cnt == 0 || !kept) return;
+    const float rf = __ldg(image + 3 * (size_t)id), gf = __ldg(image + 3 * (size_t)id + 1), bf = __ldg(image + 3 * (size_t)id + 2);
+    const float wsf = __ldg(weights_sum + id);
+    const float mix = (1.0f - wsf) * bg, k = __ldg(grad_loss) * (2.0f / (3.0f * (float)N));
+    const float gr = k * ((rf + mix) - __ldg(gt + 3 * (size_t)id)), gg = k * ((gf + mix) - __ldg(gt + 3 * (size_t)id + 1)),
+                gb = k * ((bf + mix) - __ldg(gt + 3 * (size_t)id + 2));
+    const float gw = -bg * (gr + gg + gb);
+    const float ws_term = gw * (1.0f - wsf);
+    float T = 1.0f, ar = 0.f, ag = 0.f, ab = 0.f;
+    uint32_t done = cnt;                                               // first row of this ray that holds no gradient
+    for (uint32_t base = 0; base < cnt; base += 32) {
+        const uint32_t s = base + lane;
+        const bool valid = s < cnt;
+        const size_t i = (size_t)off + (valid ? s : 0);
+        float alpha = 0.f, d0 = 0.f, cr = 0.f, cg = 0.f, cb = 0.f;
+        if (valid) {
+            d0 = __ldg(deltas + 2 * i);
+            alpha = 1.0f - __expf(-__ldg(sigmas + i) * d0);
+            cr = __ldg(rgbs + 3 * i); cg = __ldg(rgbs + 3 * i + 1); cb = __ldg(rgbs + 3 * i + 2);
+        }
+        const float incl = warp_incl_prod(1.0f - alpha, lane);
+        const float w = alpha * (T * excl_from_incl_prod(incl, lane));
+        const float T_after = T * incl;
+        const float pr = ar + warp_incl_sum(w * cr, lane), pg = ag + warp_incl_sum(w * cg, lane), pb = ab + warp_incl_sum(w * cb, lane);
+        const uint32_t stop = __ballot_sync(0xffffffffu, valid && T_after < T_thresh);
+        const int last = stop ? (__ffs(stop) - 1) : 31;
+        if (valid && lane <= last) {
+            grad_rgbs[3 * i] = gr * w; grad_rgbs[3 * i + 1] = gg * w; grad_rgbs[3 * i + 2] = gb * w;
+            grad_sigmas[i] = d0 * (gr * (T_after * cr - (rf - pr)) + gg * (T_after * cg - (gf - pg)) +
+                                   gb * (T_after * cb - (bf - pb)) + ws_term);
+        }
+        if (stop) { done = base + (uint32_t)last + 1; break; }
+        T = bcast_last(T_after); ar = bcast_last(pr); ag = bcast_last(pg); ab = bcast_last(pb);
+    }
+    if (ordered) zero_rows((uint64_t)off + done, (uint64_t)off + cnt);
+}
+
 // ------------------------------------------------------------------------------------------------ C ABI
 static inline cudaStream_t S(void* s) { return reinterpret_cast<cudaStream_t>(s); }
 
@@ -137,5 +263,25 @@ FOC_API int foc_composite_rays_train_backward(const float* grad_weights_sum, con
     if (N == 0) return 0;
     k_composite_train_bwd<<<ceil_div(N, kCompWarpsPerCta), 32 * kCompWarpsPerCta, 0, S(stream)>>>(
         grad_weights_sum, grad_image, sigmas, rgbs, deltas, rays, weights_sum, image, M, N, T_thresh, grad_sigmas, grad_rgbs);
+    FOC_LAUNCH_CHECK(); return 0;
+}
+
+FOC_API int foc_composite_mse_forward(const float* sigmas, const float* rgbs, const float* deltas, const int32_t* rays, const float* gt,
+                                      float bg, uint32_t M, uint32_t N, float T_thresh, float* weights_sum, float* depth, float* image,
+                                      float* err, float* loss, void* stream) {
+    if (N == 0) return 0;
+    k_composite_mse_fwd<<<ceil_div(N, kCompWarpsPerCta), 32 * kCompWarpsPerCta, 0, S(stream)>>>(
+        sigmas, rgbs, deltas, rays, gt, bg, M, N, T_thresh, weights_sum, depth, image, err);
+    FOC_LAUNCH_CHECK();
+    k_mse_finish<<<1, 1024, 0, S(stream)>>>(err, N, loss);
+    FOC_LAUNCH_CHECK(); return 0;
+}
+
+FOC_API int foc_composite_mse_backward(const float* grad_loss, const float* gt, float bg, const float* sigmas, const float* rgbs,
+                                       const float* deltas, const int32_t* rays, const float* weights_sum, const float* image, uint32_t M,
+                                       uint32_t N, float T_thresh, int ordered, float* grad_sigmas, float* grad_rgbs, void* stream) {
+    if (N == 0) return 0;
+    k_composite_mse_bwd<<<ceil_div(N, kCompWarpsPerCta), 32 * kCompWarpsPerCta, 0, S(stream)>>>(
+        grad_loss, gt, bg, sigmas, rgbs, deltas, rays, weights_sum, image, M, N, T_thresh, ordered, grad_sigmas, grad_rgbs);
     FOC_LAUNCH_CHECK(); return 0;
 }

@@ -408,7 +408,21 @@ __global__ void __launch_bounds__(128) k_march_expand(const float* __restrict__ 
     const uint32_t n = (blockIdx.x * blockDim.x + threadIdx.x) >> 5, lane = threadIdx.x & 31u;
     if (n >= N) return;
     const uint32_t off = (uint32_t)__ldg(rays + 3 * (size_t)n + 1), num = (uint32_t)__ldg(rays + 3 * (size_t)n + 2);
-    if (num == 0 || (uint64_t)off + num > M) return;                  // raymarching.cu:415-416
+    // Rows no ray writes must read as zero (delta == 0 marks padding for the compositors, raymarching.cu:858; the reference
+    // wrapper pre-zeroes all three buffers).  Slices are in ascending ray order, so the kept rays are a prefix: the first
+    // dropped ray (off <= M < off + num) owns [off, M); if nothing is dropped the last ray owns [off + num, M).
+    {
+        const bool kept = (uint64_t)off + num <= M;
+        uint64_t lo = M;
+        if (!kept && off < M) lo = off;
+        else if (kept && n == N - 1) lo = (uint64_t)off + num;
+        for (uint64_t i = lo + lane; i < M; i += 32) {
+            xyzs[3 * i] = 0.f; xyzs[3 * i + 1] = 0.f; xyzs[3 * i + 2] = 0.f;
+            dirs[3 * i] = 0.f; dirs[3 * i + 1] = 0.f; dirs[3 * i + 2] = 0.f;
+            reinterpret_cast<float2*>(deltas)[i] = make_float2(0.f, 0.f);
+        }
+        if (num == 0 || !kept) return;                                // raymarching.cu:415-416
+    }
     const float ox = __ldg(rays_o + 3 * (size_t)n), oy = __ldg(rays_o + 3 * (size_t)n + 1), oz = __ldg(rays_o + 3 * (size_t)n + 2);
     const float dx = __ldg(rays_d + 3 * (size_t)n), dy = __ldg(rays_d + 3 * (size_t)n + 1), dz = __ldg(rays_d + 3 * (size_t)n + 2);
     const float near = __ldg(nears + n);

@@ -92,6 +92,22 @@ class _Backend:
                                           ptr(noises), ptr(scratch), ptr(xyzs), ptr(dirs), ptr(deltas), stream()), "march_rays_expand")
 
     @staticmethod
+    def composite_mse_forward(sigmas, rgbs, deltas, rays, gt, bg, M, N, T_thresh, weights_sum, depth, image, err, loss):
+        require_cuda(sigmas, rgbs, deltas, rays, gt, weights_sum, depth, image, err, loss)
+        for t, nm in ((sigmas, "sigmas"), (rgbs, "rgbs"), (deltas, "deltas"), (gt, "gt")):
+            _f32c(t, nm)
+        check(lib().foc_composite_mse_forward(ptr(sigmas), ptr(rgbs), ptr(deltas), ptr(rays), ptr(gt), bg, M, N, T_thresh, ptr(weights_sum),
+                                              ptr(depth), ptr(image), ptr(err), ptr(loss), stream()), "composite_mse_forward")
+
+    @staticmethod
+    def composite_mse_backward(grad_loss, gt, bg, sigmas, rgbs, deltas, rays, weights_sum, image, M, N, T_thresh, ordered, grad_sigmas,
+                               grad_rgbs):
+        require_cuda(grad_loss, gt, sigmas, rgbs, deltas, rays, weights_sum, image, grad_sigmas, grad_rgbs)
+        check(lib().foc_composite_mse_backward(ptr(grad_loss), ptr(gt), bg, ptr(sigmas), ptr(rgbs), ptr(deltas), ptr(rays), ptr(weights_sum),
+                                               ptr(image), M, N, T_thresh, int(ordered), ptr(grad_sigmas), ptr(grad_rgbs), stream()),
+              "composite_mse_backward")
+
+    @staticmethod
     def compact_alive(rays_alive, n, out, n_out):
         require_cuda(rays_alive, out, n_out)
         scratch = torch.empty(max(4, lib().foc_compact_alive_scratch_bytes(n)), dtype=torch.uint8, device=rays_alive.device)

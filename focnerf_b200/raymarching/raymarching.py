@@ -110,10 +110,11 @@ class _march_rays_train(Function):
         if not force_all_rays and mean_count > 0:
             M = _pad_up(mean_count, align)
         dev, dt = rays_o.device, rays_o.dtype
-        # zero-filled: the compositors rely on delta == 0 in unused / padding slots (raymarching.cu:858)
-        xyzs = torch.zeros(M, 3, dtype=dt, device=dev)
-        dirs = torch.zeros(M, 3, dtype=dt, device=dev)
-        deltas = torch.zeros(M, 2, dtype=dt, device=dev)
+        # unused / padding slots must read as zero (the compositors rely on delta == 0, raymarching.cu:858): the reference
+        # pre-zeroes the buffers here, our expand kernel zero-fills exactly the rows no ray owns
+        xyzs = torch.empty(M, 3, dtype=dt, device=dev)
+        dirs = torch.empty(M, 3, dtype=dt, device=dev)
+        deltas = torch.empty(M, 2, dtype=dt, device=dev)
         rays = torch.empty(N, 3, dtype=torch.int32, device=dev)
         if step_counter is None:
             step_counter = torch.zeros(2, dtype=torch.int32, device=dev)
@@ -157,6 +158,42 @@ class _composite_rays_train(Function):
 
 
 composite_rays_train = _composite_rays_train.apply
+
+
+class _composite_rays_train_mse(Function):
+    """composite_rays_train + background mix + MSE against gt, fused (csrc/composite.cu k_composite_mse_*).
+    Returns (loss [], image_with_bg [N,3], weights_sum [N], depth [N]); only `loss` carries a gradient.
+    `rays` must hold slices in ascending ray order (what march_rays_train of this package produces)."""
+
+    @staticmethod
+    @_fwd32
+    def forward(ctx, sigmas, rgbs, deltas, rays, gt, bg_color=1.0, T_thresh=1e-4):
+        sigmas, rgbs, gt = sigmas.contiguous(), rgbs.contiguous(), gt.contiguous()
+        M, N = sigmas.shape[0], rays.shape[0]
+        dev = sigmas.device
+        weights_sum = torch.empty(N, dtype=torch.float32, device=dev)
+        depth = torch.empty(N, dtype=torch.float32, device=dev)
+        image = torch.empty(N, 3, dtype=torch.float32, device=dev)
+        err = torch.empty(N, dtype=torch.float32, device=dev)
+        loss = torch.empty(1, dtype=torch.float32, device=dev)
+        _backend.composite_mse_forward(sigmas, rgbs, deltas, rays, gt, float(bg_color), M, N, T_thresh, weights_sum, depth, image, err, loss)
+        ctx.save_for_backward(sigmas, rgbs, deltas, rays, gt, weights_sum, image)
+        ctx.dims = (M, N, T_thresh, float(bg_color))
+        ctx.mark_non_differentiable(weights_sum, depth, image)
+        return loss.view(()), image, weights_sum, depth
+
+    @staticmethod
+    @custom_bwd(device_type="cuda")
+    def backward(ctx, grad_loss, g_image, g_ws, g_depth):
+        sigmas, rgbs, deltas, rays, gt, weights_sum, image = ctx.saved_tensors
+        M, N, T_thresh, bg = ctx.dims
+        grad_sigmas, grad_rgbs = torch.empty_like(sigmas), torch.empty_like(rgbs)       # fully written by the kernel (ordered = 1)
+        _backend.composite_mse_backward(grad_loss.float().contiguous().view(1), gt, bg, sigmas, rgbs, deltas, rays, weights_sum, image,
+                                        M, N, T_thresh, 1, grad_sigmas, grad_rgbs)
+        return grad_sigmas, grad_rgbs, None, None, None, None, None
+
+
+composite_rays_train_mse = _composite_rays_train_mse.apply
 
 
 class _march_rays(Function):
@@ -209,9 +246,9 @@ def march_rays_all(rays_o, rays_d, bound, density_bitfield, C, H, nears, fars, a
     _backend.march_rays_count(rays_o, rays_d, density_bitfield, bound, dt_gamma, max_steps, N, C, H, nears, fars, rays, counter,
                               noises, scratch)
     M = _pad_up(max(int(counter[0].item()), 1), align)
-    xyzs = torch.zeros(M, 3, dtype=torch.float32, device=dev)
-    dirs = torch.zeros(M, 3, dtype=torch.float32, device=dev)
-    deltas = torch.zeros(M, 2, dtype=torch.float32, device=dev)
+    xyzs = torch.empty(M, 3, dtype=torch.float32, device=dev)          # the expand kernel zero-fills the padding rows
+    dirs = torch.empty(M, 3, dtype=torch.float32, device=dev)
+    deltas = torch.empty(M, 2, dtype=torch.float32, device=dev)
     _backend.march_rays_expand(rays_o, rays_d, bound, dt_gamma, max_steps, N, C, H, M, nears, rays, noises, scratch, xyzs, dirs, deltas)
     return xyzs, dirs, deltas, rays
 

@@ -175,6 +175,20 @@ int foc_rgb_sigmoid_backward(const float *grad_rgb, const float *rgb, uint32_t B
  * from the reference tree: closed form, parity unpinned).  dirs [B,3] -> outputs [B, degree^2] f32. */
 int foc_sh_encode_forward(const float *dirs, uint32_t B, uint32_t degree, float *outputs, void *stream);
 
+/* ---------------------------------------------------------------- loss head fused into the training compositor
+ * (no reference kernel: legacy/nerf/renderer.py:313-316 + nerf/utils.py:535-545 as ~14 elementwise / reduction launches)
+ * forward : composite_rays_train_forward, plus pred = image + (1 - weights_sum) * bg, err[ray] = sum_c (pred_c - gt_c)^2 and
+ *           loss[0] = sum(err) / (3N) (fixed summation order).  `image` holds the un-mixed composite (the backward needs it).
+ * backward: composite_rays_train_backward with g_image = grad_loss[0] * 2 (pred - gt) / (3N), g_ws = -bg * sum_c g_image_c
+ *           formed on the fly.  ordered != 0 (slices in ascending ray order, as foc_march_rays_train lays them out): every
+ *           gradient row without a value is zero-filled by the kernel, the caller need not pre-zero. */
+int foc_composite_mse_forward(const float *sigmas, const float *rgbs, const float *deltas, const int32_t *rays, const float *gt,
+                              float bg, uint32_t M, uint32_t N, float T_thresh, float *weights_sum, float *depth, float *image,
+                              float *err, float *loss, void *stream);
+int foc_composite_mse_backward(const float *grad_loss, const float *gt, float bg, const float *sigmas, const float *rgbs,
+                               const float *deltas, const int32_t *rays, const float *weights_sum, const float *image, uint32_t M,
+                               uint32_t N, float T_thresh, int ordered, float *grad_sigmas, float *grad_rgbs, void *stream);
+
 /* ---------------------------------------------------------------- optimiser step of the path
  * Dense Adam + dynamic loss scaling, replacing torch.optim.Adam(betas, eps) + torch.amp.GradScaler as the reference's
  * train step uses them (main_nerf.py:211,472; nerf/utils.py:866-868), with torch's arithmetic (torch/optim/adam.py,

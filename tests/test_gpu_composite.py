@@ -117,3 +117,34 @@ def test_sample_uniform_offset_and_masks():
     img2, _, _ = foc.composite_multi(sig, masked, n0, f0, bg=1.0)
     ok = ((n0 < 1e30) & (n2 < 1e30)).cpu().numpy()
     close(img.cpu().numpy()[ok], img2.cpu().numpy()[ok], "in-kernel masks vs pre-masked colours")
+
+
+def test_composite_mse_matches_unfused():
+    """composite_rays_train_mse == composite_rays_train + background mix + mse_loss, value and gradients; the fused
+    backward zero-fills the rows it does not own (no pre-zeroed buffers)."""
+    from focnerf_b200 import raymarching as rm
+    c = cases.composite_case(600, 5)
+    rays = c["rays"].copy()
+    assert np.all(np.diff(rays[:, 1]) >= 0)                        # ray-ordered slices: the fused op's contract
+    dev = "cuda"
+    sig = torch.from_numpy(c["sigmas"]).to(dev).requires_grad_(True)
+    rgb = torch.from_numpy(c["rgbs"]).to(dev).requires_grad_(True)
+    deltas, rays_t = torch.from_numpy(c["deltas"]).to(dev), torch.from_numpy(rays).to(dev)
+    N = rays.shape[0]
+    gt = torch.rand(N, 3, device=dev, generator=torch.Generator(device=dev).manual_seed(3))
+    for bg in (1.0, 0.3):
+        for t in (sig, rgb):
+            t.grad = None
+        ws, depth, image = rm.composite_rays_train(sig, rgb, deltas, rays_t)
+        loss_a = torch.nn.functional.mse_loss(image + (1 - ws).unsqueeze(-1) * bg, gt)
+        (loss_a * 1024.0).backward()
+        ga = (sig.grad.clone(), rgb.grad.clone())
+        for t in (sig, rgb):
+            t.grad = None
+        loss_b, image_b, ws_b, depth_b = rm.composite_rays_train_mse(sig, rgb, deltas, rays_t, gt, bg)
+        (loss_b * 1024.0).backward()
+        assert torch.allclose(loss_a, loss_b, rtol=1e-5, atol=1e-8), (float(loss_a), float(loss_b))
+        assert torch.equal(image, image_b) and torch.equal(ws, ws_b) and torch.equal(depth, depth_b)
+        for a, b in zip(ga, (sig.grad, rgb.grad)):
+            assert torch.isfinite(b).all()
+            assert torch.allclose(a, b, rtol=1e-4, atol=1e-6 * float(a.abs().max())), float((a - b).abs().max())
