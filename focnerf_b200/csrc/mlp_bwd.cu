@@ -58,16 +58,18 @@ struct BwdSmem {
     __host__ __device__ static uint32_t off_act(int l) { return l * kTileBytes; }
     __host__ __device__ static uint32_t off_x(int L) { return L * kTileBytes; }
     __host__ __device__ static uint32_t off_gz(int L) { return off_x(L) + ((kXBytes + 1023u) & ~1023u); }
-    __host__ __device__ static uint32_t off_wt_out(int L) { return off_gz(L) + kTileBytes; }
-    __host__ __device__ static uint32_t off_wt_h(int L, int i) { return off_wt_out(L) + 8192u + i * 8192u; }      // i = l-1
-    __host__ __device__ static uint32_t off_wt_in(int L) { return off_wt_h(L, L - 1); }
-    __host__ __device__ static uint32_t off_bars(int L) { return off_wt_in(L) + IN * 128u; }
+    // weights exactly as the forward kernel holds them (TMA, hardware swizzle): hidden matrices, then W_out, then W_in
+    __host__ __device__ static uint32_t off_w_h(int L, int i) { return off_gz(L) + kTileBytes + i * 8192u; }                  // W_{i+1} [64 o, 64 j]
+    __host__ __device__ static uint32_t off_w_out(int L) { return off_w_h(L, L - 1); }                                       // [16 o, 64 j], 2 KB
+    __host__ __device__ static uint32_t off_w_in(int L) { return off_w_out(L) + 2048u; }                                     // [64 o, IN i]
+    __host__ __device__ static uint32_t off_bars(int L) { return off_w_in(L) + ((kHidden * IN * 2u + 1023u) & ~1023u); }
     __host__ __device__ static uint32_t total(int L) { return off_bars(L) + 64 + 1024; }
 };
 
 template <int IN, int ACT>
 __global__ void __launch_bounds__(128)
-k_mlp_bwd(const __grid_constant__ CUtensorMap tm_fb, const __grid_constant__ CUtensorMap tm_in, BwdParams p) {
+k_mlp_bwd(const __grid_constant__ CUtensorMap tm_fb, const __grid_constant__ CUtensorMap tm_in, const __grid_constant__ CUtensorMap tm_win,
+          const __grid_constant__ CUtensorMap tm_w, BwdParams p) {
     using SM = BwdSmem<IN>;
     extern __shared__ uint8_t smem_raw[];
     uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~(uintptr_t)1023);
@@ -75,50 +77,36 @@ k_mlp_bwd(const __grid_constant__ CUtensorMap tm_fb, const __grid_constant__ CUt
     uint64_t* bars = reinterpret_cast<uint64_t*>(smem + SM::off_bars(L));
     uint64_t* bar_ld = bars;
     uint64_t* bar_mma = bars + 1;
-    uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(bars + 2);
+    uint64_t* bar_w = bars + 2;
+    uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(bars + 3);
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
 
     if (threadIdx.x == 0) {
-        tma_prefetch_desc(&tm_fb); tma_prefetch_desc(&tm_in);
-        mbar_init(bar_ld, 1); mbar_init(bar_mma, 1);
+        tma_prefetch_desc(&tm_fb); tma_prefetch_desc(&tm_in); tma_prefetch_desc(&tm_win); tma_prefetch_desc(&tm_w);
+        mbar_init(bar_ld, 1); mbar_init(bar_mma, 1); mbar_init(bar_w, 1);
         fence_barrier_init();
     }
     if (warp == 0) tmem_alloc(tmem_slot, p.tmem_cols);
 
-    // ---- stage the TRANSPOSED weights once: B operand of dgrad is [N = fan-in j][K = fan-out o], K-major, SWIZZLE_128B
+    // ---- weights: fetched once per CTA by TMA in their stored [fan-out o][fan-in j] layout.  The dgrad products
+    // dA_{l-1}[rows, j] = dZ_l[rows, o] . W_l[o, j] read them as MN-major B operands (N = j contiguous, K = o: 16 rows per
+    // K step), the same way the weight-gradient MMAs read the activation tiles -- no transposed copies are staged.
     const size_t in_sz = (size_t)kHidden * IN, hh = (size_t)kHidden * kHidden;
-    {
-        const __half* W_out = p.weights + in_sz + (size_t)n_hmm * hh;            // [16, 64]
-        __half* dst = reinterpret_cast<__half*>(smem + SM::off_wt_out(L));
-        for (uint32_t idx = threadIdx.x; idx < kOutPad * kHidden; idx += blockDim.x) {
-            const uint32_t o = idx / kHidden, j = idx % kHidden;
-            dst[(sw128_off(j, o >> 3) >> 1) + (o & 7u)] = __ldg(W_out + idx);
-        }
-        for (int l = 1; l <= n_hmm; ++l) {
-            const __half* W = p.weights + in_sz + (size_t)(l - 1) * hh;          // W_l [64 o, 64 j]
-            __half* d = reinterpret_cast<__half*>(smem + SM::off_wt_h(L, l - 1));
-            for (uint32_t idx = threadIdx.x; idx < kHidden * kHidden; idx += blockDim.x) {
-                const uint32_t o = idx / kHidden, j = idx % kHidden;
-                d[(sw128_off(j, o >> 3) >> 1) + (o & 7u)] = __ldg(W + idx);
-            }
-        }
-        if (p.grad_inputs) {
-            __half* d = reinterpret_cast<__half*>(smem + SM::off_wt_in(L));      // [N = IN i][K = 64 o]
-            for (uint32_t idx = threadIdx.x; idx < kHidden * IN; idx += blockDim.x) {
-                const uint32_t o = idx / IN, i = idx % IN;
-                d[(sw128_off(i, o >> 3) >> 1) + (o & 7u)] = __ldg(p.weights + idx);
-            }
-        }
-    }
     fence_proxy_async_smem();
     tc_fence_before();
     __syncthreads();
     tc_fence_after();
     const uint32_t tmem = *tmem_slot;
+    if (threadIdx.x == 0 && blockIdx.x < p.num_tiles) {
+        mbar_expect_tx(bar_w, (uint32_t)(kHidden * IN * 2) + (uint32_t)n_hmm * 8192u + 2048u);
+        tma_load_2d(smem + SM::off_w_in(L), &tm_win, bar_w, 0, 0);
+        for (int r16 = 0; r16 < n_hmm * 4 + 1; ++r16)
+            tma_load_2d(smem + SM::off_w_h(L, 0) + r16 * 2048, &tm_w, bar_w, 0, r16 * 16);
+    }
 
     // TMEM columns: [0,64) dgrad D | dW_0 (IN) | dW_1..dW_{L-1} (64 each) | dW_L^T (16)
     const uint32_t col_dw0 = 64, col_dwh0 = 64 + IN, col_dwout = 64 + IN + 64 * (uint32_t)n_hmm;
-    constexpr uint32_t id_dgrad_h = umma_idesc_f16(128, 64, 0, 0), id_dgrad_in = umma_idesc_f16(128, IN, 0, 0);
+    constexpr uint32_t id_dgrad_h = umma_idesc_f16(128, 64, 0, 1), id_dgrad_in = umma_idesc_f16(128, IN, 0, 1);      // B MN-major
     constexpr uint32_t id_wg_h = umma_idesc_f16(64, 64, 1, 1), id_wg_in = umma_idesc_f16(64, IN, 1, 1), id_wg_out = umma_idesc_f16(64, 16, 1, 1);
     constexpr uint32_t kXSwz = IN == 32 ? SWZ_64B : SWZ_128B, kXSbo = IN == 32 ? 512u : 1024u, kXk16 = IN == 32 ? 1024u : 2048u;
     const uint32_t s_gz = smem_u32(smem + SM::off_gz(L));
@@ -144,10 +132,11 @@ k_mlp_bwd(const __grid_constant__ CUtensorMap tm_fb, const __grid_constant__ CUt
         tc_fence_before();
         __syncthreads();
         if (threadIdx.x == 0) {
+            if (acc_w == 0) mbar_wait(bar_w, 0);
             mbar_wait(bar_ld, ld_phase);
             tc_fence_after();
-            // dA_{L-1} = G . W_L  (K = 16)
-            umma_f16(tmem, umma_desc(s_gz, 16, 1024, SWZ_128B), umma_desc(smem_u32(smem + SM::off_wt_out(L)), 16, 1024, SWZ_128B), id_dgrad_h, 0);
+            // dA_{L-1} = G . W_L  (K = 16 outputs = the 16 rows of the W_out tile)
+            umma_f16(tmem, umma_desc(s_gz, 16, 1024, SWZ_128B), umma_desc(smem_u32(smem + SM::off_w_out(L)), 16, 1024, SWZ_128B), id_dgrad_h, 0);
             // dW_L^T [64 j, 16 o] += A_{L-1}^T . G  (K = 128 batch rows)
             const uint32_t s_a = smem_u32(smem + SM::off_act(L - 1));
             #pragma unroll
@@ -207,10 +196,10 @@ k_mlp_bwd(const __grid_constant__ CUtensorMap tm_fb, const __grid_constant__ CUt
                     for (int k = 0; k < kTile / 16; ++k)       // dW_l [64 o, 64 j] += dZ_l^T . A_{l-1}
                         umma_f16(tmem + col_dwh0 + 64u * (uint32_t)(l - 1), umma_desc(s_gz + k * 2048, 16, 1024, SWZ_128B),
                                  umma_desc(s_prev + k * 2048, 16, 1024, SWZ_128B), id_wg_h, acc_w | (k > 0));
-                    const uint32_t s_wt = smem_u32(smem + SM::off_wt_h(L, l - 1));
+                    const uint32_t s_w = smem_u32(smem + SM::off_w_h(L, l - 1));
                     #pragma unroll
-                    for (int k = 0; k < kHidden / 16; ++k)     // dA_{l-1} = dZ_l . W_l
-                        umma_f16(tmem, umma_desc(s_gz + k * 32, 16, 1024, SWZ_128B), umma_desc(s_wt + k * 32, 16, 1024, SWZ_128B), id_dgrad_h, k > 0);
+                    for (int k = 0; k < kHidden / 16; ++k)     // dA_{l-1} = dZ_l . W_l   (K step = 16 rows o of the W_l tile)
+                        umma_f16(tmem, umma_desc(s_gz + k * 32, 16, 1024, SWZ_128B), umma_desc(s_w + k * 2048, 16, 1024, SWZ_128B), id_dgrad_h, k > 0);
                 } else {
                     const uint32_t s_x = smem_u32(smem + SM::off_x(L));
                     #pragma unroll
@@ -218,10 +207,10 @@ k_mlp_bwd(const __grid_constant__ CUtensorMap tm_fb, const __grid_constant__ CUt
                         umma_f16(tmem + col_dw0, umma_desc(s_gz + k * 2048, 16, 1024, SWZ_128B), umma_desc(s_x + k * kXk16, 16, kXSbo, kXSwz),
                                  id_wg_in, acc_w | (k > 0));
                     if (p.grad_inputs) {
-                        const uint32_t s_wt = smem_u32(smem + SM::off_wt_in(L));
+                        const uint32_t s_w = smem_u32(smem + SM::off_w_in(L));
                         #pragma unroll
-                        for (int k = 0; k < kHidden / 16; ++k) // dX = dZ_0 . W_0
-                            umma_f16(tmem, umma_desc(s_gz + k * 32, 16, 1024, SWZ_128B), umma_desc(s_wt + k * 32, 16, 1024, SWZ_128B), id_dgrad_in, k > 0);
+                        for (int k = 0; k < kHidden / 16; ++k) // dX = dZ_0 . W_0   (W_0 tile rows are IN*2 bytes: same form as the X tile)
+                            umma_f16(tmem, umma_desc(s_gz + k * 32, 16, 1024, SWZ_128B), umma_desc(s_w + k * kXk16, 16, kXSbo, kXSwz), id_dgrad_in, k > 0);
                     }
                 }
                 umma_commit(bar_mma);
@@ -338,10 +327,14 @@ int launch_bwd(const uint16_t* grad, const uint16_t* inputs, const uint16_t* wei
                uint32_t num_layers, uint32_t activation, int calc_grad_inputs, uint16_t* backward_buffer, uint16_t* grad_inputs,
                uint16_t* grad_weights, void* scratch, cudaStream_t st) {
     using SM = BwdSmem<IN>;
-    CUtensorMap tm_fb, tm_in;
+    CUtensorMap tm_fb, tm_in, tm_win, tm_w;
     int rc = make_tmap_f16_2d(&tm_fb, forward_buffer, (uint64_t)num_layers * B, kHidden, kTile, kHidden);
     if (rc) return rc;
     rc = make_tmap_f16_2d(&tm_in, inputs, B, IN, kTile, IN);
+    if (rc) return rc;
+    rc = make_tmap_f16_2d(&tm_win, weights, kHidden, IN, kHidden, IN);
+    if (rc) return rc;
+    rc = make_tmap_f16_2d(&tm_w, weights + (size_t)kHidden * IN, (uint64_t)(num_layers - 1) * kHidden + kOutPad, kHidden, 16, kHidden);
     if (rc) return rc;
     const uint32_t smem = SM::total((int)num_layers);
     if (smem > 227 * 1024) return FOC_ERR_UNSUPPORTED;
@@ -363,7 +356,7 @@ int launch_bwd(const uint16_t* grad, const uint16_t* inputs, const uint16_t* wei
     p.tmem_cols = need <= 128 ? 128 : need <= 256 ? 256 : 512;
     if (need > 512) return FOC_ERR_UNSUPPORTED;
     const uint32_t grid = bwd_grid(B);
-    k_mlp_bwd<IN, ACT><<<grid, 128, smem, st>>>(tm_fb, tm_in, p);
+    k_mlp_bwd<IN, ACT><<<grid, 128, smem, st>>>(tm_fb, tm_in, tm_win, tm_w, p);
     FOC_LAUNCH_CHECK();
     k_mlp_wgrad_finish<<<ceil_div(p.num_params, 32), 256, 0, st>>>(p.partials, grid, p.num_params, reinterpret_cast<__half*>(grad_weights));
     FOC_LAUNCH_CHECK(); return 0;
