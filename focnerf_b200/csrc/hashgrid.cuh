@@ -21,25 +21,53 @@ template <> struct Elem<__half> {
     static __device__ __forceinline__ float acc(float res, float w, float g) { return rnd(__fadd_rn(res, rnd(__fmul_rn(w, g)))); }
 };
 
-// gridencoder.cu:50-84: dense index while the running stride still fits the level, else xor-of-primes hash.
+// gridencoder.cu:50-84: dense index while the running stride still fits the level, else xor-of-primes hash, then
+// `% hashmap_size`.  Everything that does not depend on the corner is resolved ONCE per (thread, level): which dims enter
+// the dense index, whether the level is hashed, and whether the final modulo is the identity (dense level: index <
+// (res+1)^D <= size), a mask (power-of-two table, the 2^19 of every hashed level here) or a real division (tiled grids,
+// odd sizes).  The per-corner cost drops from ~45 instructions (a 32-bit division each) to ~8; the indices are identical.
 template <int D>
-__device__ __forceinline__ uint32_t grid_index(uint32_t gridtype, bool align_corners, uint32_t hashmap_size,
-                                               uint32_t resolution, const uint32_t (&pg)[D]) {
-    constexpr uint32_t primes[7] = {1u, 2654435761u, 805459861u, 3674653429u, 2097192037u, 1434869437u, 2165219737u};
-    uint32_t stride = 1, index = 0;
-    #pragma unroll
-    for (int d = 0; d < D; ++d) {
-        if (stride <= hashmap_size) {
-            index += pg[d] * stride;
-            stride *= align_corners ? resolution : (resolution + 1);
-        }
-    }
-    if (gridtype == 0 && stride > hashmap_size) {
-        index = 0;
+struct GridIndexer {
+    uint32_t st[D];          // stride of dim d in the dense index, 0 when the reference's loop skips the dim
+    uint32_t size, and_mask;
+    bool hashed, need_mod;
+    __device__ __forceinline__ GridIndexer(uint32_t gridtype, bool align_corners, uint32_t hashmap_size, uint32_t resolution) {
+        uint32_t stride = 1;
+        bool wrapped = false;                   // the reference's 32-bit stride product may wrap at very fine levels
         #pragma unroll
-        for (int d = 0; d < D; ++d) index ^= pg[d] * primes[d];
+        for (int d = 0; d < D; ++d) {
+            if (stride <= hashmap_size) {
+                st[d] = stride;
+                const uint64_t wide = (uint64_t)stride * (align_corners ? resolution : (resolution + 1));
+                wrapped |= (wide >> 32) != 0;
+                stride = (uint32_t)wide;
+            } else st[d] = 0;
+        }
+        size = hashmap_size;
+        const bool pow2 = (hashmap_size & (hashmap_size - 1)) == 0;
+        hashed = gridtype == 0 && stride > hashmap_size;
+        // the final `% size`: identity for a dense level (index < (res+1)^D <= size, unless the product wrapped), a mask
+        // for a power-of-two hash table, a division otherwise
+        need_mod = hashed ? !pow2 : !(stride <= hashmap_size && !wrapped);
+        and_mask = (hashed && pow2) ? hashmap_size - 1 : 0xffffffffu;
     }
-    return index % hashmap_size;
+    // branch-free in the common configurations (lanes of a warp sit on different levels under the sample-major mapping)
+    __device__ __forceinline__ uint32_t operator()(const uint32_t (&pg)[D]) const {
+        constexpr uint32_t primes[7] = {1u, 2654435761u, 805459861u, 3674653429u, 2097192037u, 1434869437u, 2165219737u};
+        uint32_t h = 0, dense = 0;
+        #pragma unroll
+        for (int d = 0; d < D; ++d) { h ^= pg[d] * primes[d]; dense += pg[d] * st[d]; }
+        uint32_t index = hashed ? h : dense;
+        if (need_mod) index %= size; else index &= and_mask;
+        return index;
+    }
+};
+
+// t -> (t / L, t % L) without a 64-bit division in the common cases (L a power of two; t < 2^32)
+__device__ __forceinline__ void split_index(uint64_t t, uint32_t L, uint32_t& q, uint32_t& r) {
+    if ((L & (L - 1)) == 0) { q = (uint32_t)(t >> (__ffs((int)L) - 1)); r = (uint32_t)t & (L - 1); }
+    else if ((t >> 32) == 0) { const uint32_t t32 = (uint32_t)t; q = t32 / L; r = t32 - q * L; }
+    else { q = (uint32_t)(t / L); r = (uint32_t)(t % L); }
 }
 
 struct GridLevel {

@@ -75,7 +75,9 @@ k_grid_bwd_scatter(const T* __restrict__ grad, const float* __restrict__ inputs,
                    uint32_t interp, uint32_t level0, uint32_t nl) {
     const uint64_t t = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x;
     if (t >= (uint64_t)B * nl) return;
-    const uint32_t b = (uint32_t)(t / nl), level = level0 + (uint32_t)(t % nl);
+    uint32_t b, level;
+    split_index(t, nl, b, level);
+    level += level0;
     const T* gp = LAYOUT == 0 ? grad + ((size_t)level * B + b) * C : grad + ((size_t)b * L + level) * C;
     float g[C];
     bool any = false;
@@ -90,6 +92,7 @@ k_grid_bwd_scatter(const T* __restrict__ grad, const float* __restrict__ inputs,
     for (int d = 0; d < D; ++d) x[d] = __ldg(inputs + (size_t)b * D + d);
     if (grid_oob<D>(x)) return;                                                   // gridencoder.cu:276-281
     const GridLevel lv = grid_level(offsets, level, S, H);
+    const GridIndexer<D> gidx(gridtype, align_corners, lv.hashmap_size, lv.resolution);
     T* tab = grad_table + (size_t)lv.offset * C;
     float pos[D], pder[D];
     uint32_t pg[D];
@@ -103,7 +106,7 @@ k_grid_bwd_scatter(const T* __restrict__ grad, const float* __restrict__ inputs,
             if ((idx >> d) & 1) { wt = __fmul_rn(wt, pos[d]); pl[d] = pg[d] + 1; }
             else { wt = __fmul_rn(wt, __fsub_rn(1.0f, pos[d])); pl[d] = pg[d]; }
         }
-        const uint32_t row = grid_index<D>(gridtype, align_corners, lv.hashmap_size, lv.resolution, pl);
+        const uint32_t row = gidx(pl);
         float v[C];
         #pragma unroll
         for (int c = 0; c < C; ++c) v[c] = __fmul_rn(wt, g[c]);
@@ -127,6 +130,7 @@ k_grid_bwd_runs(const T* __restrict__ grad, const float* __restrict__ inputs, co
     const uint32_t b0 = (blockIdx.x * blockDim.x + threadIdx.x) * (uint32_t)kRun;
     if (b0 >= B) return;
     const GridLevel lv = grid_level(offsets, level, S, H);
+    const GridIndexer<D> gidx(gridtype, align_corners, lv.hashmap_size, lv.resolution);
     T* tab = grad_table + (size_t)lv.offset * C;
     float acc[1 << D][C];
     uint32_t cur[D];
@@ -137,7 +141,7 @@ k_grid_bwd_runs(const T* __restrict__ grad, const float* __restrict__ inputs, co
             uint32_t pl[D];
             #pragma unroll
             for (int d = 0; d < D; ++d) pl[d] = cur[d] + ((idx >> d) & 1);
-            const uint32_t row = grid_index<D>(gridtype, align_corners, lv.hashmap_size, lv.resolution, pl);
+            const uint32_t row = gidx(pl);
             red_row<T, C>(tab + (size_t)row * C, acc[idx]);
         }
     };
@@ -218,11 +222,12 @@ k_grad_tv(const float* __restrict__ inputs, const float* __restrict__ table, flo
     for (int d = 0; d < D; ++d) x[d] = __ldg(inputs + (size_t)b * D + d);
     if (grid_oob<D>(x)) return;
     const GridLevel lv = grid_level(offsets, level, S, H);
+    const GridIndexer<D> gidx(gridtype, align_corners, lv.hashmap_size, lv.resolution);
     const float* tab = table + (size_t)lv.offset * C;
     uint32_t pg[D];
     #pragma unroll
     for (int d = 0; d < D; ++d) pg[d] = (uint32_t)floorf(fmaf(x[d], lv.scale, align_corners ? 0.0f : 0.5f));
-    const uint32_t row0 = grid_index<D>(gridtype, align_corners, lv.hashmap_size, lv.resolution, pg);
+    const uint32_t row0 = gidx(pg);
     float c0[C], res[C], idelta[C];
     #pragma unroll
     for (int c = 0; c < C; ++c) { c0[c] = __ldg(tab + (size_t)row0 * C + c); res[c] = 0.f; idelta[c] = 0.f; }
@@ -232,13 +237,13 @@ k_grad_tv(const float* __restrict__ inputs, const float* __restrict__ table, flo
         const uint32_t cur = pg[d];
         if (cur < lv.resolution) {
             pg[d] = cur + 1;
-            const uint32_t r = grid_index<D>(gridtype, align_corners, lv.hashmap_size, lv.resolution, pg);
+            const uint32_t r = gidx(pg);
             #pragma unroll
             for (int c = 0; c < C; ++c) { const float gdiff = c0[c] - __ldg(tab + (size_t)r * C + c); res[c] += gdiff; idelta[c] = fmaf(gdiff, gdiff, idelta[c]); }
         }
         if (cur > 0) {
             pg[d] = cur - 1;
-            const uint32_t r = grid_index<D>(gridtype, align_corners, lv.hashmap_size, lv.resolution, pg);
+            const uint32_t r = gidx(pg);
             #pragma unroll
             for (int c = 0; c < C; ++c) { const float gdiff = c0[c] - __ldg(tab + (size_t)r * C + c); res[c] += gdiff; idelta[c] = fmaf(gdiff, gdiff, idelta[c]); }
         }

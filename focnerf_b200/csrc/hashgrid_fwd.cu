@@ -60,7 +60,7 @@ k_grid_fwd(const float* __restrict__ inputs, const T* __restrict__ table, const 
     else {
         const uint64_t t = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x;
         if (t >= (uint64_t)B * L) return;
-        b = (uint32_t)(t / L); level = (uint32_t)(t % L);
+        split_index(t, L, b, level);
     }
     T* out = LAYOUT == 0 ? outputs + ((size_t)level * B + b) * C : outputs + ((size_t)b * L + level) * C;
     T* dyo = dy_dx ? dy_dx + (((size_t)b * L + level) * D) * C : nullptr;       // [B, L, D, C]
@@ -77,6 +77,7 @@ k_grid_fwd(const float* __restrict__ inputs, const T* __restrict__ table, const 
         return;
     }
     const GridLevel lv = grid_level(offsets, level, S, H);
+    const GridIndexer<D> gidx(gridtype, align_corners, lv.hashmap_size, lv.resolution);
     const T* tab = table + (size_t)lv.offset * C;
     float pos[D], pder[D];
     uint32_t pg[D];
@@ -94,7 +95,7 @@ k_grid_fwd(const float* __restrict__ inputs, const T* __restrict__ table, const 
             else { wt = __fmul_rn(wt, __fsub_rn(1.0f, pos[d])); pl[d] = pg[d]; }
         }
         w[idx] = wt;
-        RowVec<T, C>::ld(tab + (size_t)grid_index<D>(gridtype, align_corners, lv.hashmap_size, lv.resolution, pl) * C, rows[idx]);
+        RowVec<T, C>::ld(tab + (size_t)gidx(pl) * C, rows[idx]);
     }
     float res[C];
     #pragma unroll
@@ -125,9 +126,9 @@ k_grid_fwd(const float* __restrict__ inputs, const T* __restrict__ table, const 
             }
             float left[C], right[C];
             pl[gd] = pg[gd];
-            RowVec<T, C>::ld(tab + (size_t)grid_index<D>(gridtype, align_corners, lv.hashmap_size, lv.resolution, pl) * C, left);
+            RowVec<T, C>::ld(tab + (size_t)gidx(pl) * C, left);
             pl[gd] = pg[gd] + 1;
-            RowVec<T, C>::ld(tab + (size_t)grid_index<D>(gridtype, align_corners, lv.hashmap_size, lv.resolution, pl) * C, right);
+            RowVec<T, C>::ld(tab + (size_t)gidx(pl) * C, right);
             #pragma unroll
             for (int c = 0; c < C; ++c) {
                 if constexpr (sizeof(T) == 2) {
