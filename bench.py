@@ -248,6 +248,21 @@ def run_ours(args):
 
     render = render_bench(tr.render, dev, rank, world, frames=args.frames) if args.frames > 0 else None
 
+    # density-grid refresh (update_extra_state, every 16 steps in the reference's loop): timed on a copy of the state, after
+    # everything else, because it replaces the analytic bitfield the timed steps marched through
+    def time_refresh(full):
+        tr.iter_density = 0 if full else 16
+        tr.update_extra_state()
+        torch.cuda.synchronize()
+        t = time.perf_counter()
+        for _ in range(3):
+            tr.iter_density = 0 if full else 16
+            tr.update_extra_state()
+        torch.cuda.synchronize()
+        return (time.perf_counter() - t) / 3 * 1e3
+    refresh = {"full_ms": time_refresh(True), "partial_ms": time_refresh(False),
+               "note": "one update_extra_state call (128^3 cells x cascade full; 2 x 128^3/4 cells partial), host wall clock; not part of `value`"}
+
     def shutdown():
         """Captured graphs hold NCCL work: drop them before the communicator goes, and never let teardown hang the job."""
         if world == 1:
@@ -298,7 +313,7 @@ def run_ours(args):
         "e2e": {"value": total_rays / (ms_e2e * 1e-3), "unit": "rays/s", "ms_per_step": ms_e2e / args.steps,
                 "h2d_bytes_per_step": world * RAYS_PER_GPU * 9 * 4, "d2h_bytes_per_step": world * 4},
         "gpu_launches": int(round(kt.kernel_launches() / n_prof * args.steps)),
-        "render": render,
+        "render": render, "density_refresh": refresh,
         "roofline": roof,
     }
     if world == 1:

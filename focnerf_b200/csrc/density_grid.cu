@@ -1,0 +1,114 @@
+// density_grid.cu -- the density-grid refresh that feeds the marcher's bitfield.
+//
+// Reference: NeRFRenderer.update_extra_state, legacy/nerf/renderer.py:445-531 -- Python loops over 128^3 cells in S^3 blocks
+// x cascades (meshgrid, morton3D, jitter, density(), scatter into tmp_grid), then a masked EMA-max, `.item()` of the mean
+// and packbits with a host threshold.  Here the cells are generated directly in Morton order on the device, and the
+// EMA-max, the mean and the thresholding stay on the device (no host read of the mean):
+//   k_cell_positions : cell index (Morton) -> jittered sample position of that cell in its cascade     (l.470-479, 503-509)
+//   k_grid_ema       : grid = max(grid * decay, tmp) where both are valid (>= 0); per-CTA sums of max(grid, 0)  (l.522-524)
+//   k_grid_mean      : fixed-order sum of the per-CTA partials -> mean                                    (l.524)
+//   k_packbits_dev   : bit = grid > min(mean, density_thresh), threshold read from device memory          (l.529-530)
+#include "common.cuh"
+
+using namespace foc;
+
+namespace {
+
+constexpr int kEmaThreads = 256, kEmaPerThread = 8;
+
+// indices == nullptr: cell i of the cascade IS Morton index i (full update); else indices[i] (partial update)
+__global__ void __launch_bounds__(256)
+k_cell_positions(const int32_t* __restrict__ indices, uint32_t n, uint32_t H, float bound_c, const float* __restrict__ noise,
+                 float* __restrict__ xyzs) {
+    const uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= n) return;
+    const uint32_t m = indices ? (uint32_t)__ldg(indices + i) : i;
+    const uint32_t c[3] = {compact3(m), compact3(m >> 1), compact3(m >> 2)};
+    const float hgs = bound_c / (float)H;                              // half a cell (renderer.py:475)
+    #pragma unroll
+    for (int d = 0; d < 3; ++d) {
+        const float u = 2.0f * (float)c[d] / (float)(H - 1) - 1.0f;    // [-1, 1]
+        xyzs[3 * (size_t)i + d] = u * (bound_c - hgs) + (__ldg(noise + 3 * (size_t)i + d) * 2.0f - 1.0f) * hgs;
+    }
+}
+
+// tmp values are scattered to tmp_grid[indices] by the caller (or are the full grid when indices == nullptr)
+__global__ void __launch_bounds__(kEmaThreads)
+k_grid_ema(float* __restrict__ grid, const float* __restrict__ tmp, uint32_t n, float decay, float* __restrict__ partial) {
+    __shared__ float s[kEmaThreads / 32];
+    float acc = 0.f;
+    const uint32_t base = blockIdx.x * (kEmaThreads * kEmaPerThread);
+    #pragma unroll
+    for (int k = 0; k < kEmaPerThread; ++k) {
+        const uint32_t i = base + k * kEmaThreads + threadIdx.x;
+        if (i < n) {
+            float g = grid[i];
+            const float t = __ldg(tmp + i);
+            if (g >= 0.f && t >= 0.f) { g = fmaxf(g * decay, t); grid[i] = g; }
+            acc += fmaxf(g, 0.f);                                      // -1 regions count as zero density (l.524)
+        }
+    }
+    acc = warp_sum(acc);
+    if ((threadIdx.x & 31) == 0) s[threadIdx.x >> 5] = acc;
+    __syncthreads();
+    if (threadIdx.x == 0) {
+        float t = 0.f;
+        #pragma unroll
+        for (int w = 0; w < kEmaThreads / 32; ++w) t += s[w];
+        partial[blockIdx.x] = t;
+    }
+}
+
+__global__ void __launch_bounds__(1024) k_grid_mean(const float* __restrict__ partial, uint32_t n_partial, uint32_t n, float* __restrict__ mean) {
+    __shared__ float s[32];
+    float acc = 0.f;
+    for (uint32_t i = threadIdx.x; i < n_partial; i += 1024) acc += __ldg(partial + i);
+    acc = warp_sum(acc);
+    if ((threadIdx.x & 31) == 0) s[threadIdx.x >> 5] = acc;
+    __syncthreads();
+    if (threadIdx.x < 32) {
+        const float t = warp_sum(s[threadIdx.x]);
+        if (threadIdx.x == 0) mean[0] = t / (float)n;
+    }
+}
+
+__global__ void __launch_bounds__(256)
+k_packbits_dev(const float* __restrict__ grid, uint32_t N, const float* __restrict__ mean, float density_thresh, uint8_t* __restrict__ bitfield) {
+    const uint32_t n = blockIdx.x * blockDim.x + threadIdx.x;
+    if (n >= N) return;
+    const float thresh = fminf(__ldg(mean), density_thresh);
+    const float4 a = __ldg(reinterpret_cast<const float4*>(grid) + (size_t)n * 2), b = __ldg(reinterpret_cast<const float4*>(grid) + (size_t)n * 2 + 1);
+    bitfield[n] = (uint8_t)((a.x > thresh) | (a.y > thresh) << 1 | (a.z > thresh) << 2 | (a.w > thresh) << 3 |
+                            (b.x > thresh) << 4 | (b.y > thresh) << 5 | (b.z > thresh) << 6 | (b.w > thresh) << 7);
+}
+
+}  // namespace
+
+static inline cudaStream_t S(void* s) { return reinterpret_cast<cudaStream_t>(s); }
+
+FOC_API int foc_density_cell_positions(const int32_t* indices, uint32_t n, uint32_t H, float bound_c, const float* noise, float* xyzs,
+                                       void* stream) {
+    if (n == 0) return 0;
+    if (H < 2 || H > 1024) return FOC_ERR_UNSUPPORTED;
+    k_cell_positions<<<ceil_div(n, 256), 256, 0, S(stream)>>>(indices, n, H, bound_c, noise, xyzs);
+    FOC_LAUNCH_CHECK(); return 0;
+}
+
+FOC_API size_t foc_density_grid_update_scratch_bytes(uint32_t n) {
+    return (size_t)ceil_div(n, (uint32_t)(kEmaThreads * kEmaPerThread)) * sizeof(float);
+}
+
+// grid [n] (all cascades), tmp [n] (-1 where not sampled); writes mean[0] and bitfield [n / 8]
+FOC_API int foc_density_grid_update(float* grid, const float* tmp, uint32_t n, float decay, float density_thresh, float* mean,
+                                    uint8_t* bitfield, void* scratch, void* stream) {
+    if (n == 0) return 0;
+    if (n % 8 != 0 || (reinterpret_cast<uintptr_t>(grid) & 15u)) return FOC_ERR_UNSUPPORTED;
+    const uint32_t blocks = ceil_div(n, (uint32_t)(kEmaThreads * kEmaPerThread));
+    float* partial = static_cast<float*>(scratch);
+    k_grid_ema<<<blocks, kEmaThreads, 0, S(stream)>>>(grid, tmp, n, decay, partial);
+    FOC_LAUNCH_CHECK();
+    k_grid_mean<<<1, 1024, 0, S(stream)>>>(partial, blocks, n, mean);
+    FOC_LAUNCH_CHECK();
+    k_packbits_dev<<<ceil_div(n / 8, 256), 256, 0, S(stream)>>>(grid, n / 8, mean, density_thresh, bitfield);
+    FOC_LAUNCH_CHECK(); return 0;
+}

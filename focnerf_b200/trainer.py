@@ -25,6 +25,9 @@ class Trainer:
         self.model = NeRFNetwork(bound=bound).to(self.device)
         self.aabb = torch.tensor([-bound, -bound, -bound, bound, bound, bound], dtype=torch.float32, device=self.device)
         self.density_bitfield = torch.zeros(self.cascade * grid_size ** 3 // 8, dtype=torch.uint8, device=self.device)
+        self.density_grid = torch.zeros(self.cascade, grid_size ** 3, dtype=torch.float32, device=self.device)   # renderer.py:88-89
+        self.mean_density = torch.zeros(1, dtype=torch.float32, device=self.device)      # stays on the device
+        self.density_thresh, self.density_scale, self.iter_density = float(density_thresh), 1.0, 0
         if density_grid is not None:
             self.set_density_grid(density_grid, density_thresh)
         self.step_counter = torch.zeros(16, 2, dtype=torch.int32, device=self.device)     # renderer.py:96-98
@@ -50,8 +53,51 @@ class Trainer:
     def set_density_grid(self, density_grid, density_thresh=10.0):
         """density_grid [cascade, H^3] (Morton order) -> bitfield, as update_extra_state does (renderer.py:529-531)."""
         g = density_grid.to(self.device, torch.float32).contiguous()
+        self.density_grid.copy_(g.view_as(self.density_grid))
         thresh = min(float(g.clamp(min=0).mean()), density_thresh)
         raymarching.packbits(g, thresh, self.density_bitfield)
+
+    @torch.no_grad()
+    def update_extra_state(self, decay=0.95):
+        """NeRFRenderer.update_extra_state (legacy/nerf/renderer.py:445-536): re-sample the field's density at jittered cell
+        positions (every cell for the first 16 calls, then H^3/4 random + H^3/4 occupied cells per cascade), EMA-max into
+        the density grid, threshold at min(mean, density_thresh) into the bitfield the marcher reads.  Cells are generated in
+        Morton order on the device (no meshgrid loops) and the mean / threshold never visit the host (csrc/density_grid.cu);
+        the one host read left is torch.nonzero of the partial update, as in the reference (l.495)."""
+        from ._lib import check, lib, ptr, stream
+        H, n, dev = self.grid_size, self.grid_size ** 3, self.device
+        tmp = torch.full_like(self.density_grid, -1.0)
+        was_training = self.model.training
+        self.model.eval()
+        for cas in range(self.cascade):
+            bound_c = float(min(2 ** cas, self.bound))
+            if self.iter_density < 16:
+                indices, m = None, n
+            else:
+                m = n // 4
+                coords = torch.randint(0, H, (m, 3), device=dev)
+                idx_rand = raymarching.morton3D(coords).long()
+                occ = torch.nonzero(self.density_grid[cas] > 0).squeeze(-1)
+                if occ.numel() > 0:
+                    occ = occ[torch.randint(0, occ.shape[0], [m], dtype=torch.long, device=dev)]
+                    idx_rand = torch.cat([idx_rand, occ], 0)
+                indices, m = idx_rand.int().contiguous(), idx_rand.shape[0]
+            noise = torch.rand(m, 3, device=dev)
+            xyzs = torch.empty(m, 3, dtype=torch.float32, device=dev)
+            check(lib().foc_density_cell_positions(ptr(indices), m, H, bound_c, ptr(noise), ptr(xyzs), stream()), "density_cell_positions")
+            with torch.autocast("cuda", dtype=torch.float16, enabled=self.fp16):
+                sig = self.model.density(xyzs)["sigma"].reshape(-1).float() * self.density_scale
+            if indices is None:
+                tmp[cas] = sig
+            else:
+                tmp[cas, indices.long()] = sig
+        total = self.cascade * n
+        scratch = torch.empty(max(4, lib().foc_density_grid_update_scratch_bytes(total)), dtype=torch.uint8, device=dev)
+        check(lib().foc_density_grid_update(ptr(self.density_grid), ptr(tmp), total, decay, self.density_thresh, ptr(self.mean_density),
+                                            ptr(self.density_bitfield), ptr(scratch), stream()), "density_grid_update")
+        self.iter_density += 1
+        self.model.train(was_training)
+        self.update_mean_count()
 
     # ------------------------------------------------------------------------------------------------ training
     def render_train(self, rays_o, rays_d, bg_color=1.0, perturb=True, force_all_rays=False, counter=None, mean_count=None):

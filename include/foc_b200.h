@@ -175,6 +175,18 @@ int foc_rgb_sigmoid_backward(const float *grad_rgb, const float *rgb, uint32_t B
  * from the reference tree: closed form, parity unpinned).  dirs [B,3] -> outputs [B, degree^2] f32. */
 int foc_sh_encode_forward(const float *dirs, uint32_t B, uint32_t degree, float *outputs, void *stream);
 
+/* ---------------------------------------------------------------- density-grid refresh
+ * NeRFRenderer.update_extra_state, legacy/nerf/renderer.py:445-531, without its Python cell loops and host reads.
+ * cell_positions: Morton cell index i (or indices[i]) of an H^3 cascade with half-extent bound_c -> jittered position
+ *                 xyz = (2 c / (H-1) - 1) (bound_c - hgs) + (2 noise - 1) hgs, hgs = bound_c / H (l.470-479); noise [n,3] in [0,1).
+ * grid_update   : grid = max(grid * decay, tmp) where grid >= 0 and tmp >= 0 (l.522-523); mean[0] = mean(max(grid, 0));
+ *                 bitfield = packbits(grid, min(mean, density_thresh)) with the threshold read on the device (l.524-530). */
+int foc_density_cell_positions(const int32_t *indices, uint32_t n, uint32_t H, float bound_c, const float *noise, float *xyzs,
+                               void *stream);
+size_t foc_density_grid_update_scratch_bytes(uint32_t n);
+int foc_density_grid_update(float *grid, const float *tmp, uint32_t n, float decay, float density_thresh, float *mean,
+                            uint8_t *bitfield, void *scratch, void *stream);
+
 /* ---------------------------------------------------------------- loss head fused into the training compositor
  * (no reference kernel: legacy/nerf/renderer.py:313-316 + nerf/utils.py:535-545 as ~14 elementwise / reduction launches)
  * forward : composite_rays_train_forward, plus pred = image + (1 - weights_sum) * bg, err[ray] = sum_c (pred_c - gt_c)^2 and

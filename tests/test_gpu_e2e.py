@@ -114,3 +114,50 @@ def test_graph_step_trains_and_tracks_counter():
     tr.mean_count = max(captured) + 3 * Trainer.GRAPH_QUANTUM
     tr.train_step(o, d, gt)
     assert tr._graph[0][0] > max(captured)
+
+
+def test_update_extra_state_matches_reference_logic():
+    """Density-grid refresh on the device (csrc/density_grid.cu) == the reference's steps (legacy/nerf/renderer.py:445-531)
+    restated with torch ops on the same jittered positions: masked EMA-max, mean with -1 regions as 0, packbits at
+    min(mean, density_thresh)."""
+    from focnerf_b200 import raymarching as rm
+    from focnerf_b200._lib import check, lib, ptr, stream
+    scene, tr = _trainer()
+    for it in range(20):                                            # a little training so the field is not flat
+        o, d = cases.camera_rays(4096, 500 + it)
+        o, d = torch.from_numpy(o).cuda(), torch.from_numpy(d).cuda()
+        tr.train_step(o, d, scene.render_gt(o, d))
+    H, n = tr.grid_size, tr.grid_size ** 3
+    # cell positions: kernel vs the reference formula through morton3D_invert
+    idx = torch.arange(n, dtype=torch.int32, device="cuda")
+    noise = torch.rand(n, 3, device="cuda")
+    xyz = torch.empty(n, 3, device="cuda")
+    check(lib().foc_density_cell_positions(None, n, H, 1.0, ptr(noise), ptr(xyz), stream()), "cell_positions")
+    coords = rm.morton3D_invert(idx).float()
+    hgs = 1.0 / H
+    want = (2 * coords / (H - 1) - 1) * (1.0 - hgs) + (noise * 2 - 1) * hgs
+    assert torch.allclose(xyz, want, atol=1e-6)
+    # one full update against the torch restatement, same RNG stream
+    grid0 = tr.density_grid.clone()
+    grid0[0, ::7] = -1.0                                             # some untrained (-1) cells must stay untouched
+    tr.density_grid.copy_(grid0)
+    torch.manual_seed(77)
+    tr.update_extra_state(decay=0.95)
+    torch.manual_seed(77)
+    noise = torch.rand(n, 3, device="cuda")
+    check(lib().foc_density_cell_positions(None, n, H, 1.0, ptr(noise), ptr(xyz), stream()), "cell_positions")
+    tr.model.eval()
+    with torch.no_grad(), torch.autocast("cuda", dtype=torch.float16):
+        tmp = tr.model.density(xyz)["sigma"].reshape(1, -1).float()
+    valid = (grid0 >= 0) & (tmp >= 0)
+    want_grid = torch.where(valid, torch.maximum(grid0 * 0.95, tmp), grid0)
+    assert torch.equal(tr.density_grid, want_grid)
+    mean = float(want_grid.clamp(min=0).mean())
+    assert abs(float(tr.mean_density) - mean) <= 1e-5 * max(mean, 1e-6)
+    want_bits = rm.packbits(want_grid, min(mean, tr.density_thresh))
+    differing = int((want_bits ^ tr.density_bitfield).to(torch.int32).ne(0).sum())
+    assert differing <= 2                                            # cells within float rounding of the mean threshold
+    # partial updates run and keep the grid consistent
+    tr.iter_density = 16
+    tr.update_extra_state()
+    assert torch.isfinite(tr.density_grid).all() and int(tr.density_bitfield.count_nonzero()) > 0
