@@ -117,6 +117,25 @@ def cpu_baseline(scene, bits, cascade, rays=1024):
             "sample": f"1 train step (fwd+bwd+Adam) on {rays} rays of the same scene, oracle C port with OpenMP, {dt:.1f} s"}
 
 
+def psnr_run(make_trainer, scene, dev, steps, pool_dev):
+    """Fixed-iteration quality check (north_star: PSNR within 0.1 dB of the reference): a FRESH trainer, `steps` train steps
+    over the same batch pool, then PSNR of the inference render against the analytic ground truth on 32768 held-out rays."""
+    import cases
+    import torch
+    tr = make_trainer()
+    for i in range(steps):
+        tr.train_step(*pool_dev[i % len(pool_dev)])
+        if tr.local_step % 16 == 0:
+            tr.update_mean_count()
+    o, d = cases.camera_rays(32768, 424242)
+    o, d = torch.from_numpy(o).to(dev), torch.from_numpy(d).to(dev)
+    gt = scene.render_gt(o, d)
+    image = tr.render(o, d)[0]
+    mse = float(torch.mean((image.float() - gt) ** 2).item())
+    return {"psnr_db": -10.0 * math.log10(max(mse, 1e-12)), "steps": steps, "eval_rays": 32768,
+            "note": "fresh model, fixed number of steps on the benchmark's batch pool, held-out rays of the synthetic scene"}
+
+
 def render_bench(render_fn, dev, rank, world, frames=3, H=800, W=800):
     """configs[2]: 800x800 inference render (march_rays / composite_rays loop with early termination), ray tiles sharded
     over the ranks, tiles gathered once per frame.  -> {"value": Mrays/s whole job, ...} (same dict on every rank)."""
@@ -263,6 +282,12 @@ def run_ours(args):
     refresh = {"full_ms": time_refresh(True), "partial_ms": time_refresh(False),
                "note": "one update_extra_state call (128^3 cells x cascade full; 2 x 128^3/4 cells partial), host wall clock; not part of `value`"}
 
+    quality = None
+    if args.psnr_steps > 0 and world == 1:
+        quality = psnr_run(lambda: Trainer(bound=1.0, density_grid=torch.from_numpy(grid), device=dev, seed=0, fused=not args.no_fused,
+                                           use_graph=use_graph, optimizer="torch" if args.torch_optim else "fused"),
+                           scene, dev, args.psnr_steps, pool_dev)
+
     def shutdown():
         """Captured graphs hold NCCL work: drop them before the communicator goes, and never let teardown hang the job."""
         if world == 1:
@@ -313,7 +338,7 @@ def run_ours(args):
         "e2e": {"value": total_rays / (ms_e2e * 1e-3), "unit": "rays/s", "ms_per_step": ms_e2e / args.steps,
                 "h2d_bytes_per_step": world * RAYS_PER_GPU * 9 * 4, "d2h_bytes_per_step": world * 4},
         "gpu_launches": int(round(kt.kernel_launches() / n_prof * args.steps)),
-        "render": render, "density_refresh": refresh,
+        "render": render, "density_refresh": refresh, "quality": quality,
         "roofline": roof,
     }
     if world == 1:
@@ -346,7 +371,8 @@ def run_reference(args):
 if __name__ == "__main__":
     ap = argparse.ArgumentParser()
     ap.add_argument("--gpus", type=int, default=1)
-    ap.add_argument("--steps", type=int, default=256)
+    ap.add_argument("--steps", type=int, default=1024)
+    ap.add_argument("--psnr-steps", type=int, default=512, help="steps of the fixed-iteration PSNR run (0 = skip)")
     ap.add_argument("--frames", type=int, default=3, help="800x800 frames of the render workload (0 = skip)")
     ap.add_argument("--warmup", type=int, default=8)
     ap.add_argument("--impl", default="ours", choices=["ours", "reference"])

@@ -300,6 +300,7 @@ def run(args):
     rays = bench.RAYS_PER_GPU * args.steps
     val, val_e2e = rays / (ms * 1e-3), rays / (ms_e2e * 1e-3)
     render = bench.render_bench(tr.render, dev, 0, 1, frames=args.frames) if args.frames > 0 else None
+    quality = bench.psnr_run(lambda: RefTrainer(torch.from_numpy(grid)), scene, dev, args.psnr_steps, pool_dev) if args.psnr_steps > 0 else None
     return {
         "impl": "reference", "metric": "train rays/s", "value": val, "unit": "rays/s", "n_gpus": 1, "steps": args.steps, "warmup": warm,
         "ms_per_step": ms / args.steps, "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "f16", "data": "synthetic",
@@ -308,7 +309,7 @@ def run(args):
                    "note": "the reference's own CUDA extensions (raymarching, gridencoder, ffmlp: unmodified sources compiled for sm_100a) on the "
                            "same B200; the reference has no CPU implementation of this path and no multi-GPU path, so this arm always runs on "
                            "one GPU"},
-        "clocks": clk, "render": render,
+        "clocks": clk, "render": render, "quality": quality,
         "cpu_baseline": {"value": val, "unit": "rays/s", "cores": 0, "kind": "reference",
                          "sample": f"{args.steps} full train steps of 4096 rays on the reference CUDA extensions (GPU; the reference has no CPU path)"},
         "e2e": {"value": val_e2e, "unit": "rays/s", "ms_per_step": ms_e2e / args.steps, "h2d_bytes_per_step": bench.RAYS_PER_GPU * 36,

@@ -33,6 +33,7 @@ __global__ void __launch_bounds__(32 * kCompWarpsPerCta)
 k_composite_train_fwd(const float* __restrict__ sigmas, const float* __restrict__ rgbs, const float* __restrict__ deltas,
                       const int32_t* __restrict__ rays, uint32_t M, uint32_t N, float T_thresh,
                       float* __restrict__ weights_sum, float* __restrict__ depth, float* __restrict__ image) {
+    pdl_sync();
     const int lane = threadIdx.x & 31;
     const uint32_t n = blockIdx.x * kCompWarpsPerCta + (threadIdx.x >> 5);
     if (n >= N) return;
@@ -81,6 +82,7 @@ k_composite_train_bwd(const float* __restrict__ grad_weights_sum, const float* _
                       const float* __restrict__ sigmas, const float* __restrict__ rgbs, const float* __restrict__ deltas,
                       const int32_t* __restrict__ rays, const float* __restrict__ weights_sum, const float* __restrict__ image,
                       uint32_t M, uint32_t N, float T_thresh, float* __restrict__ grad_sigmas, float* __restrict__ grad_rgbs) {
+    pdl_sync();
     const int lane = threadIdx.x & 31;
     const uint32_t n = blockIdx.x * kCompWarpsPerCta + (threadIdx.x >> 5);
     if (n >= N) return;
@@ -130,6 +132,7 @@ __global__ void __launch_bounds__(32 * kCompWarpsPerCta)
 k_composite_mse_fwd(const float* __restrict__ sigmas, const float* __restrict__ rgbs, const float* __restrict__ deltas,
                     const int32_t* __restrict__ rays, const float* __restrict__ gt, float bg, uint32_t M, uint32_t N, float T_thresh,
                     float* __restrict__ weights_sum, float* __restrict__ depth, float* __restrict__ image, float* __restrict__ err) {
+    pdl_sync();
     const int lane = threadIdx.x & 31;
     const uint32_t n = blockIdx.x * kCompWarpsPerCta + (threadIdx.x >> 5);
     if (n >= N) return;
@@ -175,6 +178,7 @@ k_composite_mse_fwd(const float* __restrict__ sigmas, const float* __restrict__ 
 
 // loss[0] = sum(err[0..N)) / (3N), one CTA, fixed summation order
 __global__ void __launch_bounds__(1024) k_mse_finish(const float* __restrict__ err, uint32_t N, float* __restrict__ loss) {
+    pdl_sync();
     __shared__ float part[32];
     float acc = 0.f;
     for (uint32_t i = threadIdx.x; i < N; i += 1024) acc += __ldg(err + i);
@@ -192,6 +196,7 @@ k_composite_mse_bwd(const float* __restrict__ grad_loss, const float* __restrict
                     const float* __restrict__ sigmas, const float* __restrict__ rgbs, const float* __restrict__ deltas,
                     const int32_t* __restrict__ rays, const float* __restrict__ weights_sum, const float* __restrict__ image,
                     uint32_t M, uint32_t N, float T_thresh, int ordered, float* __restrict__ grad_sigmas, float* __restrict__ grad_rgbs) {
+    pdl_sync();
     const int lane = threadIdx.x & 31;
     const uint32_t n = blockIdx.x * kCompWarpsPerCta + (threadIdx.x >> 5);
     if (n >= N) return;
@@ -251,7 +256,7 @@ FOC_API int foc_composite_rays_train_forward(const float* sigmas, const float* r
                                              uint32_t M, uint32_t N, float T_thresh, float* weights_sum, float* depth,
                                              float* image, void* stream) {
     if (N == 0) return 0;
-    k_composite_train_fwd<<<ceil_div(N, kCompWarpsPerCta), 32 * kCompWarpsPerCta, 0, S(stream)>>>(
+    foc::launch(k_composite_train_fwd, ceil_div(N, kCompWarpsPerCta), 32 * kCompWarpsPerCta, 0, S(stream), 
         sigmas, rgbs, deltas, rays, M, N, T_thresh, weights_sum, depth, image);
     FOC_LAUNCH_CHECK(); return 0;
 }
@@ -261,7 +266,7 @@ FOC_API int foc_composite_rays_train_backward(const float* grad_weights_sum, con
                                               const float* weights_sum, const float* image, uint32_t M, uint32_t N,
                                               float T_thresh, float* grad_sigmas, float* grad_rgbs, void* stream) {
     if (N == 0) return 0;
-    k_composite_train_bwd<<<ceil_div(N, kCompWarpsPerCta), 32 * kCompWarpsPerCta, 0, S(stream)>>>(
+    foc::launch(k_composite_train_bwd, ceil_div(N, kCompWarpsPerCta), 32 * kCompWarpsPerCta, 0, S(stream), 
         grad_weights_sum, grad_image, sigmas, rgbs, deltas, rays, weights_sum, image, M, N, T_thresh, grad_sigmas, grad_rgbs);
     FOC_LAUNCH_CHECK(); return 0;
 }
@@ -270,10 +275,10 @@ FOC_API int foc_composite_mse_forward(const float* sigmas, const float* rgbs, co
                                       float bg, uint32_t M, uint32_t N, float T_thresh, float* weights_sum, float* depth, float* image,
                                       float* err, float* loss, void* stream) {
     if (N == 0) return 0;
-    k_composite_mse_fwd<<<ceil_div(N, kCompWarpsPerCta), 32 * kCompWarpsPerCta, 0, S(stream)>>>(
+    foc::launch(k_composite_mse_fwd, ceil_div(N, kCompWarpsPerCta), 32 * kCompWarpsPerCta, 0, S(stream), 
         sigmas, rgbs, deltas, rays, gt, bg, M, N, T_thresh, weights_sum, depth, image, err);
     FOC_LAUNCH_CHECK();
-    k_mse_finish<<<1, 1024, 0, S(stream)>>>(err, N, loss);
+    foc::launch(k_mse_finish, 1, 1024, 0, S(stream), err, N, loss);
     FOC_LAUNCH_CHECK(); return 0;
 }
 
@@ -281,7 +286,7 @@ FOC_API int foc_composite_mse_backward(const float* grad_loss, const float* gt, 
                                        const float* deltas, const int32_t* rays, const float* weights_sum, const float* image, uint32_t M,
                                        uint32_t N, float T_thresh, int ordered, float* grad_sigmas, float* grad_rgbs, void* stream) {
     if (N == 0) return 0;
-    k_composite_mse_bwd<<<ceil_div(N, kCompWarpsPerCta), 32 * kCompWarpsPerCta, 0, S(stream)>>>(
+    foc::launch(k_composite_mse_bwd, ceil_div(N, kCompWarpsPerCta), 32 * kCompWarpsPerCta, 0, S(stream), 
         grad_loss, gt, bg, sigmas, rgbs, deltas, rays, weights_sum, image, M, N, T_thresh, ordered, grad_sigmas, grad_rgbs);
     FOC_LAUNCH_CHECK(); return 0;
 }

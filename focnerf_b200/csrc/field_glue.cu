@@ -36,6 +36,7 @@ __device__ __forceinline__ uint32_t pack2h(__half a, __half b) { const __half2 h
 // h [B,16] f16 (sigma-net output), dirs [B,3] f32  ->  sigma [B] f32,  cin [B,32] f16 = [SH4(d) | h[1:16] | 0]
 __global__ void __launch_bounds__(256)
 k_field_mid_fwd(const float* __restrict__ dirs, const __half* __restrict__ h, uint32_t B, float* __restrict__ sigma, __half* __restrict__ cin) {
+    pdl_sync();
     const uint32_t b = blockIdx.x * blockDim.x + threadIdx.x;
     if (b >= B) return;
     const uint4 h0 = __ldg(reinterpret_cast<const uint4*>(h + (size_t)b * 16)), h1 = __ldg(reinterpret_cast<const uint4*>(h + (size_t)b * 16) + 1);
@@ -59,6 +60,7 @@ k_field_mid_fwd(const float* __restrict__ dirs, const __half* __restrict__ h, ui
 __global__ void __launch_bounds__(256)
 k_field_mid_bwd(const float* __restrict__ grad_sigma, const __half* __restrict__ grad_cin, const __half* __restrict__ h, uint32_t B,
                 __half* __restrict__ grad_h) {
+    pdl_sync();
     const uint32_t b = blockIdx.x * blockDim.x + threadIdx.x;
     if (b >= B) return;
     const uint4 g2 = __ldg(reinterpret_cast<const uint4*>(grad_cin + (size_t)b * 32) + 2), g3 = __ldg(reinterpret_cast<const uint4*>(grad_cin + (size_t)b * 32) + 3);
@@ -74,6 +76,7 @@ k_field_mid_bwd(const float* __restrict__ grad_sigma, const __half* __restrict__
 // hc [B,16] f16 (colour-net output)  ->  rgb [B,3] f32 = float(half(sigmoid(float(hc[0:3]))))
 __global__ void __launch_bounds__(256)
 k_rgb_fwd(const __half* __restrict__ hc, uint32_t B, float* __restrict__ rgb) {
+    pdl_sync();
     const uint32_t b = blockIdx.x * blockDim.x + threadIdx.x;
     if (b >= B) return;
     const uint2 v = __ldg(reinterpret_cast<const uint2*>(hc + (size_t)b * 16));
@@ -86,6 +89,7 @@ k_rgb_fwd(const __half* __restrict__ hc, uint32_t B, float* __restrict__ rgb) {
 // grad_rgb [B,3] f32, rgb [B,3] f32 (the forward's output)  ->  grad_hc [B,16] f16 (columns 3..15 zero)
 __global__ void __launch_bounds__(256)
 k_rgb_bwd(const float* __restrict__ grad_rgb, const float* __restrict__ rgb, uint32_t B, __half* __restrict__ grad_hc) {
+    pdl_sync();
     const uint32_t b = blockIdx.x * blockDim.x + threadIdx.x;
     if (b >= B) return;
     float g[3];
@@ -104,22 +108,22 @@ static inline cudaStream_t S(void* s) { return reinterpret_cast<cudaStream_t>(s)
 
 FOC_API int foc_field_mid_forward(const float* dirs, const uint16_t* h, uint32_t B, float* sigma, uint16_t* cin, void* stream) {
     if (B == 0) return 0;
-    k_field_mid_fwd<<<ceil_div(B, 256), 256, 0, S(stream)>>>(dirs, reinterpret_cast<const __half*>(h), B, sigma, reinterpret_cast<__half*>(cin));
+    foc::launch(k_field_mid_fwd, ceil_div(B, 256), 256, 0, S(stream), dirs, reinterpret_cast<const __half*>(h), B, sigma, reinterpret_cast<__half*>(cin));
     FOC_LAUNCH_CHECK(); return 0;
 }
 FOC_API int foc_field_mid_backward(const float* grad_sigma, const uint16_t* grad_cin, const uint16_t* h, uint32_t B, uint16_t* grad_h, void* stream) {
     if (B == 0) return 0;
-    k_field_mid_bwd<<<ceil_div(B, 256), 256, 0, S(stream)>>>(grad_sigma, reinterpret_cast<const __half*>(grad_cin), reinterpret_cast<const __half*>(h), B,
+    foc::launch(k_field_mid_bwd, ceil_div(B, 256), 256, 0, S(stream), grad_sigma, reinterpret_cast<const __half*>(grad_cin), reinterpret_cast<const __half*>(h), B,
                                                             reinterpret_cast<__half*>(grad_h));
     FOC_LAUNCH_CHECK(); return 0;
 }
 FOC_API int foc_rgb_sigmoid_forward(const uint16_t* hc, uint32_t B, float* rgb, void* stream) {
     if (B == 0) return 0;
-    k_rgb_fwd<<<ceil_div(B, 256), 256, 0, S(stream)>>>(reinterpret_cast<const __half*>(hc), B, rgb);
+    foc::launch(k_rgb_fwd, ceil_div(B, 256), 256, 0, S(stream), reinterpret_cast<const __half*>(hc), B, rgb);
     FOC_LAUNCH_CHECK(); return 0;
 }
 FOC_API int foc_rgb_sigmoid_backward(const float* grad_rgb, const float* rgb, uint32_t B, uint16_t* grad_hc, void* stream) {
     if (B == 0) return 0;
-    k_rgb_bwd<<<ceil_div(B, 256), 256, 0, S(stream)>>>(grad_rgb, rgb, B, reinterpret_cast<__half*>(grad_hc));
+    foc::launch(k_rgb_bwd, ceil_div(B, 256), 256, 0, S(stream), grad_rgb, rgb, B, reinterpret_cast<__half*>(grad_hc));
     FOC_LAUNCH_CHECK(); return 0;
 }

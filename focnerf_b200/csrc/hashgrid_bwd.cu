@@ -73,6 +73,7 @@ __global__ void __launch_bounds__(256)
 k_grid_bwd_scatter(const T* __restrict__ grad, const float* __restrict__ inputs, const int32_t* __restrict__ offsets,
                    T* __restrict__ grad_table, uint32_t B, uint32_t L, float S, uint32_t H, uint32_t gridtype, bool align_corners,
                    uint32_t interp, uint32_t level0, uint32_t nl) {
+    pdl_sync();
     const uint64_t t = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x;
     if (t >= (uint64_t)B * nl) return;
     uint32_t b, level;
@@ -126,6 +127,7 @@ __global__ void __launch_bounds__(128)
 k_grid_bwd_runs(const T* __restrict__ grad, const float* __restrict__ inputs, const int32_t* __restrict__ offsets,
                 T* __restrict__ grad_table, uint32_t B, uint32_t L, float S, uint32_t H, uint32_t gridtype, bool align_corners,
                 uint32_t interp) {
+    pdl_sync();
     const uint32_t level = blockIdx.y;
     const uint32_t b0 = (blockIdx.x * blockDim.x + threadIdx.x) * (uint32_t)kRun;
     if (b0 >= B) return;
@@ -266,13 +268,13 @@ int launch_bwd_layout(const void* grad, const float* inputs, const int32_t* offs
     while (n_coarse < L && (uint32_t)ceilf(exp2f((float)n_coarse * S) * (float)H - 1.0f) + 1u <= kCoarseRes) ++n_coarse;
     if (n_coarse > 0) {
         dim3 rgrid(ceil_div(ceil_div(B, (uint32_t)kRun), 128u), n_coarse);
-        k_grid_bwd_runs<T, D, C, LAYOUT><<<rgrid, 128, 0, st>>>((const T*)grad, inputs, offsets, (T*)grad_table, B, L, S, H, gridtype, ac, interp);
+        foc::launch(k_grid_bwd_runs<T, D, C, LAYOUT>, rgrid, 128, 0, st, (const T*)grad, inputs, offsets, (T*)grad_table, B, L, S, H, gridtype, ac, interp);
         FOC_LAUNCH_CHECK();
     }
     if (n_coarse < L) {
         const uint32_t nl = L - n_coarse;
         const uint64_t total = (uint64_t)B * nl;
-        k_grid_bwd_scatter<T, D, C, LAYOUT><<<(uint32_t)((total + 255) / 256), 256, 0, st>>>((const T*)grad, inputs, offsets, (T*)grad_table, B, L, S, H,
+        foc::launch(k_grid_bwd_scatter<T, D, C, LAYOUT>, (uint32_t)((total + 255) / 256), 256, 0, st, (const T*)grad, inputs, offsets, (T*)grad_table, B, L, S, H,
                                                                                           gridtype, ac, interp, n_coarse, nl);
         FOC_LAUNCH_CHECK();
     }

@@ -55,6 +55,7 @@ __global__ void __launch_bounds__(256)
 k_grid_fwd(const float* __restrict__ inputs, const T* __restrict__ table, const int32_t* __restrict__ offsets,
            T* __restrict__ outputs, uint32_t B, uint32_t L, float S, uint32_t H, T* __restrict__ dy_dx,
            uint32_t gridtype, bool align_corners, uint32_t interp) {
+    pdl_sync();
     uint32_t b, level;
     if constexpr (LAYOUT == 0) { b = blockIdx.x * blockDim.x + threadIdx.x; level = blockIdx.y; if (b >= B) return; }
     else {
@@ -149,10 +150,10 @@ int launch_fwd(const float* inputs, const void* table, const int32_t* offsets, v
                float S, uint32_t H, void* dy_dx, uint32_t gridtype, bool ac, uint32_t interp, int layout, cudaStream_t st) {
     if (layout == 0) {
         dim3 grid(ceil_div(B, 256), L);
-        k_grid_fwd<T, D, C, 0><<<grid, 256, 0, st>>>(inputs, (const T*)table, offsets, (T*)outputs, B, L, S, H, (T*)dy_dx, gridtype, ac, interp);
+        foc::launch(k_grid_fwd<T, D, C, 0>, grid, 256, 0, st, inputs, (const T*)table, offsets, (T*)outputs, B, L, S, H, (T*)dy_dx, gridtype, ac, interp);
     } else {
         const uint64_t total = (uint64_t)B * L;
-        k_grid_fwd<T, D, C, 1><<<(uint32_t)((total + 255) / 256), 256, 0, st>>>(inputs, (const T*)table, offsets, (T*)outputs, B, L, S, H, (T*)dy_dx, gridtype, ac, interp);
+        foc::launch(k_grid_fwd<T, D, C, 1>, (uint32_t)((total + 255) / 256), 256, 0, st, inputs, (const T*)table, offsets, (T*)outputs, B, L, S, H, (T*)dy_dx, gridtype, ac, interp);
     }
     FOC_LAUNCH_CHECK(); return 0;
 }

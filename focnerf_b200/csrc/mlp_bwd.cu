@@ -97,6 +97,7 @@ k_mlp_bwd(const __grid_constant__ CUtensorMap tm_fb, const __grid_constant__ CUt
     __syncthreads();
     tc_fence_after();
     const uint32_t tmem = *tmem_slot;
+    pdl_sync();                                                      // everything above overlaps the previous kernel's tail
     if (threadIdx.x == 0 && blockIdx.x < p.num_tiles) {
         mbar_expect_tx(bar_w, (uint32_t)(kHidden * IN * 2) + (uint32_t)n_hmm * 8192u + 2048u);
         tma_load_2d(smem + SM::off_w_in(L), &tm_win, bar_w, 0, 0);
@@ -298,6 +299,7 @@ k_mlp_bwd(const __grid_constant__ CUtensorMap tm_fb, const __grid_constant__ CUt
 // sums are combined in a fixed order through shared memory -> deterministic, and 8x shorter dependent-load chains.
 __global__ void __launch_bounds__(256)
 k_mlp_wgrad_finish(const float* __restrict__ partials, uint32_t n_cta, uint32_t num_params, __half* __restrict__ grad_weights) {
+    pdl_sync();
     __shared__ float s[8][32];
     const uint32_t lane = threadIdx.x & 31, slice = threadIdx.x >> 5;
     const uint32_t i = blockIdx.x * 32 + lane;
@@ -356,9 +358,9 @@ int launch_bwd(const uint16_t* grad, const uint16_t* inputs, const uint16_t* wei
     p.tmem_cols = need <= 128 ? 128 : need <= 256 ? 256 : 512;
     if (need > 512) return FOC_ERR_UNSUPPORTED;
     const uint32_t grid = bwd_grid(B);
-    k_mlp_bwd<IN, ACT><<<grid, 128, smem, st>>>(tm_fb, tm_in, tm_win, tm_w, p);
+    foc::launch(k_mlp_bwd<IN, ACT>, grid, 128, smem, st, tm_fb, tm_in, tm_win, tm_w, p);
     FOC_LAUNCH_CHECK();
-    k_mlp_wgrad_finish<<<ceil_div(p.num_params, 32), 256, 0, st>>>(p.partials, grid, p.num_params, reinterpret_cast<__half*>(grad_weights));
+    foc::launch(k_mlp_wgrad_finish, ceil_div(p.num_params, 32), 256, 0, st, p.partials, grid, p.num_params, reinterpret_cast<__half*>(grad_weights));
     FOC_LAUNCH_CHECK(); return 0;
 }
 

@@ -95,6 +95,7 @@ k_mlp_fwd(const __grid_constant__ CUtensorMap tm_in, const __grid_constant__ CUt
     __syncthreads();
     tc_fence_after();
     const uint32_t tmem = *tmem_slot;
+    pdl_sync();                                                      // everything above overlaps the previous kernel's tail
 
     const uint32_t first = blockIdx.x, stride = gridDim.x;
     if (first >= p.num_tiles) { __syncthreads(); if (warp == 0) tmem_dealloc(tmem, 64); return; }
@@ -235,7 +236,7 @@ int launch_fwd(const uint16_t* inputs, const uint16_t* weights, uint32_t B, uint
     p.num_tiles = B / kTile;
     const uint32_t ctas_per_sm = 4;                                    // 4 x 64 TMEM columns, ~4 x 45 KB shared memory
     const uint32_t grid = p.num_tiles < (uint32_t)kNumSMs * ctas_per_sm ? p.num_tiles : (uint32_t)kNumSMs * ctas_per_sm;
-    k_mlp_fwd<IN, ACT><<<grid, 128, smem, st>>>(tm_in, tm_win, tm_w, p);
+    foc::launch(k_mlp_fwd<IN, ACT>, grid, 128, smem, st, tm_in, tm_win, tm_w, p);
     FOC_LAUNCH_CHECK(); return 0;
 }
 

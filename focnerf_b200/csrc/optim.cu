@@ -63,20 +63,38 @@ __device__ __forceinline__ void load_grad4(const FocAdamTensor& T, uint64_t i, u
     }
 }
 
-// found_inf = 1 when any gradient element is inf / nan (never cleared here)
+// found_inf = 1 when any gradient element is inf / nan (never cleared here).  16-byte loads: 8 halfs / 4 floats per access.
 __global__ void __launch_bounds__(kThreads) k_adam_nonfinite(const __grid_constant__ AdamList L, float* __restrict__ found_inf) {
+    pdl_sync();
     const int ti = find_tensor(L, blockIdx.x);
     const FocAdamTensor& T = L.t[ti];
     if (T.grad == nullptr) return;
     const uint64_t base = (uint64_t)(blockIdx.x - L.block_start[ti]) * kPerBlock;
+    const uint64_t end = min(T.n, base + (uint64_t)kPerBlock);
     bool ok = true;
-    #pragma unroll
-    for (int u = 0; u < kUnroll; ++u) {
-        const uint64_t i = base + ((uint64_t)u * kThreads + threadIdx.x) * kVec;
-        if (i >= T.n) break;
-        float g[4];
-        load_grad4(T, i, T.n, g);
-        ok = ok && finite4(g[0], g[1], g[2], g[3]);
+    if (T.grad_dtype == 1) {
+        const __half* g = static_cast<const __half*>(T.grad);
+        uint64_t i = base + (uint64_t)threadIdx.x * 8;
+        #pragma unroll
+        for (int u = 0; u < kPerBlock / (kThreads * 8); ++u, i += (uint64_t)kThreads * 8) {
+            if (i + 8 <= end) {
+                const uint4 v = *reinterpret_cast<const uint4*>(g + i);
+                const uint32_t w[4] = {v.x, v.y, v.z, v.w};
+                #pragma unroll
+                for (int k = 0; k < 4; ++k)         // exponent field all ones <=> inf / nan, per 16-bit half
+                    ok = ok && ((w[k] & 0x7c00u) != 0x7c00u) && ((w[k] & 0x7c000000u) != 0x7c000000u);
+            } else {
+                for (uint64_t j = i; j < end && j < i + 8; ++j) ok = ok && ((__half_as_ushort(g[j]) & 0x7c00u) != 0x7c00u);
+            }
+        }
+    } else {
+        const float* g = static_cast<const float*>(T.grad);
+        uint64_t i = base + (uint64_t)threadIdx.x * 4;
+        #pragma unroll
+        for (int u = 0; u < kPerBlock / (kThreads * 4); ++u, i += (uint64_t)kThreads * 4) {
+            if (i + 4 <= end) { const float4 v = *reinterpret_cast<const float4*>(g + i); ok = ok && finite4(v.x, v.y, v.z, v.w); }
+            else { for (uint64_t j = i; j < end && j < i + 4; ++j) ok = ok && (fabsf(g[j]) <= 3.402823466e+38f); }
+        }
     }
     if (!ok) *found_inf = 1.0f;
 }
@@ -84,6 +102,7 @@ __global__ void __launch_bounds__(kThreads) k_adam_nonfinite(const __grid_consta
 __global__ void __launch_bounds__(kThreads) k_adam_step(const __grid_constant__ AdamList L, const float* __restrict__ lr_p, float beta1, float beta2,
                                                         float eps, const float* __restrict__ scale, const float* __restrict__ found_inf,
                                                         const int32_t* __restrict__ step) {
+    pdl_sync();
     const int ti = find_tensor(L, blockIdx.x);
     const FocAdamTensor& T = L.t[ti];
     const uint64_t base = (uint64_t)(blockIdx.x - L.block_start[ti]) * kPerBlock;
@@ -154,6 +173,7 @@ __global__ void __launch_bounds__(kThreads) k_adam_step(const __grid_constant__ 
 // torch.amp.GradScaler.update() (torch/amp/grad_scaler.py, amp_update_scale_cuda_kernel) + the step counter
 __global__ void k_scaler_update(float* __restrict__ scale, int32_t* __restrict__ growth_tracker, float* __restrict__ found_inf,
                                 int32_t* __restrict__ step, float growth, float backoff, int32_t interval) {
+    pdl_sync();
     if (threadIdx.x != 0 || blockIdx.x != 0) return;
     const bool bad = found_inf != nullptr && *found_inf != 0.0f;
     if (scale != nullptr) {
@@ -195,7 +215,7 @@ int make_list(const FocAdamTensor* tensors, int count, AdamList& L) {
 FOC_API int foc_adam_nonfinite(const FocAdamTensor* tensors, int count, float* found_inf, void* stream) {
     AdamList L;
     if (int rc = make_list(tensors, count, L)) return rc;
-    k_adam_nonfinite<<<L.block_start[kMaxTensors], kThreads, 0, reinterpret_cast<cudaStream_t>(stream)>>>(L, found_inf);
+    foc::launch(k_adam_nonfinite, L.block_start[kMaxTensors], kThreads, 0, reinterpret_cast<cudaStream_t>(stream), L, found_inf);
     FOC_LAUNCH_CHECK(); return 0;
 }
 
@@ -203,12 +223,12 @@ FOC_API int foc_adam_step(const FocAdamTensor* tensors, int count, const float* 
                           const float* scale, const float* found_inf, const int32_t* step, void* stream) {
     AdamList L;
     if (int rc = make_list(tensors, count, L)) return rc;
-    k_adam_step<<<L.block_start[kMaxTensors], kThreads, 0, reinterpret_cast<cudaStream_t>(stream)>>>(L, lr, beta1, beta2, eps, scale, found_inf, step);
+    foc::launch(k_adam_step, L.block_start[kMaxTensors], kThreads, 0, reinterpret_cast<cudaStream_t>(stream), L, lr, beta1, beta2, eps, scale, found_inf, step);
     FOC_LAUNCH_CHECK(); return 0;
 }
 
 FOC_API int foc_scaler_update(float* scale, int32_t* growth_tracker, float* found_inf, int32_t* step, float growth_factor,
                               float backoff_factor, int32_t growth_interval, void* stream) {
-    k_scaler_update<<<1, 32, 0, reinterpret_cast<cudaStream_t>(stream)>>>(scale, growth_tracker, found_inf, step, growth_factor, backoff_factor, growth_interval);
+    foc::launch(k_scaler_update, 1, 32, 0, reinterpret_cast<cudaStream_t>(stream), scale, growth_tracker, found_inf, step, growth_factor, backoff_factor, growth_interval);
     FOC_LAUNCH_CHECK(); return 0;
 }

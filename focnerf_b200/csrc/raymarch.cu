@@ -107,6 +107,7 @@ using namespace foc;
 __global__ void __launch_bounds__(256) k_near_far(const float* __restrict__ rays_o, const float* __restrict__ rays_d,
                                                   const float* __restrict__ aabb, uint32_t N, float min_near,
                                                   float* __restrict__ nears, float* __restrict__ fars) {
+    pdl_sync();
     const uint32_t n = blockIdx.x * blockDim.x + threadIdx.x;
     if (n >= N) return;
     float tn = 0.f, tf = 0.f;
@@ -256,6 +257,7 @@ __global__ void __launch_bounds__(32 * kSeqWarps) k_march_record_const(const flo
                                                             const float* __restrict__ nears, const float* __restrict__ fars,
                                                             const float* __restrict__ noises, uint32_t N, uint32_t max_steps,
                                                             MarchParams p, uint32_t* __restrict__ counts, float* __restrict__ tbuf) {
+    pdl_sync();
     __shared__ MarchSeq seq[kSeqWarps];
     const uint32_t lane = threadIdx.x & 31u, n = blockIdx.x * (uint32_t)kSeqWarps + (threadIdx.x >> 5);
     if (n >= N) return;                                              // warp-uniform
@@ -369,6 +371,7 @@ __global__ void __launch_bounds__(32 * kSeqWarps) k_march_record_const(const flo
 // counter[0] += total, counter[1] += N  (raymarching.cu:405-413).
 __global__ void __launch_bounds__(1024) k_march_scan(const uint32_t* __restrict__ counts, uint32_t N,
                                                      int32_t* __restrict__ rays, int32_t* __restrict__ counter) {
+    pdl_sync();
     __shared__ uint32_t warp_tot[32];
     __shared__ uint32_t s_base;
     const int lane = threadIdx.x & 31, wid = threadIdx.x >> 5;
@@ -405,6 +408,7 @@ __global__ void __launch_bounds__(128) k_march_expand(const float* __restrict__ 
                                                       uint32_t N, uint32_t M, uint32_t max_steps, MarchParams p,
                                                       const int32_t* __restrict__ rays, const float* __restrict__ tbuf,
                                                       float* __restrict__ xyzs, float* __restrict__ dirs, float* __restrict__ deltas) {
+    pdl_sync();
     const uint32_t n = (blockIdx.x * blockDim.x + threadIdx.x) >> 5, lane = threadIdx.x & 31u;
     if (n >= N) return;
     const uint32_t off = (uint32_t)__ldg(rays + 3 * (size_t)n + 1), num = (uint32_t)__ldg(rays + 3 * (size_t)n + 2);
@@ -477,7 +481,7 @@ static inline cudaStream_t S(void* s) { return reinterpret_cast<cudaStream_t>(s)
 FOC_API int foc_near_far_from_aabb(const float* rays_o, const float* rays_d, const float* aabb, uint32_t N, float min_near,
                                    float* nears, float* fars, void* stream) {
     if (N == 0) return 0;
-    k_near_far<<<ceil_div(N, 256), 256, 0, S(stream)>>>(rays_o, rays_d, aabb, N, min_near, nears, fars);
+    foc::launch(k_near_far, ceil_div(N, 256), 256, 0, S(stream), rays_o, rays_d, aabb, N, min_near, nears, fars);
     FOC_LAUNCH_CHECK(); return 0;
 }
 FOC_API int foc_sph_from_ray(const float* rays_o, const float* rays_d, float radius, uint32_t N, float* coords, void* stream) {
@@ -523,13 +527,13 @@ FOC_API int foc_march_rays_count(const float* rays_o, const float* rays_d, const
     float* tbuf = reinterpret_cast<float*>(static_cast<uint8_t*>(scratch) + march_counts_bytes(N));
     // constant step: warp-per-ray parallel walk; else serial walk, 4 rays per warp for small batches (see ray_of_thread)
     if (dt_gamma == 0.0f)
-        k_march_record_const<<<ceil_div(N, (uint32_t)kSeqWarps), 32 * kSeqWarps, 0, S(stream)>>>(rays_o, rays_d, nears, fars, noises, N, max_steps, p, counts, tbuf);
+        foc::launch(k_march_record_const, ceil_div(N, (uint32_t)kSeqWarps), 32 * kSeqWarps, 0, S(stream), rays_o, rays_d, nears, fars, noises, N, max_steps, p, counts, tbuf);
     else if (N <= (uint32_t)kNumSMs * 32u * 8u)
         k_march_record<4><<<ceil_div(ceil_div(N, 4) * 32, 128), 128, 0, S(stream)>>>(rays_o, rays_d, nears, fars, noises, N, max_steps, p, counts, tbuf);
     else
         k_march_record<32><<<ceil_div(N, 128), 128, 0, S(stream)>>>(rays_o, rays_d, nears, fars, noises, N, max_steps, p, counts, tbuf);
     FOC_LAUNCH_CHECK();
-    k_march_scan<<<1, 1024, 0, S(stream)>>>(counts, N, rays, counter);
+    foc::launch(k_march_scan, 1, 1024, 0, S(stream), counts, N, rays, counter);
     FOC_LAUNCH_CHECK(); return 0;
 }
 
@@ -541,7 +545,7 @@ FOC_API int foc_march_rays_expand(const float* rays_o, const float* rays_d, floa
     if (C == 0 || C > 8 || H == 0 || H > 1024) return FOC_ERR_UNSUPPORTED;
     const MarchParams p = make_march_params(nullptr, bound, dt_gamma, max_steps, C, H);
     const float* tbuf = reinterpret_cast<const float*>(static_cast<const uint8_t*>(scratch) + march_counts_bytes(N));
-    k_march_expand<<<ceil_div(N, 4), 128, 0, S(stream)>>>(rays_o, rays_d, nears, noises, N, M, max_steps, p, rays, tbuf, xyzs, dirs, deltas);
+    foc::launch(k_march_expand, ceil_div(N, 4), 128, 0, S(stream), rays_o, rays_d, nears, noises, N, M, max_steps, p, rays, tbuf, xyzs, dirs, deltas);
     FOC_LAUNCH_CHECK(); return 0;
 }
 
