@@ -98,20 +98,32 @@ k_grid_bwd_scatter(const T* __restrict__ grad, const float* __restrict__ inputs,
     float pos[D], pder[D];
     uint32_t pg[D];
     grid_locate<D>(x, lv.scale, align_corners, interp, pos, pder, pg);
+    // corners come in pairs along x (idx, idx | 1).  Their rows are neighbours whenever the dense index is used, and on a
+    // hashed level whenever x is even (x + 1 only flips bit 0 of x * 1, the first hash prime): an aligned neighbour pair of
+    // the C = 2 fp16 table is 8 contiguous bytes, one vector reduction instead of two.
     #pragma unroll
-    for (int idx = 0; idx < (1 << D); ++idx) {
-        float wt = 1.0f;
-        uint32_t pl[D];
+    for (int idx = 0; idx < (1 << D); idx += 2) {
+        float wt[2];
+        uint32_t row[2];
         #pragma unroll
-        for (int d = 0; d < D; ++d) {
-            if ((idx >> d) & 1) { wt = __fmul_rn(wt, pos[d]); pl[d] = pg[d] + 1; }
-            else { wt = __fmul_rn(wt, __fsub_rn(1.0f, pos[d])); pl[d] = pg[d]; }
+        for (int s = 0; s < 2; ++s) {
+            float w = 1.0f;
+            uint32_t pl[D];
+            #pragma unroll
+            for (int d = 0; d < D; ++d) {
+                if (((idx + s) >> d) & 1) { w = __fmul_rn(w, pos[d]); pl[d] = pg[d] + 1; }
+                else { w = __fmul_rn(w, __fsub_rn(1.0f, pos[d])); pl[d] = pg[d]; }
+            }
+            wt[s] = w; row[s] = gidx(pl);
         }
-        const uint32_t row = gidx(pl);
-        float v[C];
+        float v0[C], v1[C];
         #pragma unroll
-        for (int c = 0; c < C; ++c) v[c] = __fmul_rn(wt, g[c]);
-        red_row<T, C>(tab + (size_t)row * C, v);
+        for (int c = 0; c < C; ++c) { v0[c] = __fmul_rn(wt[0], g[c]); v1[c] = __fmul_rn(wt[1], g[c]); }
+        if constexpr (sizeof(T) == 2 && C == 2) {
+            if (row[1] == row[0] + 1 && (row[0] & 1u) == 0) { red_f16x4(reinterpret_cast<__half*>(tab) + (size_t)row[0] * 2, v0[0], v0[1], v1[0], v1[1]); continue; }
+        }
+        red_row<T, C>(tab + (size_t)row[0] * C, v0);
+        red_row<T, C>(tab + (size_t)row[1] * C, v1);
     }
 }
 
@@ -139,12 +151,23 @@ k_grid_bwd_runs(const T* __restrict__ grad, const float* __restrict__ inputs, co
     bool have = false;
     auto flush = [&]() {
         #pragma unroll
-        for (int idx = 0; idx < (1 << D); ++idx) {
-            uint32_t pl[D];
+        for (int idx = 0; idx < (1 << D); idx += 2) {                // x-neighbour pairs, see k_grid_bwd_scatter
+            uint32_t row[2];
             #pragma unroll
-            for (int d = 0; d < D; ++d) pl[d] = cur[d] + ((idx >> d) & 1);
-            const uint32_t row = gidx(pl);
-            red_row<T, C>(tab + (size_t)row * C, acc[idx]);
+            for (int s = 0; s < 2; ++s) {
+                uint32_t pl[D];
+                #pragma unroll
+                for (int d = 0; d < D; ++d) pl[d] = cur[d] + (((idx + s) >> d) & 1);
+                row[s] = gidx(pl);
+            }
+            if constexpr (sizeof(T) == 2 && C == 2) {
+                if (row[1] == row[0] + 1 && (row[0] & 1u) == 0) {
+                    red_f16x4(reinterpret_cast<__half*>(tab) + (size_t)row[0] * 2, acc[idx][0], acc[idx][1], acc[idx + 1][0], acc[idx + 1][1]);
+                    continue;
+                }
+            }
+            red_row<T, C>(tab + (size_t)row[0] * C, acc[idx]);
+            red_row<T, C>(tab + (size_t)row[1] * C, acc[idx + 1]);
         }
     };
     const uint32_t n = min((uint32_t)kRun, B - b0);
