@@ -87,24 +87,57 @@ k_grid_fwd(const float* __restrict__ inputs, const T* __restrict__ table, const 
     // gather: all corner rows first (independent loads), then the ordered accumulation of the reference
     float w[1 << D], rows[1 << D][C];
     #pragma unroll
-    for (int idx = 0; idx < (1 << D); ++idx) {
-        float wt = 1.0f;
-        uint32_t pl[D];
+    for (int idx = 0; idx < (1 << D); idx += 2) {
+        // corners (idx, idx | 1) differ in x only: neighbouring rows on dense levels, and on hashed levels whenever x is even.
+        // An aligned neighbour pair of the C = 2 fp16 table is fetched with one 8-byte load.
+        uint32_t row[2];
         #pragma unroll
-        for (int d = 0; d < D; ++d) {
-            if ((idx >> d) & 1) { wt = __fmul_rn(wt, pos[d]); pl[d] = pg[d] + 1; }
-            else { wt = __fmul_rn(wt, __fsub_rn(1.0f, pos[d])); pl[d] = pg[d]; }
+        for (int s = 0; s < 2; ++s) {
+            float wt = 1.0f;
+            uint32_t pl[D];
+            #pragma unroll
+            for (int d = 0; d < D; ++d) {
+                if (((idx + s) >> d) & 1) { wt = __fmul_rn(wt, pos[d]); pl[d] = pg[d] + 1; }
+                else { wt = __fmul_rn(wt, __fsub_rn(1.0f, pos[d])); pl[d] = pg[d]; }
+            }
+            w[idx + s] = wt; row[s] = gidx(pl);
         }
-        w[idx] = wt;
-        RowVec<T, C>::ld(tab + (size_t)gidx(pl) * C, rows[idx]);
+        if constexpr (sizeof(T) == 2 && C == 2) {
+            if (row[1] == row[0] + 1 && (row[0] & 1u) == 0) {
+                const uint2 u = __ldg(reinterpret_cast<const uint2*>(tab + (size_t)row[0] * 2));
+                const __half2 a = *reinterpret_cast<const __half2*>(&u.x), b = *reinterpret_cast<const __half2*>(&u.y);
+                rows[idx][0] = __low2float(a); rows[idx][1] = __high2float(a); rows[idx + 1][0] = __low2float(b); rows[idx + 1][1] = __high2float(b);
+                continue;
+            }
+        }
+        RowVec<T, C>::ld(tab + (size_t)row[0] * C, rows[idx]);
+        RowVec<T, C>::ld(tab + (size_t)row[1] * C, rows[idx + 1]);
     }
     float res[C];
-    #pragma unroll
-    for (int c = 0; c < C; ++c) res[c] = 0.f;
-    #pragma unroll
-    for (int idx = 0; idx < (1 << D); ++idx) {
+    if constexpr (sizeof(T) == 2 && C % 2 == 0) {
+        // c10::Half `results += w * g`: the product is rounded to half, the sum is formed in float and rounded to half
+        // (hashgrid.cuh Elem<__half>::acc).  A native fp16 add rounds the exact sum once; rounding through fp32 first is
+        // innocuous because fp32 carries 24 >= 2 * 11 + 2 significand bits, so HADD2 gives the same bits with a third of
+        // the conversion instructions (the kernel was throttled on the conversion pipe).
+        __half2 r2[C / 2];
         #pragma unroll
-        for (int c = 0; c < C; ++c) res[c] = Elem<T>::acc(res[c], w[idx], rows[idx][c]);
+        for (int c = 0; c < C / 2; ++c) r2[c] = __floats2half2_rn(0.f, 0.f);
+        #pragma unroll
+        for (int idx = 0; idx < (1 << D); ++idx) {
+            #pragma unroll
+            for (int c = 0; c < C / 2; ++c)
+                r2[c] = __hadd2(r2[c], __floats2half2_rn(__fmul_rn(w[idx], rows[idx][2 * c]), __fmul_rn(w[idx], rows[idx][2 * c + 1])));
+        }
+        #pragma unroll
+        for (int c = 0; c < C / 2; ++c) { res[2 * c] = __low2float(r2[c]); res[2 * c + 1] = __high2float(r2[c]); }
+    } else {
+        #pragma unroll
+        for (int c = 0; c < C; ++c) res[c] = 0.f;
+        #pragma unroll
+        for (int idx = 0; idx < (1 << D); ++idx) {
+            #pragma unroll
+            for (int c = 0; c < C; ++c) res[c] = Elem<T>::acc(res[c], w[idx], rows[idx][c]);
+        }
     }
     store_row<T, C>(out, res);
 
