@@ -193,7 +193,7 @@ def run_ours(args):
     scene, cascade, grid, bits, thresh = cases.scene_bitfield(1.0)
     use_graph = (not args.no_graph) and (world == 1 or os.environ.get("FOC_GRAPH_DP", "1") == "1")
     tr = Trainer(bound=1.0, density_grid=torch.from_numpy(grid), device=dev, seed=0, fused=not args.no_fused, use_graph=use_graph,
-                 optimizer="torch" if args.torch_optim else "fused")
+                 optimizer="torch" if args.torch_optim else "fused", pipeline=args.pipeline)
     params = [p for p in tr.model.parameters()]
     if world > 1:                                   # data-parallel: identical replicas, gradients all-reduced every step
         from focnerf_b200 import dist as fdist
@@ -230,6 +230,7 @@ def run_ours(args):
     e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
     e0.record()
     loop(args.steps, False, 100)
+    tr.flush()                                      # the pipelined step defers each optimiser sweep into the next step: apply the last one
     e1.record()
     sync_all()
     if prof:
@@ -247,6 +248,7 @@ def run_ours(args):
     t0 = torch.cuda.Event(enable_timing=True); t1 = torch.cuda.Event(enable_timing=True)
     t0.record()
     loop(args.steps, True, 300)
+    tr.flush()
     t1.record()
     sync_all()
     ms_e2e = torch.tensor([t0.elapsed_time(t1)], device=dev)
@@ -377,6 +379,7 @@ if __name__ == "__main__":
     ap.add_argument("--warmup", type=int, default=8)
     ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
     ap.add_argument("--no-graph", action="store_true", help="launch the step eagerly instead of replaying a CUDA graph")
+    ap.add_argument("--pipeline", action="store_true", help="defer each optimiser sweep into the next step's graph, beside the march")
     ap.add_argument("--torch-optim", action="store_true", help="torch.optim.Adam + GradScaler instead of the fused ScaledAdam")
     ap.add_argument("--no-fused", action="store_true", help="field network through the unfused operator modules")
     a = ap.parse_args()

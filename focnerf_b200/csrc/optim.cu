@@ -103,10 +103,7 @@ __global__ void __launch_bounds__(kThreads) k_adam_step(const __grid_constant__ 
                                                         float eps, const float* __restrict__ scale, const float* __restrict__ found_inf,
                                                         const int32_t* __restrict__ step) {
     pdl_sync();
-    const int ti = find_tensor(L, blockIdx.x);
-    const FocAdamTensor& T = L.t[ti];
-    const uint64_t base = (uint64_t)(blockIdx.x - L.block_start[ti]) * kPerBlock;
-    const bool skip = (found_inf != nullptr && *found_inf != 0.0f) || T.grad == nullptr;
+    const bool bad = found_inf != nullptr && *found_inf != 0.0f;
     __shared__ float s_step_size, s_rsqrt_bc2, s_inv_scale;
     if (threadIdx.x == 0) {
         const double t = (double)(*step + 1);
@@ -117,6 +114,13 @@ __global__ void __launch_bounds__(kThreads) k_adam_step(const __grid_constant__ 
     }
     __syncthreads();
     const float step_size = s_step_size, rs = s_rsqrt_bc2, inv_scale = s_inv_scale, w1 = 1.0f - beta1, w2 = 1.0f - beta2;
+    // block-stride over the 4096-parameter blocks (the grid covers them all by default; a smaller persistent grid was
+    // measured slower: 2 CTAs per SM do not keep enough loads in flight for the HBM-bound sweep)
+    for (uint32_t vb = blockIdx.x; vb < L.block_start[kMaxTensors]; vb += gridDim.x) {
+    const int ti = find_tensor(L, vb);
+    const FocAdamTensor& T = L.t[ti];
+    const uint64_t base = (uint64_t)(vb - L.block_start[ti]) * kPerBlock;
+    const bool skip = bad || T.grad == nullptr;
     #pragma unroll
     for (int u = 0; u < kUnroll; ++u) {
         const uint64_t i = base + ((uint64_t)u * kThreads + threadIdx.x) * kVec;
@@ -167,6 +171,7 @@ __global__ void __launch_bounds__(kThreads) k_adam_step(const __grid_constant__ 
                 else for (int k = 0; k < 4 && i + k < T.n; ++k) gp[k] = 0.f;
             }
         }
+    }
     }
 }
 
@@ -223,7 +228,8 @@ FOC_API int foc_adam_step(const FocAdamTensor* tensors, int count, const float* 
                           const float* scale, const float* found_inf, const int32_t* step, void* stream) {
     AdamList L;
     if (int rc = make_list(tensors, count, L)) return rc;
-    foc::launch(k_adam_step, L.block_start[kMaxTensors], kThreads, 0, reinterpret_cast<cudaStream_t>(stream), L, lr, beta1, beta2, eps, scale, found_inf, step);
+    const uint32_t adam_grid = L.block_start[kMaxTensors];
+    foc::launch(k_adam_step, adam_grid, kThreads, 0, reinterpret_cast<cudaStream_t>(stream), L, lr, beta1, beta2, eps, scale, found_inf, step);
     FOC_LAUNCH_CHECK(); return 0;
 }
 

@@ -25,8 +25,12 @@ class ScaledAdam:
     MAX_TENSORS = 8                    # per launch (csrc/optim.cu kMaxTensors)
 
     def __init__(self, params, lr=1e-2, betas=(0.9, 0.99), eps=1e-15, loss_scaling=True, init_scale=65536.0, growth_factor=2.0,
-                 backoff_factor=0.5, growth_interval=2000):
+                 backoff_factor=0.5, growth_interval=2000, persistent_grads=False):
         self.params = [p for p in params]
+        # persistent_grads: every gradient tensor (param.grad included) is zeroed by the step kernel after it is consumed and
+        # zero_grad() becomes a no-op, so gradients live at fixed addresses -- what a CUDA graph that applies the PREVIOUS
+        # step's gradients needs (Trainer's pipelined step)
+        self.persistent_grads = bool(persistent_grads)
         if not self.params:
             raise ValueError("ScaledAdam: no parameters")
         for p in self.params:
@@ -76,6 +80,8 @@ class ScaledAdam:
         self.lr.fill_(float(lr))
 
     def zero_grad(self, set_to_none=True):
+        if self.persistent_grads:
+            return
         for p in self.params:
             if p.grad is not None:
                 if set_to_none:
@@ -93,9 +99,11 @@ class ScaledAdam:
             if g is None:
                 continue
             if g.dtype not in (torch.float32, torch.float16) or not g.is_contiguous():
+                if self.persistent_grads:
+                    raise RuntimeError("ScaledAdam(persistent_grads=True) needs contiguous fp32 / fp16 gradients")
                 g = g.contiguous().float()
             rows.append(FocAdamTensor(p.data_ptr(), m.data_ptr(), v.data_ptr(), g.data_ptr(), 0 if s16 is None else s16.data_ptr(), p.numel(),
-                                      1 if g.dtype == torch.float16 else 0, 1 if g16 is not None else 0))
+                                      1 if g.dtype == torch.float16 else 0, 1 if (g16 is not None or self.persistent_grads) else 0))
         return rows
 
     @torch.no_grad()

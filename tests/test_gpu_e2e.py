@@ -89,12 +89,13 @@ def test_forward_fused_matches_forward():
         assert rel < 2e-2, rel                              # fp16 gradient rounding (different add order in the unfused cat/slice)
 
 
-def test_graph_step_trains_and_tracks_counter():
+@pytest.mark.parametrize("pipeline", [False, True])
+def test_graph_step_trains_and_tracks_counter(pipeline):
     """use_graph=True: the step replayed as one CUDA graph still trains, keeps the step_counter ring current, and
-    re-captures when the sample-buffer quantum changes."""
+    re-captures when the sample-buffer quantum changes.  pipeline=True defers each optimiser sweep into the next replay."""
     from focnerf_b200.trainer import Trainer
     scene, cascade, grid, bits, thresh = cases.scene_bitfield(1.0)
-    tr = Trainer(bound=1.0, density_grid=torch.from_numpy(grid), use_graph=True)
+    tr = Trainer(bound=1.0, density_grid=torch.from_numpy(grid), use_graph=True, pipeline=pipeline)
     losses, captured = [], set()
     for it in range(80):
         o, d = cases.camera_rays(4096, 100 + it)
@@ -107,11 +108,19 @@ def test_graph_step_trains_and_tracks_counter():
             tr.update_mean_count()
     assert tr._graph is not None and len(captured) >= 1
     assert all(np.isfinite(losses)), losses
+    # pipelined replay: the last step's gradients are still pending; flush() applies them exactly once
+    assert tr._pending == pipeline
+    steps_before = int(tr.optimizer.step_count.item())
+    tr.flush()
+    assert not tr._pending and int(tr.optimizer.step_count.item()) == steps_before + (1 if pipeline else 0)
+    tr.flush()
+    assert int(tr.optimizer.step_count.item()) == 80                # one optimiser step per train_step, none lost or doubled
     assert np.mean(losses[-10:]) < 0.5 * np.mean(losses[:5]), (losses[:5], losses[-10:])
     cnt = tr.step_counter[:, 0].cpu().numpy()
     assert (cnt > 0).all()
     # a forced quantum change re-captures
     tr.mean_count = max(captured) + 3 * Trainer.GRAPH_QUANTUM
+    tr.train_step(o, d, gt)                                          # (after the flush above: an eager step that leaves gradients pending)
     tr.train_step(o, d, gt)
     assert tr._graph[0][0] > max(captured)
 
