@@ -94,9 +94,17 @@ ALG_BYTES = {
     "foc_grid_encode_backward": 12 + 64 + 512,         # coords + fp16 grad + 16 x 8 x 4 B atomic targets
     "foc_composite_rays_train_forward": 24,
     "foc_composite_rays_train_backward": 24 + 16,
+    "foc_composite_mse_forward": 24,
+    "foc_composite_mse_backward": 24 + 16,
     "foc_march_rays_train": 32,
 }
 TIMED = list(ALG_BYTES) + ["foc_ffmlp_forward", "foc_ffmlp_backward"]
+# DRAM bytes (dram__bytes_read.sum + dram__bytes_write.sum) per CALL of each entry point, from the round-1 `ncu --set full`
+# capture of this same workload (profiles/r1_kernels.md; two-kernel entry points summed, two-net entry points averaged)
+NCU_TRAFFIC = {
+    "foc_ffmlp_backward": 78.8e6, "foc_ffmlp_forward": 16.8e6, "foc_grid_encode_backward": 42.9e6, "foc_grid_encode_forward": 21.5e6,
+    "foc_march_rays_train": 1.4e6, "foc_composite_rays_train_forward": 3.9e6, "foc_composite_rays_train_backward": 3.9e6,
+}
 
 
 def cpu_baseline(scene, bits, cascade, rays=1024):
@@ -326,6 +334,8 @@ def run_ours(args):
         achieved = flops / (kt.mean_ms(top) * 1e-3) / 1e12
         roof = {"kernel": top, "bound": "tensor", "achieved": achieved, "peak": tc, "unit": "TFLOP/s", "frac": achieved / tc, "traffic": None,
                 "peak_source": how, "ms_per_launch": kt.mean_ms(top)}
+    roof["traffic"] = NCU_TRAFFIC.get(top)
+    roof["traffic_source"] = "profiles/r1_kernels.md (ncu --set full, DRAM bytes per call)"
     roof["ms_per_step_by_entry_point"] = {k: round(v, 4) for k, v in sorted(per.items(), key=lambda kv: -kv[1])}
     out = {
         "metric": "train rays/s", "value": total_rays / (ms * 1e-3), "unit": "rays/s", "n_gpus": world, "steps": args.steps,
