@@ -145,24 +145,46 @@ def psnr_run(make_trainer, scene, dev, steps, pool_dev):
 
 
 def render_bench(render_fn, dev, rank, world, frames=3, H=800, W=800):
-    """configs[2]: 800x800 inference render (march_rays / composite_rays loop with early termination), ray tiles sharded
-    over the ranks, tiles gathered once per frame.  -> {"value": Mrays/s whole job, ...} (same dict on every rank)."""
+    """configs[2]: 800x800 inference render (march_rays / composite_rays loop with early termination), 128-ray blocks dealt
+    round-robin to the ranks, gathered once per frame.  -> {"value": Mrays/s whole job, ...} (same dict on every rank)."""
     import torch
     import torch.distributed as dist
     from focnerf_b200 import synthetic
-    from focnerf_b200.dist import gather_tiles, ray_tile
+    from focnerf_b200.dist import cyclic_tile, gather_cyclic
     pose = synthetic.ring_poses(8, radius=2.2, seed=123)[3]
     o, d = synthetic.get_rays(pose, synthetic.intrinsics(H, W), H, W)
     n = H * W
-    s, e = ray_tile(n, rank, world)
-    o, d = o[s:e].contiguous().to(dev), d[s:e].contiguous().to(dev)
+    if world > 1:                                    # 128-ray blocks dealt round-robin: balances the samples, not just the rays
+        idx = cyclic_tile(n, rank, world)
+        o, d = o[idx], d[idx]
+    o, d = o.contiguous().to(dev), d.contiguous().to(dev)
+
+    buf = {"out": None}
+    brk = os.environ.get("FOC_RENDER_BREAKDOWN") == "1"
 
     def frame():
+        t0 = time.perf_counter()
         image, depth, ws = render_fn(o, d)
         out = torch.cat([image, depth.unsqueeze(-1), ws.unsqueeze(-1)], -1)
-        return gather_tiles(out, n) if world > 1 else out
+        if brk:
+            torch.cuda.synchronize(); t1 = time.perf_counter()
+        if world > 1:
+            out, buf["out"] = gather_cyclic(out, n, out=buf["out"])
+        if brk:
+            torch.cuda.synchronize(); t2 = time.perf_counter()
+            if rank == 0:
+                print(f"[render breakdown] render {1e3 * (t1 - t0):.2f} ms, gather {1e3 * (t2 - t1):.2f} ms", file=sys.stderr)
+        return out
 
     frame()                                          # warm-up (allocator, autotune-free: just first-touch)
+    if brk:                                          # one profiled frame: device time per kernel, to stderr (rank 0 prints)
+        from torch.profiler import ProfilerActivity, profile
+        torch.cuda.synchronize()
+        with profile(activities=[ProfilerActivity.CUDA, ProfilerActivity.CPU]) as prof:
+            frame()
+            torch.cuda.synchronize()
+        if rank == 0:
+            print(prof.key_averages().table(sort_by="cuda_time_total", row_limit=30, max_name_column_width=60), file=sys.stderr)
     if world > 1:
         dist.barrier()
     torch.cuda.synchronize()
@@ -200,14 +222,11 @@ def run_ours(args):
     dev = torch.device("cuda", local)
     scene, cascade, grid, bits, thresh = cases.scene_bitfield(1.0)
     use_graph = (not args.no_graph) and (world == 1 or os.environ.get("FOC_GRAPH_DP", "1") == "1")
+    # N > 1: data parallel.  Default: gradient exchange fused into the optimiser over NVLink peer memory (csrc/peer.cu);
+    # FOC_DP=nccl selects the all-reduce + replicated sweep it replaces (A/B)
+    dp = None if world == 1 else os.environ.get("FOC_DP", "peer")
     tr = Trainer(bound=1.0, density_grid=torch.from_numpy(grid), device=dev, seed=0, fused=not args.no_fused, use_graph=use_graph,
-                 optimizer="torch" if args.torch_optim else "fused", pipeline=args.pipeline)
-    params = [p for p in tr.model.parameters()]
-    if world > 1:                                   # data-parallel: identical replicas, gradients all-reduced every step
-        from focnerf_b200 import dist as fdist
-        fdist.broadcast_parameters(params)
-        tr.optimizer.refresh_shadows() if hasattr(tr.optimizer, "refresh_shadows") else None
-        tr.grad_sync = lambda: fdist.all_reduce_mean(tr.grad_tensors())
+                 optimizer="torch" if args.torch_optim else "fused", pipeline=args.pipeline, data_parallel=dp)
     pool_dev, pool_host = make_pool(scene, POOL, RAYS_PER_GPU, 1000 + 7919 * rank, dev)
     stage = [torch.empty_like(t) for t in pool_dev[0]]
 

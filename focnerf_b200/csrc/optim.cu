@@ -29,6 +29,11 @@ struct AdamList {
     uint32_t block_start[kMaxTensors + 1];                         // CTA ranges of the tensors, concatenated
     int count;
 };
+// data-parallel sweep (peer.cu): tensor `tensor`'s fp16 copy goes to every rank's table instead of the local one only
+struct PeerShadow {
+    uint16_t* base[FOC_MAX_PEERS];
+    int world, tensor;
+};
 
 __device__ __forceinline__ int find_tensor(const AdamList& L, uint32_t block) {
     int i = 0;
@@ -99,9 +104,10 @@ __global__ void __launch_bounds__(kThreads) k_adam_nonfinite(const __grid_consta
     if (!ok) *found_inf = 1.0f;
 }
 
+template <bool PEERS>
 __global__ void __launch_bounds__(kThreads) k_adam_step(const __grid_constant__ AdamList L, const float* __restrict__ lr_p, float beta1, float beta2,
                                                         float eps, const float* __restrict__ scale, const float* __restrict__ found_inf,
-                                                        const int32_t* __restrict__ step) {
+                                                        const int32_t* __restrict__ step, const __grid_constant__ PeerShadow PS) {
     pdl_sync();
     const bool bad = found_inf != nullptr && *found_inf != 0.0f;
     __shared__ float s_step_size, s_rsqrt_bc2, s_inv_scale;
@@ -149,14 +155,18 @@ __global__ void __launch_bounds__(kThreads) k_adam_step(const __grid_constant__ 
                 *reinterpret_cast<float4*>(T.param + i) = make_float4(p[0], p[1], p[2], p[3]);
                 *reinterpret_cast<float4*>(T.exp_avg + i) = make_float4(m[0], m[1], m[2], m[3]);
                 *reinterpret_cast<float4*>(T.exp_avg_sq + i) = make_float4(v[0], v[1], v[2], v[3]);
-                if (T.shadow16) {
-                    const __half2 a = __floats2half2_rn(p[0], p[1]), b = __floats2half2_rn(p[2], p[3]);
-                    *reinterpret_cast<uint2*>(T.shadow16 + i) = make_uint2(*reinterpret_cast<const uint32_t*>(&a), *reinterpret_cast<const uint32_t*>(&b));
-                }
+                const __half2 a = __floats2half2_rn(p[0], p[1]), b = __floats2half2_rn(p[2], p[3]);
+                const uint2 packed = make_uint2(*reinterpret_cast<const uint32_t*>(&a), *reinterpret_cast<const uint32_t*>(&b));
+                if (PEERS && ti == PS.tensor) {
+                    #pragma unroll
+                    for (int r = 0; r < FOC_MAX_PEERS; ++r) if (r < PS.world) *reinterpret_cast<uint2*>(PS.base[r] + i) = packed;
+                } else if (T.shadow16) *reinterpret_cast<uint2*>(T.shadow16 + i) = packed;
             } else {
                 for (int k = 0; k < 4 && i + k < T.n; ++k) {
                     T.param[i + k] = p[k]; T.exp_avg[i + k] = m[k]; T.exp_avg_sq[i + k] = v[k];
-                    if (T.shadow16) reinterpret_cast<__half*>(T.shadow16)[i + k] = __float2half_rn(p[k]);
+                    const __half h = __float2half_rn(p[k]);
+                    if (PEERS && ti == PS.tensor) { for (int r = 0; r < PS.world; ++r) reinterpret_cast<__half*>(PS.base[r])[i + k] = h; }
+                    else if (T.shadow16) reinterpret_cast<__half*>(T.shadow16)[i + k] = h;
                 }
             }
         }
@@ -173,6 +183,7 @@ __global__ void __launch_bounds__(kThreads) k_adam_step(const __grid_constant__ 
         }
     }
     }
+    if (PEERS) __threadfence_system();             // the pushed fp16 copies must be visible to the peers before the barrier that follows
 }
 
 // torch.amp.GradScaler.update() (torch/amp/grad_scaler.py, amp_update_scale_cuda_kernel) + the step counter
@@ -229,7 +240,25 @@ FOC_API int foc_adam_step(const FocAdamTensor* tensors, int count, const float* 
     AdamList L;
     if (int rc = make_list(tensors, count, L)) return rc;
     const uint32_t adam_grid = L.block_start[kMaxTensors];
-    foc::launch(k_adam_step, adam_grid, kThreads, 0, reinterpret_cast<cudaStream_t>(stream), L, lr, beta1, beta2, eps, scale, found_inf, step);
+    PeerShadow ps{};
+    foc::launch(k_adam_step<false>, adam_grid, kThreads, 0, reinterpret_cast<cudaStream_t>(stream), L, lr, beta1, beta2, eps, scale, found_inf, step, ps);
+    FOC_LAUNCH_CHECK(); return 0;
+}
+
+FOC_API int foc_adam_step_peers(const FocAdamTensor* tensors, int count, const float* lr, float beta1, float beta2, float eps,
+                                const float* scale, const float* found_inf, const int32_t* step, int peer_tensor, int world,
+                                uint16_t* const* peer_shadow16, void* stream) {
+    AdamList L;
+    if (int rc = make_list(tensors, count, L)) return rc;
+    if (world < 1 || world > FOC_MAX_PEERS || peer_tensor < 0 || peer_tensor >= count || peer_shadow16 == nullptr) return FOC_ERR_UNSUPPORTED;
+    PeerShadow ps{};
+    ps.world = world; ps.tensor = peer_tensor;
+    for (int r = 0; r < world; ++r) {
+        if (peer_shadow16[r] == nullptr || (reinterpret_cast<uintptr_t>(peer_shadow16[r]) & 15u)) return FOC_ERR_UNSUPPORTED;
+        ps.base[r] = peer_shadow16[r];
+    }
+    foc::launch(k_adam_step<true>, L.block_start[kMaxTensors], kThreads, 0, reinterpret_cast<cudaStream_t>(stream), L, lr, beta1, beta2, eps, scale,
+                found_inf, step, ps);
     FOC_LAUNCH_CHECK(); return 0;
 }
 

@@ -169,7 +169,7 @@ class GridEncoder(nn.Module):
         std = 1e-4
         self.embeddings.data.uniform_(-std, std)
 
-    def enable_fp16_side_buffers(self):
+    def enable_fp16_side_buffers(self, grad16=None, shadow16=None):
         """Not in the reference.  Allocates (grad16, shadow16), both [offset, C] half: under fp16 autocast the forward then
         gathers from `shadow16` (no per-step `.to(half)` of the 49 MB table) and the backward scatters into `grad16`
         (no per-step zeros_like + half->float copy); `embeddings.grad` stays None.  The owner of the buffers -- an
@@ -177,8 +177,16 @@ class GridEncoder(nn.Module):
         grad16 after consuming it."""
         if self.level_dim % 2 != 0:
             raise RuntimeError("fp16 side buffers need an even level_dim (the fp16 path of the encoder, grid.py:43)")
-        self._shadow16 = self.embeddings.detach().to(torch.half).contiguous()
-        self._grad16 = torch.zeros_like(self._shadow16)
+        for t in (grad16, shadow16):                               # caller-owned storage (e.g. peer-visible memory, optim.PeerAdam)
+            if t is not None and (t.dtype != torch.half or tuple(t.shape) != tuple(self.embeddings.shape) or not t.is_contiguous()):
+                raise RuntimeError("fp16 side buffers must be contiguous half tensors of the table's shape")
+        if shadow16 is None:
+            shadow16 = torch.empty_like(self.embeddings, dtype=torch.half)
+        shadow16.copy_(self.embeddings.detach())
+        if grad16 is None:
+            grad16 = torch.empty_like(shadow16)
+        grad16.zero_()
+        self._shadow16, self._grad16 = shadow16, grad16
         return self._grad16, self._shadow16
 
     def __repr__(self):

@@ -148,3 +148,133 @@ class ScaledAdam:
             s16 = self._side.get(id(p), (None, None))[1]
             if s16 is not None:
                 s16.copy_(p.detach())
+
+
+class FocDpReduce(ctypes.Structure):
+    """include/foc_b200.h: struct FocDpReduce"""
+    _fields_ = [("world", ctypes.c_int32), ("rank", ctypes.c_int32), ("grad16", ctypes.c_void_p * 8), ("shard_start", ctypes.c_uint64),
+                ("shard_n", ctypes.c_uint64), ("reduced", ctypes.c_void_p), ("tail", ctypes.c_void_p * 8), ("tail_n", ctypes.c_uint64),
+                ("reduced_tail", ctypes.c_void_p), ("inf_flag", ctypes.c_void_p), ("shard_blocks", ctypes.c_uint32)]
+
+
+class PeerAdam(ScaledAdam):
+    """ScaledAdam for data-parallel training on one NVSwitch node, with the gradient exchange fused into the optimiser over
+    peer memory instead of an NCCL all-reduce in front of it (csrc/peer.cu has the protocol):
+
+    * `table` (the hash grid, 99.9 % of the parameters) is SHARDED: rank r keeps fp32 master values and Adam moments current
+      for elements [r * shard, (r + 1) * shard) only, pulls that slice of every rank's fp16 gradient table, and pushes the
+      fp16 copy of the updated slice into every rank's table.  The forward / backward only ever touch the fp16 copies, which
+      are complete on every rank.  `sync_master()` (a collective) completes the fp32 tensors, e.g. before a checkpoint.
+    * every other parameter (the MLP weights, ~10 k values) is replicated: each rank averages all ranks' gradients in the
+      same order and applies the same update -- bit-identical replicas without a broadcast.
+
+    The table's fp16 gradient / parameter copies live in a PeerArena; hand them to the encoder with
+    `encoder.enable_fp16_side_buffers(opt.grad16, opt.shadow16)` (Trainer does)."""
+    BLOCK = 4096                       # csrc/optim.cu kPerBlock: shard boundaries are multiples of it
+
+    def __init__(self, params, table, group=None, **kw):
+        import torch.distributed as dist
+        from .peer import PeerArena
+        kw.pop("persistent_grads", None)
+        super().__init__(params, **kw)
+        if not any(table is p for p in self.params):
+            raise ValueError("PeerAdam: `table` must be one of the parameters")
+        self.group, self.table = group, table
+        self.world, self.rank = dist.get_world_size(group), dist.get_rank(group)
+        n = table.numel()
+        if n % 8:
+            raise RuntimeError("PeerAdam: the sharded table must hold a multiple of 8 values")
+        per = -(-n // self.world)
+        per = -(-per // self.BLOCK) * self.BLOCK
+        self.shard_start = min(self.rank * per, n)
+        self.shard_n = min(self.shard_start + per, n) - self.shard_start
+        self.shard_len = per
+        self.tail = [p for p in self.params if p is not table]
+        self.tail_off, off = [], 0
+        for p in self.tail:
+            self.tail_off.append(off)
+            off += -(-p.numel() // 4) * 4
+        self.tail_n = off
+        g_bytes = -(-n * 2 // 256) * 256
+        t_bytes = -(-max(self.tail_n, 4) * 4 // 256) * 256
+        self.arena = PeerArena(g_bytes + t_bytes + g_bytes, group=group, device=table.device)
+        self._off_grad, self._off_tail, self._off_shadow = 0, g_bytes, g_bytes + t_bytes
+        self.grad16 = self.arena.tensor(self._off_grad, n, torch.float16).view(table.shape)
+        self.tail_grad = self.arena.tensor(self._off_tail, max(self.tail_n, 4), torch.float32)
+        self._grad_span = self.arena.tensor(self._off_grad, (g_bytes + t_bytes) // 4, torch.float32)     # grad16 + tail, zeroed in one fill
+        self.shadow16 = self.arena.tensor(self._off_shadow, n, torch.float16).view(table.shape)
+        self.attach(table, grad16=self.grad16, shadow16=self.shadow16)
+        dev = table.device
+        self.reduced = torch.zeros(max(self.shard_n, 4), dtype=torch.float32, device=dev)
+        self.reduced_tail = torch.zeros(max(self.tail_n, 4), dtype=torch.float32, device=dev)
+        a = self.arena
+        self._reduce_args = FocDpReduce(
+            self.world, self.rank, (ctypes.c_void_p * 8)(*[a.address(r, self._off_grad) for r in range(self.world)]), self.shard_start, self.shard_n,
+            self.reduced.data_ptr(), (ctypes.c_void_p * 8)(*[a.address(r, self._off_tail) for r in range(self.world)]), self.tail_n,
+            self.reduced_tail.data_ptr(), a.state.data_ptr() + 4, 0)
+        self._peer_shadow = (ctypes.c_void_p * 8)(*[a.address(r, self._off_shadow + 2 * self.shard_start) for r in range(self.world)])
+        dist.barrier(group=group)
+
+    def grad_tensors(self):
+        return []                      # nothing for an NCCL all-reduce: step() exchanges the gradients itself
+
+    def _descriptors(self):
+        rows = []
+        s, n = self.shard_start, self.shard_n
+        ti = [i for i, p in enumerate(self.params) if p is self.table][0]
+        if n > 0:
+            flat = lambda t: t.view(-1)[s:s + n]
+            rows.append(FocAdamTensor(flat(self.table.data).data_ptr(), flat(self.exp_avg[ti]).data_ptr(), flat(self.exp_avg_sq[ti]).data_ptr(),
+                                      self.reduced.data_ptr(), 0, n, 0, 0))
+        for p, off in zip(self.tail, self.tail_off):
+            i = [k for k, q in enumerate(self.params) if q is p][0]
+            rows.append(FocAdamTensor(p.data_ptr(), self.exp_avg[i].data_ptr(), self.exp_avg_sq[i].data_ptr(),
+                                      self.reduced_tail.data_ptr() + 4 * off, 0, p.numel(), 0, 0))
+        return rows
+
+    @torch.no_grad()
+    def step(self):
+        l, st = lib(), stream()
+        for p, off in zip(self.tail, self.tail_off):           # stage the small gradients where the peers can read them
+            if p.grad is not None:
+                self.tail_grad[off:off + p.numel()].copy_(p.grad.reshape(-1))
+        fi = None if self.scale is None else self.found_inf
+        self.arena.barrier()                                   # every rank's gradients are complete
+        check(l.foc_dp_reduce(ctypes.byref(self._reduce_args), st), "dp_reduce")
+        self.arena.barrier(fi)                                 # every rank has pulled what it needs; non-finite flags exchanged
+        self._grad_span.zero_()
+        rows = self._descriptors()
+        arr = (FocAdamTensor * len(rows))(*rows)
+        b1, b2 = self.betas
+        sc = None if self.scale is None else self.scale.data_ptr()
+        fip = None if fi is None else fi.data_ptr()
+        if self.shard_n > 0:
+            check(l.foc_adam_step_peers(ctypes.cast(arr, ctypes.c_void_p), len(rows), self.lr.data_ptr(), b1, b2, self.eps, sc, fip,
+                                        self.step_count.data_ptr(), 0, self.world, ctypes.cast(self._peer_shadow, ctypes.c_void_p), st), "adam_step_peers")
+        else:
+            check(l.foc_adam_step(ctypes.cast(arr, ctypes.c_void_p), len(rows), self.lr.data_ptr(), b1, b2, self.eps, sc, fip,
+                                  self.step_count.data_ptr(), st), "adam_step")
+        self.arena.barrier()                                   # every shard of the fp16 table has arrived
+        check(l.foc_scaler_update(sc, self.growth_tracker.data_ptr(), fip, self.step_count.data_ptr(), self.growth_factor, self.backoff_factor,
+                                  self.growth_interval, st), "scaler_update")
+
+    @torch.no_grad()
+    def sync_master(self):
+        """Collective: complete the sharded fp32 tensors (table parameters and both Adam moments) on every rank."""
+        import torch.distributed as dist
+        ti = [i for i, p in enumerate(self.params) if p is self.table][0]
+        n, per = self.table.numel(), self.shard_len
+        for t in (self.table.data, self.exp_avg[ti], self.exp_avg_sq[ti]):
+            flat = t.view(-1)
+            mine = flat.new_zeros(per)
+            mine[:self.shard_n] = flat[self.shard_start:self.shard_start + self.shard_n]
+            parts = [flat.new_empty(per) for _ in range(self.world)]
+            dist.all_gather(parts, mine, group=self.group)
+            flat.copy_(torch.cat(parts)[:n])
+
+    def state_dict(self):
+        self.sync_master()
+        return super().state_dict()
+
+    def refresh_shadows(self):
+        self.shadow16.copy_(self.table.detach())

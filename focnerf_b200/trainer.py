@@ -13,7 +13,8 @@ from .network import NeRFNetwork
 
 class Trainer:
     def __init__(self, bound=1.0, density_grid=None, density_thresh=10.0, min_near=0.2, dt_gamma=0.0, max_steps=1024,
-                 lr=1e-2, fp16=True, device="cuda", grid_size=128, seed=0, fused=True, use_graph=False, optimizer="fused", pipeline=False):
+                 lr=1e-2, fp16=True, device="cuda", grid_size=128, seed=0, fused=True, use_graph=False, optimizer="fused", pipeline=False,
+                 data_parallel=None, group=None):
         if not torch.cuda.is_available():
             raise RuntimeError("focnerf_b200.Trainer needs a CUDA device (there is no CPU path)")
         import math
@@ -42,22 +43,43 @@ class Trainer:
         # gradients that no sweep has consumed yet; flush() applies them.  Measured on B200: 0.441 ms vs 0.443 ms per step --
         # the sweep saturates HBM/L2 and the latency-bound march slows down beside it by as much as the overlap saves, so the
         # default keeps the plain order (and parameters that are always current).
-        self.pipeline = bool(pipeline) and optimizer == "fused"
+        self.pipeline = bool(pipeline) and optimizer == "fused" and data_parallel != "peer"
+        # data_parallel (needs an initialised torch.distributed group, one process per GPU): every rank marches its own rays,
+        # the replicas start from rank 0's parameters and see the mean gradient every step.
+        #   "peer": the exchange is fused into the optimiser over NVLink peer memory (optim.PeerAdam, csrc/peer.cu) --
+        #           sharded table sweep, no NCCL on the data path;   "nccl": all-reduce of the gradient tensors, then the
+        #           replicated sweep (the baseline the peer path is measured against)
+        if data_parallel not in (None, "peer", "nccl"):
+            raise ValueError("data_parallel must be None, 'peer' or 'nccl'")
+        if data_parallel == "peer" and not (optimizer == "fused" and fp16):
+            data_parallel = "nccl"
+        self.data_parallel = data_parallel
+        if data_parallel is not None:
+            from . import dist as fdist
+            fdist.broadcast_parameters(list(self.model.parameters()), group=group)
         self._pending = False
         self._side_stream, self._capture_stream = None, None
         # optimizer="fused": ScaledAdam (csrc/optim.cu) with the encoder's fp16 side buffers; "torch": the reference's
         # torch.optim.Adam + torch.amp.GradScaler pair, kept for A/B checks
         if optimizer == "fused":
-            from .optim import ScaledAdam
-            self.optimizer = ScaledAdam(self.model.parameters(), lr=lr, betas=(0.9, 0.99), eps=1e-15, loss_scaling=fp16,
-                                        persistent_grads=pipeline)
-            if fp16:
-                g16, s16 = self.model.encoder.enable_fp16_side_buffers()
-                self.optimizer.attach(self.model.encoder.embeddings, grad16=g16, shadow16=s16)
+            from .optim import PeerAdam, ScaledAdam
+            if data_parallel == "peer":
+                self.optimizer = PeerAdam(self.model.parameters(), table=self.model.encoder.embeddings, group=group, lr=lr, betas=(0.9, 0.99),
+                                          eps=1e-15, loss_scaling=True)
+                self.model.encoder.enable_fp16_side_buffers(self.optimizer.grad16, self.optimizer.shadow16)
+            else:
+                self.optimizer = ScaledAdam(self.model.parameters(), lr=lr, betas=(0.9, 0.99), eps=1e-15, loss_scaling=fp16,
+                                            persistent_grads=self.pipeline)
+                if fp16:
+                    g16, s16 = self.model.encoder.enable_fp16_side_buffers()
+                    self.optimizer.attach(self.model.encoder.embeddings, grad16=g16, shadow16=s16)
             self.scaler = None
         else:
             self.optimizer = torch.optim.Adam(self.model.get_params(lr), betas=(0.9, 0.99), eps=1e-15, fused=True, capturable=use_graph)
             self.scaler = torch.amp.GradScaler("cuda", enabled=fp16)
+        if data_parallel == "nccl":
+            from . import dist as fdist
+            self.grad_sync = lambda: fdist.all_reduce_mean(self.grad_tensors(), group=group)
 
     def set_density_grid(self, density_grid, density_thresh=10.0):
         """density_grid [cascade, H^3] (Morton order) -> bitfield, as update_extra_state does (renderer.py:529-531)."""
@@ -205,7 +227,9 @@ class Trainer:
         self.model.train()
         if self.use_graph and self.mean_count > 0:
             return self._graph_step(rays_o, rays_d, gt_rgb, bg_color)
-        return self._step_body(rays_o, rays_d, gt_rgb, bg_color)
+        # detached: a caller holding on to the loss must not keep this step's autograd graph (and its AccumulateGrad nodes,
+        # bound to the eager stream) alive into a later graph capture
+        return self._step_body(rays_o, rays_d, gt_rgb, bg_color).detach()
 
     # ---- CUDA-graph replay of the step -------------------------------------------------------------------------------
     GRAPH_QUANTUM = 16384          # sample-buffer sizes are rounded up to this, so the captured shapes rarely change

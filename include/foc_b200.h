@@ -228,6 +228,48 @@ int foc_adam_step(const FocAdamTensor *tensors, int count, const float *lr, floa
 int foc_scaler_update(float *scale, int32_t *growth_tracker, float *found_inf, int32_t *step, float growth_factor,
                       float backoff_factor, int32_t growth_interval, void *stream);
 
+/* ---------------------------------------------------------------- data-parallel training over NVLink peer memory
+ * No reference counterpart (the reference trains on one GPU; torch DDP would all-reduce every gradient over NCCL and
+ * repeat the whole Adam sweep on every rank).  One process per GPU; every rank owns 1/world of the hash table's fp32
+ * master parameters and Adam moments.  Per step: barrier -> foc_dp_reduce (pull + average this rank's shard of the fp16
+ * table gradients from all peers, deterministic rank order) -> barrier exchanging the non-finite flags ->
+ * foc_adam_step_peers (sweep over the shard, fp16 parameter copy pushed into every peer's table) -> barrier.
+ * See csrc/peer.cu.  All of it is plain kernel launches: CUDA-graph capturable, no host synchronisation. */
+#define FOC_MAX_PEERS 8
+#define FOC_PEER_HANDLE_BYTES 64
+/* peer-visible device memory: cudaMalloc'd (zero-filled), exported as a 64-byte IPC handle that another process of the
+ * same node opens (peer access is enabled on first open).  A process must not open its own handles. */
+int foc_peer_alloc(uint64_t bytes, void **ptr);
+int foc_peer_free(void *ptr);
+int foc_peer_export(void *ptr, uint8_t *handle64);
+int foc_peer_open(const uint8_t *handle64, void **ptr);
+int foc_peer_close(void *ptr);
+typedef struct FocPeerGroup {
+    int32_t world, rank;
+    uint32_t *flags[FOC_MAX_PEERS]; /* every rank's signal pad (>= 24 uint32, zero-initialised), [rank] = the local one */
+    uint32_t *state;                /* local: [0] epoch, [1] non-finite flag of foc_dp_reduce, [2] sticky status (1 = barrier timeout) */
+} FocPeerGroup;
+/* All ranks of the group meet; found_inf != NULL additionally ORs the ranks' state[1] flags into *found_inf (sets 1.0f,
+ * never clears) and resets state[1].  Gives up after ~2 s without progress and sets state[2] instead of hanging. */
+int foc_peer_barrier(const FocPeerGroup *group, float *found_inf, void *stream);
+typedef struct FocDpReduce {
+    int32_t world, rank;
+    const uint16_t *grad16[FOC_MAX_PEERS]; /* every rank's fp16 gradient table (whole table; [rank] = local) */
+    uint64_t shard_start, shard_n;         /* this rank's element range of the table; multiples of 8 */
+    float *reduced;                        /* [shard_n] local: mean over ranks, fp32 */
+    const float *tail[FOC_MAX_PEERS];      /* every rank's flat fp32 gradients of the replicated small tensors */
+    uint64_t tail_n;                       /* multiple of 4 */
+    float *reduced_tail;                   /* [tail_n] local: mean over ranks (computed in full by every rank) */
+    uint32_t *inf_flag;                    /* local: set to 1 when a reduced value is inf / nan (FocPeerGroup.state + 1) */
+    uint32_t shard_blocks;                 /* filled in by the callee */
+} FocDpReduce;
+int foc_dp_reduce(const FocDpReduce *args, void *stream);
+/* foc_adam_step, and additionally tensor `peer_tensor`'s fp16 parameter copy is stored into peer_shadow16[r] (r < world,
+ * already offset to this rank's shard: same indexing as tensors[peer_tensor].shadow16, which may be NULL) */
+int foc_adam_step_peers(const FocAdamTensor *tensors, int count, const float *lr, float beta1, float beta2, float eps,
+                        const float *scale, const float *found_inf, const int32_t *step, int peer_tensor, int world,
+                        uint16_t *const *peer_shadow16, void *stream);
+
 #ifdef __cplusplus
 }
 #endif

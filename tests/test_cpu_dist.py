@@ -21,6 +21,9 @@ def _worker(rank, world, port, out):
     img = torch.arange(n * 3, dtype=torch.float32).view(n, 3)
     full = fd.gather_tiles(img[s:e].clone(), n)
     ok_gather = torch.equal(full, img)
+    idx = fd.cyclic_tile(n, rank, world)
+    frame, _ = fd.gather_cyclic(img[idx].clone(), n)
+    ok_gather = ok_gather and torch.equal(frame, img) and idx.shape[0] == 512
     g32 = torch.full((5,), float(rank + 1))
     g16 = torch.full((7,), float(rank + 1), dtype=torch.float16)
     fd.all_reduce_mean([g32, g16])
@@ -51,3 +54,19 @@ def test_ray_tiles_cover():
                 assert s == pos and e >= s and (s % 128 == 0 or s == n)
                 pos = e
             assert pos == n
+
+
+def test_cyclic_tiles_cover():
+    from focnerf_b200.dist import cyclic_tile
+    for n in (1, 127, 128, 129, 1000, 640000):
+        for world in (1, 2, 4, 8):
+            seen = torch.zeros(n, dtype=torch.int32)
+            lens = set()
+            for r in range(world):
+                idx = cyclic_tile(n, r, world)
+                lens.add(idx.shape[0])
+                seen[idx] += 1
+                blk = idx[::128] // 128
+                assert bool(((blk % world == r) | (idx[::128] == n - 1)).all())
+            assert len(lens) == 1 and int(seen.min()) >= 1
+            assert int((seen[:-1] > 1).sum()) == 0          # only the last ray may repeat (padding)
