@@ -145,8 +145,10 @@ def psnr_run(make_trainer, scene, dev, steps, pool_dev):
 
 
 def render_bench(render_fn, dev, rank, world, frames=3, H=800, W=800):
-    """configs[2]: 800x800 inference render (march_rays / composite_rays loop with early termination), 128-ray blocks dealt
-    round-robin to the ranks, gathered once per frame.  -> {"value": Mrays/s whole job, ...} (same dict on every rank)."""
+    """configs[2]: 800x800 inference render, single pass with early termination.  N > 1: the frame's rays are dealt to the ranks
+    in 128-ray blocks round-robin and every rank's finished rows are stored straight into every rank's frame buffer over NVLink
+    peer memory by the render epilogue (peer.FrameExchange; FOC_RENDER_GATHER=nccl selects all_gather + un-deal copy instead).
+    -> {"value": Mrays/s whole job, ...} (same dict on every rank)."""
     import torch
     import torch.distributed as dist
     from focnerf_b200 import synthetic
@@ -154,7 +156,14 @@ def render_bench(render_fn, dev, rank, world, frames=3, H=800, W=800):
     pose = synthetic.ring_poses(8, radius=2.2, seed=123)[3]
     o, d = synthetic.get_rays(pose, synthetic.intrinsics(H, W), H, W)
     n = H * W
-    if world > 1:                                    # 128-ray blocks dealt round-robin: balances the samples, not just the rays
+    via_peer = world > 1 and os.environ.get("FOC_RENDER_GATHER", "peer") == "peer"
+    ex = None
+    if via_peer:
+        from focnerf_b200.peer import FrameExchange
+        ex = FrameExchange(n, device=dev)
+        idx = ex.my_rays()
+        o, d = o[idx], d[idx]
+    elif world > 1:                                  # 128-ray blocks dealt round-robin: balances the samples, not just the rays
         idx = cyclic_tile(n, rank, world)
         o, d = o[idx], d[idx]
     o, d = o.contiguous().to(dev), d.contiguous().to(dev)
@@ -163,18 +172,22 @@ def render_bench(render_fn, dev, rank, world, frames=3, H=800, W=800):
     brk = os.environ.get("FOC_RENDER_BREAKDOWN") == "1"
 
     def frame():
+        """-> (image [n,3], depth [n], weights_sum [n]) of the WHOLE frame on this rank"""
         t0 = time.perf_counter()
+        if via_peer:
+            return render_fn(o, d, exchange=ex)
         image, depth, ws = render_fn(o, d)
+        if world == 1:
+            return image, depth, ws
         out = torch.cat([image, depth.unsqueeze(-1), ws.unsqueeze(-1)], -1)
         if brk:
             torch.cuda.synchronize(); t1 = time.perf_counter()
-        if world > 1:
-            out, buf["out"] = gather_cyclic(out, n, out=buf["out"])
+        out, buf["out"] = gather_cyclic(out, n, out=buf["out"])
         if brk:
             torch.cuda.synchronize(); t2 = time.perf_counter()
             if rank == 0:
                 print(f"[render breakdown] render {1e3 * (t1 - t0):.2f} ms, gather {1e3 * (t2 - t1):.2f} ms", file=sys.stderr)
-        return out
+        return out[:, :3], out[:, 3], out[:, 4]
 
     frame()                                          # warm-up (allocator, autotune-free: just first-touch)
     if brk:                                          # one profiled frame: device time per kernel, to stderr (rank 0 prints)
@@ -201,7 +214,8 @@ def render_bench(render_fn, dev, rank, world, frames=3, H=800, W=800):
         dist.all_reduce(ms, op=dist.ReduceOp.MAX)
     ms = float(ms.item()) / frames
     return {"metric": "800x800 render Mrays/s", "value": n / (ms * 1e-3) / 1e6, "unit": "Mrays/s", "ms_per_frame": ms, "frames": frames,
-            "rays": n, "scaling": "strong", "coverage": float((out[:, 4] > 0.5).float().mean().item()),
+            "rays": n, "scaling": "strong", "coverage": float((out[2] > 0.5).float().mean().item()),
+            "exchange": "peer-memory stores in the render epilogue" if via_peer else ("all_gather" if world > 1 else None),
             "workload": "configs[2]: one 800x800 test pose of the synthetic scene, T_thresh 1e-4, max_steps 1024, model as trained by the timed steps"}
 
 

@@ -124,6 +124,46 @@ __global__ void __launch_bounds__(kThreads) k_dp_reduce(const __grid_constant__ 
     if (!ok) *a.inf_flag = 1u;
 }
 
+// Epilogue of an inference render (legacy/nerf/renderer.py:369-372: background mix, depth normalisation), fused with the
+// packing into [r, g, b, depth, weights_sum] rows and -- when the frame's rays were dealt to the ranks in kDeal-ray blocks
+// (dist.cyclic_tile: block b -> rank b % world) -- with the exchange: one CTA per local block stages its 128 rows
+// (2560 contiguous bytes of the frame) in shared memory and stores them, 16 bytes per thread, into EVERY rank's frame
+// buffer over peer memory.  Arithmetic = the reference's separate torch ops (no fma contraction).
+constexpr uint32_t kDeal = 128;
+
+__global__ void __launch_bounds__(kDeal) k_render_finish(const float* __restrict__ image, const float* __restrict__ depth, const float* __restrict__ weights_sum,
+                                                         const float* __restrict__ nears, const float* __restrict__ fars, uint32_t N, float bg,
+                                                         int depth_from_first_sample, const __grid_constant__ FocFrameOut o) {
+    __shared__ __align__(16) float rows[kDeal * 5];
+    const uint32_t i = blockIdx.x * kDeal + threadIdx.x;
+    if (i < N) {
+        const float ws = weights_sum[i], near = nears[i], far = fars[i];
+        const float mix = __fmul_rn(__fsub_rn(1.0f, ws), bg);
+        float d = depth[i];
+        if (depth_from_first_sample) d = __fadd_rn(d, __fmul_rn(ws > 0.0f ? near : 0.0f, ws));
+        d = __fdiv_rn(fmaxf(__fsub_rn(d, near), 0.0f), __fsub_rn(far, near));
+        float* r = rows + 5 * threadIdx.x;
+        r[0] = __fadd_rn(image[3 * (size_t)i], mix); r[1] = __fadd_rn(image[3 * (size_t)i + 1], mix); r[2] = __fadd_rn(image[3 * (size_t)i + 2], mix);
+        r[3] = d; r[4] = ws;
+    }
+    __syncthreads();
+    const uint32_t g0 = ((uint32_t)blockIdx.x * (uint32_t)o.world + (uint32_t)o.rank) * kDeal;       // first frame row of this block
+    if (g0 >= o.n_total) return;                                                                       // a padding block of the deal
+    const uint32_t valid = min(min(kDeal, o.n_total - g0), N - blockIdx.x * kDeal);                    // rows of this block inside the frame
+    const float4* src = reinterpret_cast<const float4*>(rows);
+    for (uint32_t q = threadIdx.x; q < (valid * 5 + 3) / 4; q += kDeal) {
+        const bool whole = (q + 1) * 4 <= valid * 5;
+        #pragma unroll
+        for (int r = 0; r < FOC_MAX_PEERS; ++r) {
+            if (r >= o.world) break;
+            float* dst = o.frame[r] + (size_t)g0 * 5;
+            if (whole) reinterpret_cast<float4*>(dst)[q] = src[q];
+            else for (uint32_t k = q * 4; k < valid * 5; ++k) dst[k] = rows[k];
+        }
+    }
+    if (o.world > 1) __threadfence_system();
+}
+
 inline bool valid_group(const FocPeerGroup* g) {
     if (g == nullptr || g->world < 1 || g->world > FOC_MAX_PEERS || g->rank < 0 || g->rank >= g->world || g->state == nullptr) return false;
     for (int r = 0; r < g->world; ++r) if (g->flags[r] == nullptr) return false;
@@ -185,5 +225,16 @@ FOC_API int foc_dp_reduce(const FocDpReduce* args, void* stream) {
         case 7: k_dp_reduce<7><<<grid, kThreads, 0, s>>>(a); break;
         default: k_dp_reduce<8><<<grid, kThreads, 0, s>>>(a); break;
     }
+    FOC_LAUNCH_CHECK(); return 0;
+}
+
+FOC_API int foc_render_finish(const float* image, const float* depth, const float* weights_sum, const float* nears, const float* fars,
+                              uint32_t N, float bg, int depth_from_first_sample, const FocFrameOut* out, void* stream) {
+    if (N == 0) return 0;
+    if (out == nullptr || out->world < 1 || out->world > FOC_MAX_PEERS || out->rank < 0 || out->rank >= out->world) return FOC_ERR_UNSUPPORTED;
+    for (int r = 0; r < out->world; ++r)
+        if (out->frame[r] == nullptr || (reinterpret_cast<uintptr_t>(out->frame[r]) & 15u)) return FOC_ERR_UNSUPPORTED;
+    k_render_finish<<<ceil_div(N, kDeal), kDeal, 0, reinterpret_cast<cudaStream_t>(stream)>>>(image, depth, weights_sum, nears, fars, N, bg,
+                                                                                             depth_from_first_sample, *out);
     FOC_LAUNCH_CHECK(); return 0;
 }

@@ -400,6 +400,68 @@ __global__ void __launch_bounds__(1024) k_march_scan(const uint32_t* __restrict_
     if (threadIdx.x == 0) { counter[0] = (int32_t)s_base; counter[1] += (int32_t)N; }
 }
 
+// The same scan for a whole frame of rays (march_rays_all: 640 000 rays), three launches: per-4096-ray block sums, one CTA
+// scanning the block sums (and updating the counter), every block scanning its own rays from its offset.
+constexpr uint32_t kScanBlock = 4096;               // 1024 threads x 4 consecutive rays
+
+__device__ __forceinline__ uint32_t block_excl_scan_1024(uint32_t v, uint32_t* warp_tot, uint32_t& total) {
+    const int lane = threadIdx.x & 31, wid = threadIdx.x >> 5;
+    const uint32_t incl = warp_incl_sum_u32(v, lane);
+    if (lane == 31) warp_tot[wid] = incl;
+    __syncthreads();
+    const uint32_t wv = warp_tot[lane];
+    const uint32_t wincl = warp_incl_sum_u32(wv, lane);
+    const uint32_t woff = __shfl_sync(0xffffffffu, wincl - wv, wid);
+    total = __shfl_sync(0xffffffffu, wincl, 31);
+    __syncthreads();                                 // warp_tot may be reused
+    return woff + incl - v;
+}
+
+__global__ void __launch_bounds__(1024) k_scan_partial(const uint32_t* __restrict__ counts, uint32_t N, uint32_t* __restrict__ block_sums) {
+    __shared__ uint32_t warp_tot[32];
+    const uint32_t i = blockIdx.x * kScanBlock + threadIdx.x * 4;
+    uint32_t v = 0;
+    if (i + 4 <= N) { const uint4 c = *reinterpret_cast<const uint4*>(counts + i); v = c.x + c.y + c.z + c.w; }
+    else for (uint32_t k = i; k < N; ++k) v += counts[k];
+    uint32_t total;
+    block_excl_scan_1024(v, warp_tot, total);
+    if (threadIdx.x == 0) block_sums[blockIdx.x] = total;
+}
+
+__global__ void __launch_bounds__(1024) k_scan_tops(uint32_t* __restrict__ block_sums, uint32_t nb, uint32_t N, int32_t* __restrict__ counter) {
+    __shared__ uint32_t warp_tot[32];
+    uint32_t base = (uint32_t)counter[0];
+    for (uint32_t start = 0; start < nb; start += 1024) {
+        const uint32_t b = start + threadIdx.x;
+        const uint32_t v = b < nb ? block_sums[b] : 0u;
+        uint32_t total;
+        const uint32_t excl = block_excl_scan_1024(v, warp_tot, total);
+        if (b < nb) block_sums[b] = base + excl;
+        base += total;
+    }
+    if (threadIdx.x == 0) { counter[0] = (int32_t)base; counter[1] += (int32_t)N; }
+}
+
+__global__ void __launch_bounds__(1024) k_scan_apply(const uint32_t* __restrict__ counts, uint32_t N, const uint32_t* __restrict__ block_sums,
+                                                     int32_t* __restrict__ rays) {
+    __shared__ uint32_t warp_tot[32];
+    const uint32_t i = blockIdx.x * kScanBlock + threadIdx.x * 4;
+    uint32_t c[4] = {0u, 0u, 0u, 0u};
+    if (i + 4 <= N) { const uint4 q = *reinterpret_cast<const uint4*>(counts + i); c[0] = q.x; c[1] = q.y; c[2] = q.z; c[3] = q.w; }
+    else for (uint32_t k = 0; k < 4 && i + k < N; ++k) c[k] = counts[i + k];
+    uint32_t total;
+    uint32_t off = block_sums[blockIdx.x] + block_excl_scan_1024(c[0] + c[1] + c[2] + c[3], warp_tot, total);
+    #pragma unroll
+    for (uint32_t k = 0; k < 4; ++k) {
+        if (i + k < N) {
+            rays[3 * (size_t)(i + k)] = (int32_t)(i + k);
+            rays[3 * (size_t)(i + k) + 1] = (int32_t)off;
+            rays[3 * (size_t)(i + k) + 2] = (int32_t)c[k];
+        }
+        off += c[k];
+    }
+}
+
 // pass 2 (raymarching.cu:404-479), now data-parallel: ONE WARP PER RAY expands the recorded t's into samples with the
 // same float operations the serial walk would have applied, and writes its slice with coalesced 12/12/8-byte rows.
 //   x = clamp(o + t d);  dt = clamp(t gamma);  delta1 = (t + dt) - last_t,  last_t = previous sample's t + dt (t0 first).
@@ -507,8 +569,11 @@ FOC_API int foc_packbits(const float* grid, uint32_t N, float density_thresh, ui
     FOC_LAUNCH_CHECK(); return 0;
 }
 
-// scratch = counts [N] u32 (rounded up to 256 B) + recorded sample parameters [N, max_steps] f32
-static inline size_t march_counts_bytes(uint32_t N) { return (((size_t)N * sizeof(uint32_t)) + 255) & ~(size_t)255; }
+// scratch = counts [N] u32 (rounded up to 256 B) + block sums of the multi-block scan + recorded sample parameters [N, max_steps] f32
+static inline size_t march_block_sums_offset(uint32_t N) { return (((size_t)N * sizeof(uint32_t)) + 255) & ~(size_t)255; }
+static inline size_t march_counts_bytes(uint32_t N) {
+    return march_block_sums_offset(N) + ((((size_t)ceil_div(N, kScanBlock) + 1) * sizeof(uint32_t) + 255) & ~(size_t)255);
+}
 FOC_API size_t foc_march_rays_train_scratch_bytes(uint32_t N, uint32_t max_steps) {
     return march_counts_bytes(N) + (size_t)N * max_steps * sizeof(float);
 }
@@ -533,7 +598,15 @@ FOC_API int foc_march_rays_count(const float* rays_o, const float* rays_d, const
     else
         k_march_record<32><<<ceil_div(N, 128), 128, 0, S(stream)>>>(rays_o, rays_d, nears, fars, noises, N, max_steps, p, counts, tbuf);
     FOC_LAUNCH_CHECK();
-    foc::launch(k_march_scan, 1, 1024, 0, S(stream), counts, N, rays, counter);
+    if (N <= 8 * kScanBlock) {
+        foc::launch(k_march_scan, 1, 1024, 0, S(stream), counts, N, rays, counter);
+    } else {
+        uint32_t* block_sums = reinterpret_cast<uint32_t*>(static_cast<uint8_t*>(scratch) + march_block_sums_offset(N));
+        const uint32_t nb = ceil_div(N, kScanBlock);
+        k_scan_partial<<<nb, 1024, 0, S(stream)>>>(counts, N, block_sums);
+        k_scan_tops<<<1, 1024, 0, S(stream)>>>(block_sums, nb, N, counter);
+        k_scan_apply<<<nb, 1024, 0, S(stream)>>>(counts, N, block_sums, rays);
+    }
     FOC_LAUNCH_CHECK(); return 0;
 }
 

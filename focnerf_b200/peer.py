@@ -89,3 +89,62 @@ class PeerArena:
         if self._local:
             l.foc_peer_free(self._local)
             self._local = 0
+
+
+class FocFrameOut(ctypes.Structure):
+    """include/foc_b200.h: struct FocFrameOut"""
+    _fields_ = [("world", ctypes.c_int32), ("rank", ctypes.c_int32), ("n_total", ctypes.c_uint32), ("frame", ctypes.c_void_p * MAX_PEERS)]
+
+
+def render_finish(image, depth, weights_sum, nears, fars, bg, depth_from_first_sample, out_struct):
+    """csrc/peer.cu k_render_finish: background mix + depth normalisation + packing into [r, g, b, depth, weights_sum] rows of
+    the frame buffer(s) `out_struct` names, one launch."""
+    N = weights_sum.shape[0]
+    for t in (image, depth, weights_sum, nears, fars):
+        if t.dtype != torch.float32 or not t.is_contiguous() or not t.is_cuda:
+            raise RuntimeError("render_finish: contiguous float32 CUDA tensors expected")
+    check(lib().foc_render_finish(image.data_ptr(), depth.data_ptr(), weights_sum.data_ptr(), nears.data_ptr(), fars.data_ptr(), N, float(bg),
+                                  int(bool(depth_from_first_sample)), ctypes.byref(out_struct), stream()), "render_finish")
+
+
+def local_frame(n_rays, device):
+    """Single-GPU target of render_finish: ([n_rays, 5] buffer, FocFrameOut naming it)."""
+    buf = torch.empty(n_rays, 5, dtype=torch.float32, device=device)
+    fr = (ctypes.c_void_p * MAX_PEERS)()
+    fr[0] = buf.data_ptr()
+    return buf, FocFrameOut(1, 0, n_rays, fr)
+
+
+class FrameExchange:
+    """An n_rays-ray frame rendered by all ranks of the group: rays dealt in 128-ray blocks round-robin (dist.cyclic_tile),
+    every rank's finished rows stored straight into every rank's frame buffer over peer memory by the render epilogue, one
+    device-side barrier per frame -- no collective, no staging copy.  Two frame buffers alternate so that a fast rank's
+    next frame never lands in the buffer a slow rank is still reading."""
+
+    def __init__(self, n_rays, group=None, device=None):
+        self.n_rays = int(n_rays)
+        self._bytes = -(-self.n_rays * 20 // 256) * 256
+        self.arena = PeerArena(2 * self._bytes, group=group, device=device)
+        a = self.arena
+        self.world, self.rank = a.world, a.rank
+        self._frames = [a.tensor(k * self._bytes, self.n_rays * 5, torch.float32).view(self.n_rays, 5) for k in range(2)]
+        self._structs = [FocFrameOut(a.world, a.rank, self.n_rays, (ctypes.c_void_p * MAX_PEERS)(*[a.address(r, k * self._bytes) for r in range(a.world)]))
+                         for k in range(2)]
+        self._k = 0
+
+    def my_rays(self, device=None):
+        """Indices (int64) of the frame's rays this rank renders."""
+        from .dist import cyclic_tile
+        return cyclic_tile(self.n_rays, self.rank, self.world, device=device)
+
+    def finish(self, image, depth, weights_sum, nears, fars, bg, depth_from_first_sample):
+        """-> the complete [n_rays, 5] frame on this rank (valid once the stream reaches this point)."""
+        k = self._k
+        self._k ^= 1
+        render_finish(image, depth, weights_sum, nears, fars, bg, depth_from_first_sample, self._structs[k])
+        self.arena.barrier()
+        return self._frames[k]
+
+    def close(self):
+        self._frames = []
+        self.arena.close()

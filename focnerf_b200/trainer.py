@@ -292,7 +292,7 @@ class Trainer:
 
     # ------------------------------------------------------------------------------------------------ inference
     @torch.no_grad()
-    def render(self, rays_o, rays_d, bg_color=1.0, T_thresh=1e-4, device_compaction=True, mode="single_pass"):
+    def render(self, rays_o, rays_d, bg_color=1.0, T_thresh=1e-4, device_compaction=True, mode="single_pass", exchange=None):
         """run_cuda, inference branch (legacy/nerf/renderer.py:331-372).
 
         mode="loop": the reference's caller-owned loop (march_rays -> field -> composite_rays, n_step = min(N // n_alive, 8)).
@@ -302,24 +302,35 @@ class Trainer:
         mode="single_pass" (default): the same samples and the same front-to-back recurrence, but marched for all rays at once
           into exactly-sized ray-ordered buffers (march_rays_all: one 4-byte host read per frame), one field evaluation, one
           compositor launch with the same early termination.  Samples behind the termination point are evaluated and
-          discarded -- the tensor pipe and HBM are far from saturated, the launch/sync chain was the bound."""
+          discarded -- the tensor pipe and HBM are far from saturated, the launch/sync chain was the bound.
+        The epilogue (background mix, depth normalisation) is one kernel writing [r, g, b, depth, weights_sum] rows; the
+        returned image / depth / weights_sum are views of that buffer.
+        exchange (peer.FrameExchange, multi-GPU): rays_o / rays_d are this rank's share (`exchange.my_rays()`) of the frame; the
+          epilogue stores its rows into every rank's frame buffer over NVLink and the views returned cover the WHOLE frame."""
+        from . import peer
         self.flush()
         self.model.eval()
         rays_o, rays_d = rays_o.contiguous().view(-1, 3), rays_d.contiguous().view(-1, 3)
         N, dev = rays_o.shape[0], rays_o.device
         nears, fars = raymarching.near_far_from_aabb(rays_o, rays_d, self.aabb, self.min_near)
+
+        def finish(image, depth, weights_sum, from_first):
+            if exchange is not None:
+                frame = exchange.finish(image, depth, weights_sum, nears, fars, bg_color, from_first)
+            else:
+                frame, out = peer.local_frame(N, dev)
+                peer.render_finish(image, depth, weights_sum, nears, fars, bg_color, from_first, out)
+            return frame[:, :3], frame[:, 3], frame[:, 4]
+
         if mode == "single_pass":
             xyzs, dirs, deltas, rays = raymarching.march_rays_all(rays_o, rays_d, self.bound, self.density_bitfield, self.cascade,
                                                                   self.grid_size, nears, fars, 128, self.dt_gamma, self.max_steps)
             with torch.autocast("cuda", dtype=torch.float16, enabled=self.fp16):
                 sigmas, rgbs = (self.model.forward_fused if self.fused and self.fp16 else self.model)(xyzs, dirs)
                 weights_sum, depth, image = raymarching.composite_rays_train(sigmas, rgbs, deltas, rays, T_thresh)
-            image = image + (1 - weights_sum).unsqueeze(-1) * bg_color
             # the training compositor measures depth from the first sample's start (raymarching.cu:545 starts t at 0), the
-            # inference one from the ray origin (raymarching.cu:858 starts at rays_t): add the offset sum_i w_i * near
-            depth = depth + torch.where(weights_sum > 0, nears, torch.zeros_like(nears)) * weights_sum
-            depth = torch.clamp(depth - nears, min=0) / (fars - nears)
-            return image, depth, weights_sum
+            # inference one from the ray origin (raymarching.cu:858 starts at rays_t): the epilogue adds sum_i w_i * near
+            return finish(image.float().contiguous(), depth.float().contiguous(), weights_sum.float().contiguous(), True)
         weights_sum = torch.zeros(N, dtype=torch.float32, device=dev)
         depth = torch.zeros(N, dtype=torch.float32, device=dev)
         image = torch.zeros(N, 3, dtype=torch.float32, device=dev)
@@ -345,6 +356,4 @@ class Trainer:
                 else:
                     rays_alive = rays_alive[rays_alive >= 0]
                 step += n_step
-        image = image + (1 - weights_sum).unsqueeze(-1) * bg_color
-        depth = torch.clamp(depth - nears, min=0) / (fars - nears)
-        return image, depth, weights_sum
+        return finish(image, depth, weights_sum, False)

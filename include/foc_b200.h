@@ -270,6 +270,20 @@ int foc_adam_step_peers(const FocAdamTensor *tensors, int count, const float *lr
                         const float *scale, const float *found_inf, const int32_t *step, int peer_tensor, int world,
                         uint16_t *const *peer_shadow16, void *stream);
 
+/* Epilogue of an inference render (legacy/nerf/renderer.py:369-372), one launch: image + (1 - weights_sum) * bg, depth
+ * normalised to [near, far] (depth_from_first_sample != 0: `depth` came from the training compositor, which measures from
+ * the first sample -- near * weights_sum is added first), packed into rows [r, g, b, depth, weights_sum].  The N rays are
+ * this rank's share of an n_total-ray frame dealt in 128-ray blocks (block b -> rank b % world; world = 1: the whole
+ * frame): every block's rows are stored into frame[r] (an [n_total, 5] f32 buffer of rank r, peer-visible) for all r.
+ * Follow with foc_peer_barrier before any rank reads its frame. */
+typedef struct FocFrameOut {
+    int32_t world, rank;
+    uint32_t n_total;
+    float *frame[FOC_MAX_PEERS];
+} FocFrameOut;
+int foc_render_finish(const float *image, const float *depth, const float *weights_sum, const float *nears, const float *fars,
+                      uint32_t N, float bg, int depth_from_first_sample, const FocFrameOut *out, void *stream);
+
 #ifdef __cplusplus
 }
 #endif

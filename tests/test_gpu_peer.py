@@ -148,3 +148,63 @@ def test_data_parallel_trainer_peer_vs_nccl():
     lp, ln = out["peer"][0][0], out["nccl"][0][0]
     assert float(lp[-8:].mean()) < 0.6 * float(lp[:4].mean())                                              # it trains
     assert abs(float(lp[-8:].mean()) - float(ln[-8:].mean())) < 0.15 * float(ln[-8:].mean()), (lp[-8:], ln[-8:])
+
+
+def test_render_finish_matches_torch_ops():
+    """The fused render epilogue = the reference's separate elementwise ops (renderer.py:369-372), bit for bit."""
+    from focnerf_b200 import peer
+    g = torch.Generator(device="cuda").manual_seed(5)
+    n = 1000                                                          # not a multiple of the 128-ray block
+    image, depth, ws = torch.rand(n, 3, device="cuda", generator=g), torch.rand(n, device="cuda", generator=g) * 3, torch.rand(n, device="cuda", generator=g)
+    ws[::7] = 0.0
+    nears = torch.rand(n, device="cuda", generator=g) + 0.2
+    fars = nears + torch.rand(n, device="cuda", generator=g) * 3 + 0.1
+    for from_first in (False, True):
+        buf, out = peer.local_frame(n, image.device)
+        buf.fill_(-7.0)
+        peer.render_finish(image, depth, ws, nears, fars, 0.75, from_first, out)
+        d = depth + torch.where(ws > 0, nears, torch.zeros_like(nears)) * ws if from_first else depth
+        want = torch.cat([image + (1 - ws).unsqueeze(-1) * 0.75, (torch.clamp(d - nears, min=0) / (fars - nears)).unsqueeze(-1), ws.unsqueeze(-1)], -1)
+        assert torch.equal(buf, want)
+
+
+def _render_rank(rank, world, port, result):
+    os.environ.update(MASTER_ADDR="127.0.0.1", MASTER_PORT=str(port))
+    torch.cuda.set_device(rank)
+    dev = torch.device("cuda", rank)
+    dist.init_process_group("gloo", rank=rank, world_size=world)
+    import cases
+    from focnerf_b200.peer import FrameExchange
+    from focnerf_b200.trainer import Trainer
+    scene, cascade, grid, bits, thresh = cases.scene_bitfield(1.0)
+    tr = Trainer(bound=1.0, density_grid=torch.from_numpy(grid), device=dev, seed=0)      # same seed: identical replicas
+    n = 5000                                                                             # 40 blocks of 128 rays, the last one short
+    o, d = cases.camera_rays(n, seed=9)
+    o, d = torch.from_numpy(o).to(dev), torch.from_numpy(d).to(dev)
+    ex = FrameExchange(n, device=dev)
+    idx = ex.my_rays(device=dev)
+    ok = {}
+    for k in range(3):                                                                   # both frame buffers, and the first one again
+        img, dep, ws = tr.render(o[idx], d[idx], exchange=ex)
+        full = tr.render(o, d)
+        torch.cuda.synchronize()
+        ok[f"shape{k}"] = img.shape[0] == n
+        for name, a, b in zip(("image", "depth", "ws"), (img, dep, ws), full):
+            ok[f"{name}{k}"] = torch.equal(a.nan_to_num(nan=-1.0), b.nan_to_num(nan=-1.0)) or float((a - b).abs().max())   # 0/0 depth on rays that miss the box
+    ok["no_timeout"] = not ex.arena.timed_out()
+    ok["covered"] = bool((ws > 0).any())
+    result[rank] = ok
+    dist.barrier()
+    ex.close()
+    dist.destroy_process_group()
+
+
+@pytest.mark.parametrize("world", [1, 2])
+def test_frame_exchange_equals_single_gpu_render(world):
+    if torch.cuda.device_count() < world:
+        pytest.skip(f"needs {world} GPUs")
+    mgr = mp.Manager()
+    result = mgr.dict()
+    mp.spawn(_render_rank, args=(world, _free_port(), result), nprocs=world, join=True)
+    for r in range(world):
+        assert all(v is True for v in result[r].values()), (r, dict(result[r]))

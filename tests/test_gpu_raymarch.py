@@ -63,6 +63,28 @@ def test_march_train_vs_reference(bound, dt_gamma):
         assert pos == int(r["counter"][0])
 
 
+def test_march_large_batch_multi_block_scan():
+    """> 32768 rays take the three-launch scan (frame-sized march_rays_all): same per-ray results as the same rays marched in
+    single-CTA-scan sized pieces, offsets = exclusive scan of the counts, counter = (total, N)."""
+    c = cases.march_case(70001, 21, 1.0)                              # not a multiple of the 4096-ray scan block
+    n = c["rays_o"].shape[0]
+    got = runners.march_train(ours(), c, M=n * 128)
+    assert np.array_equal(got["offsets"], np.concatenate([[0], np.cumsum(got["counts"])[:-1]]))
+    assert int(got["counter"][0]) == int(got["counts"].sum()) <= n * 128 and int(got["counter"][1]) == n
+    pos = 0
+    for s0 in range(0, n, 30000):
+        sub = {k: (v[s0:s0 + 30000] if isinstance(v, np.ndarray) and v.shape[:1] == (n,) else v) for k, v in c.items()}
+        m = sub["rays_o"].shape[0]
+        part = runners.march_train(ours(), sub, M=m * 160)
+        assert np.array_equal(part["counts"], got["counts"][s0:s0 + m])
+        tot = int(part["counter"][0])
+        assert tot <= m * 160 and part["xyzs"].shape[0] == tot
+        assert np.array_equal(part["xyzs"].view(np.uint32), got["xyzs"][pos:pos + tot].view(np.uint32))
+        assert np.array_equal(part["deltas"].view(np.uint32), got["deltas"][pos:pos + tot].view(np.uint32))
+        pos += tot
+    assert pos == int(got["counter"][0]) == got["xyzs"].shape[0]
+
+
 def test_march_train_truncated():
     """mean_count underestimates (M too small): kept rays are exact, nothing is written past M."""
     c = cases.march_case(512, 3, 1.0)
