@@ -219,6 +219,81 @@ def render_bench(render_fn, dev, rank, world, frames=3, H=800, W=800):
             "workload": "configs[2]: one 800x800 test pose of the synthetic scene, T_thresh 1e-4, max_steps 1024, model as trained by the timed steps"}
 
 
+def multi_rays(H=480, W=640, device="cpu"):
+    """configs[3]: the 640x480 table-top view (fx = fy = 554, radius 1.8) -> rays_o, rays_d [H*W, 3]"""
+    import torch
+    from focnerf_b200 import synthetic
+    pose = synthetic.ring_poses(8, radius=1.8, seed=321)[2]
+    intr = (554.0, 554.0, W / 2.0, H / 2.0)
+    o, d = synthetic.get_rays(pose, intr, H, W)
+    return o.contiguous().to(device), d.contiguous().to(device)
+
+
+def multi_objects(make_model, K, dev):
+    """K independently seeded object fields (the workload does not depend on the weights: the reference composites with no early
+    termination); tables drawn wide so densities differ from place to place."""
+    import torch
+    models = []
+    for k in range(K):
+        m = make_model().to(dev)
+        torch.manual_seed(4000 + k)                  # after construction: FFMLP.reset_parameters re-seeds the global generator (ffmlp.py:139)
+        with torch.no_grad():
+            emb = m.encoder.embeddings if hasattr(m, "encoder") else m.embeddings
+            emb.copy_(torch.randn_like(emb) * 1.5)
+        models.append(m.eval())
+    return models
+
+
+def multi_bench(dev, rank, world, frames=2, K=4, T=512, H=480, W=640, chunk=16384):
+    """configs[3]: FOC multi-object composition (COMBINED.py), K = 4 resident object hash grids, 640x480 rays, T = 512 uniform
+    samples per ray and object, arg-max-density selection + per-object colour masks + 4-channel composite.  N > 1: 128-ray
+    blocks dealt round-robin, no data-path collective, one gather per frame."""
+    import torch
+    import torch.distributed as dist
+    from focnerf_b200.multiobject import MultiObjectRenderer
+    from focnerf_b200.network import NeRFNetwork
+    from focnerf_b200.dist import cyclic_tile, gather_cyclic
+    o, d = multi_rays(H, W)
+    n = H * W
+    if world > 1:
+        idx = cyclic_tile(n, rank, world)
+        o, d = o[idx], d[idx]
+    o, d = o.contiguous().to(dev), d.contiguous().to(dev)
+    aabb = torch.tensor([-1.0] * 3 + [1.0] * 3, device=dev)
+    r = MultiObjectRenderer(multi_objects(lambda: NeRFNetwork(bound=1.0), K, dev), aabb, num_steps=T)
+    buf = {"out": None}
+
+    def frame():
+        img, dep, ws = r.render(o, d, bg=1.0, chunk=chunk)
+        if world == 1:
+            return img, dep, ws
+        out = torch.cat([img, dep.unsqueeze(-1), ws.unsqueeze(-1)], -1)
+        out, buf["out"] = gather_cyclic(out, n, out=buf["out"])
+        return out[:, :4], out[:, 4], out[:, 5]
+
+    frame()
+    if world > 1:
+        dist.barrier()
+    torch.cuda.synchronize()
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    e0.record()
+    for _ in range(frames):
+        out = frame()
+    e1.record()
+    if world > 1:
+        dist.barrier()
+    torch.cuda.synchronize()
+    ms = torch.tensor([e0.elapsed_time(e1)], device=dev)
+    if world > 1:
+        dist.all_reduce(ms, op=dist.ReduceOp.MAX)
+    ms = float(ms.item()) / frames
+    return {"metric": "640x480 multi-object composite Mrays/s", "value": n / (ms * 1e-3) / 1e6, "unit": "Mrays/s", "ms_per_frame": ms,
+            "frames": frames, "rays": n, "objects": K, "samples_per_ray": T, "field_evaluations_per_s": n * K * T / (ms * 1e-3),
+            "scaling": "strong", "coverage": float((out[2] > 0.5).float().mean().item()),
+            "workload": "configs[3]: 4 resident object hash grids (16 levels, 2^19, F=2, 64-wide FFMLPs), 640x480 rays, 512 uniform samples "
+                        "per ray and object, per-sample arg-max density + per-object colour masks + 4-channel composite, no early termination"}
+
+
 def run_ours(args):
     import numpy as np
     import torch
@@ -309,6 +384,7 @@ def run_ours(args):
     tr.use_graph = use_graph
 
     render = render_bench(tr.render, dev, rank, world, frames=args.frames) if args.frames > 0 else None
+    multi = multi_bench(dev, rank, world, frames=args.multi_frames) if args.multi_frames > 0 else None
 
     # density-grid refresh (update_extra_state, every 16 steps in the reference's loop): timed on a copy of the state, after
     # everything else, because it replaces the analytic bitfield the timed steps marched through
@@ -383,7 +459,7 @@ def run_ours(args):
         "e2e": {"value": total_rays / (ms_e2e * 1e-3), "unit": "rays/s", "ms_per_step": ms_e2e / args.steps,
                 "h2d_bytes_per_step": world * RAYS_PER_GPU * 9 * 4, "d2h_bytes_per_step": world * 4},
         "gpu_launches": int(round(kt.kernel_launches() / n_prof * args.steps)),
-        "render": render, "density_refresh": refresh, "quality": quality,
+        "render": render, "multi_object": multi, "density_refresh": refresh, "quality": quality,
         "roofline": roof,
     }
     if world == 1:
@@ -419,6 +495,7 @@ if __name__ == "__main__":
     ap.add_argument("--steps", type=int, default=1024)
     ap.add_argument("--psnr-steps", type=int, default=512, help="steps of the fixed-iteration PSNR run (0 = skip)")
     ap.add_argument("--frames", type=int, default=3, help="800x800 frames of the render workload (0 = skip)")
+    ap.add_argument("--multi-frames", type=int, default=2, help="640x480 frames of the 4-object composite workload (0 = skip)")
     ap.add_argument("--warmup", type=int, default=8)
     ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
     ap.add_argument("--no-graph", action="store_true", help="launch the step eagerly instead of replaying a CUDA graph")

@@ -166,6 +166,69 @@ class RefNetwork(nn.Module):
         return sigma, torch.sigmoid(self.color_net(h))
 
 
+def _ref_density(self, x):
+    """nerf/network_ff.py:76-90"""
+    from focnerf_b200.activation import trunc_exp
+    x = (x + self.bound) / (2 * self.bound)
+    h = self.sigma_net(_grid_encode.apply(x.view(-1, 3), self.embeddings, self.offsets, self.pls, self.H))
+    return {'sigma': trunc_exp(h[..., 0]), 'geo_feat': h[..., 1:]}
+
+
+def _ref_color(self, x, d, mask=None, geo_feat=None, **kwargs):
+    """nerf/network_ff.py:92-123: colour net on the masked subset (boolean gather / scatter)"""
+    from focnerf_b200.shencoder import sh_encode
+    if mask is not None:
+        rgbs = torch.zeros(mask.shape[0], 3, dtype=x.dtype, device=x.device)
+        if not mask.any():
+            return rgbs
+        x, d, geo_feat = x[mask], d[mask], geo_feat[mask]
+    dd = sh_encode(d)
+    h = torch.cat([dd.to(geo_feat.dtype), geo_feat, torch.zeros_like(geo_feat[..., :1])], dim=-1)
+    h = torch.sigmoid(self.color_net(h))
+    if mask is not None:
+        rgbs[mask] = h.to(rgbs.dtype)
+        return rgbs
+    return h
+
+
+RefNetwork.density = _ref_density
+RefNetwork.color = _ref_color
+
+
+def multi_bench(dev, chunks=3, K=4, T=512, batch=4096):
+    """configs[3] on the reference stack: COMBINED.py's per-image loop body (tests/foc_eager.py restates it op for op) over
+    RefNetwork objects, in the reference's own 4096-ray batches; a bounded sample of the 640x480 frame (75 batches)."""
+    import bench
+    import foc_eager
+
+    def near_far(o, d, aabb, min_near):
+        n = o.shape[0]
+        nears, fars = torch.empty(n, device=o.device), torch.empty(n, device=o.device)
+        _rm.near_far_from_aabb(o.contiguous(), d.contiguous(), aabb, n, min_near, nears, fars)
+        return nears, fars
+
+    models = bench.multi_objects(lambda: RefNetwork(1.0), K, dev)
+    aabb = torch.tensor([-1.0] * 3 + [1.0] * 3, device=dev)
+    o, d = bench.multi_rays(device=dev)
+    n = o.shape[0]
+    starts = [(n // 2 // batch) * batch + i * batch for i in range(chunks + 1)]      # batches from the middle of the frame
+    foc_eager.render_chunk(models, near_far, o[starts[0]:starts[0] + batch], d[starts[0]:starts[0] + batch], aabb, T)
+    torch.cuda.synchronize()
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    e0.record()
+    for s0 in starts[1:]:
+        out = foc_eager.render_chunk(models, near_far, o[s0:s0 + batch], d[s0:s0 + batch], aabb, T)
+    e1.record()
+    torch.cuda.synchronize()
+    ms = e0.elapsed_time(e1) / chunks
+    return {"metric": "640x480 multi-object composite Mrays/s", "value": batch / (ms * 1e-3) / 1e6, "unit": "Mrays/s",
+            "ms_per_frame": ms * n / batch, "rays": n, "objects": K, "samples_per_ray": T,
+            "field_evaluations_per_s": batch * K * T / (ms * 1e-3), "coverage": float((out[2] > 0.5).float().mean().item()),
+            "sample": f"{chunks} of the frame's {n // batch} batches of {batch} rays (the reference's max_ray_batch), objects resident "
+                      "(the reference also reloads every checkpoint from disk per image: not timed)",
+            "workload": "configs[3] on the reference extensions: eager COMBINED.py loop body (linspace / cumprod / masked colour / running max)"}
+
+
 class RefTrainer:
     """Same step as focnerf_b200.trainer.Trainer.train_step (legacy/nerf/renderer.py:268-319 + utils.py:510-560, 863-868)."""
 
@@ -300,6 +363,7 @@ def run(args):
     rays = bench.RAYS_PER_GPU * args.steps
     val, val_e2e = rays / (ms * 1e-3), rays / (ms_e2e * 1e-3)
     render = bench.render_bench(tr.render, dev, 0, 1, frames=args.frames) if args.frames > 0 else None
+    multi = multi_bench(dev) if getattr(args, "multi_frames", 0) > 0 else None
     quality = bench.psnr_run(lambda: RefTrainer(torch.from_numpy(grid)), scene, dev, args.psnr_steps, pool_dev) if args.psnr_steps > 0 else None
     return {
         "impl": "reference", "metric": "train rays/s", "value": val, "unit": "rays/s", "n_gpus": 1, "steps": args.steps, "warmup": warm,
@@ -309,7 +373,7 @@ def run(args):
                    "note": "the reference's own CUDA extensions (raymarching, gridencoder, ffmlp: unmodified sources compiled for sm_100a) on the "
                            "same B200; the reference has no CPU implementation of this path and no multi-GPU path, so this arm always runs on "
                            "one GPU"},
-        "clocks": clk, "render": render, "quality": quality,
+        "clocks": clk, "render": render, "multi_object": multi, "quality": quality,
         "cpu_baseline": {"value": val, "unit": "rays/s", "cores": 0, "kind": "reference",
                          "sample": f"{args.steps} full train steps of 4096 rays on the reference CUDA extensions (GPU; the reference has no CPU path)"},
         "e2e": {"value": val_e2e, "unit": "rays/s", "ms_per_step": ms_e2e / args.steps, "h2d_bytes_per_step": bench.RAYS_PER_GPU * 36,
