@@ -44,6 +44,57 @@ k_composite_rays(uint32_t n_alive, uint32_t n_step, float T_thresh, int32_t* __r
     image[3 * (size_t)id] = r; image[3 * (size_t)id + 1] = g; image[3 * (size_t)id + 2] = b;
 }
 
+// K10's recurrence over a DEPTH WINDOW of ray-ordered samples (render without the host-driven loop: a frame is a few windows
+// over the records of foc_march_rays_count).  One warp per ray: the window's slice [off, off + cnt) is read with coalesced
+// requests, the carried state (weights_sum, depth, image, rays_t) is updated in place, alive[n] is cleared when the ray
+// terminated -- K10's rule: stop AFTER accumulating the first sample whose transmittance BEFORE it is below T_thresh
+// (raymarching.cu:885).  T = 1 - weights_sum is carried as K10 does; inside a window it is the running product.
+__global__ void __launch_bounds__(128)
+k_composite_window(const float* __restrict__ sigmas, const float* __restrict__ rgbs, const float* __restrict__ deltas,
+                   const int32_t* __restrict__ rays_w, uint32_t M, uint32_t N, float T_thresh, float* __restrict__ rays_t,
+                   float* __restrict__ weights_sum, float* __restrict__ depth, float* __restrict__ image, uint8_t* __restrict__ alive) {
+    const int lane = threadIdx.x & 31;
+    const uint32_t n = blockIdx.x * 4 + (threadIdx.x >> 5);
+    if (n >= N) return;
+    const uint32_t off = (uint32_t)__ldg(rays_w + 3 * (size_t)n + 1), cnt = (uint32_t)__ldg(rays_w + 3 * (size_t)n + 2);
+    if (cnt == 0 || (uint64_t)off + cnt > M) return;
+    const float ws0 = weights_sum[n];
+    float T = 1.0f - ws0, t_base = rays_t[n];
+    float r = 0.f, g = 0.f, b = 0.f, d = 0.f, ws = 0.f;
+    bool terminated = false;
+    for (uint32_t base = 0; base < cnt; base += 32) {
+        const uint32_t s = base + lane;
+        const bool valid = s < cnt;
+        const size_t i = (size_t)off + (valid ? s : 0);
+        float alpha = 0.f, d1 = 0.f, cr = 0.f, cg = 0.f, cb = 0.f;
+        if (valid) {
+            const float2 dl = __ldg(reinterpret_cast<const float2*>(deltas) + i);
+            alpha = 1.0f - __expf(-__ldg(sigmas + i) * dl.x);
+            d1 = dl.y;
+            cr = __ldg(rgbs + 3 * i); cg = __ldg(rgbs + 3 * i + 1); cb = __ldg(rgbs + 3 * i + 2);
+        }
+        const float incl = warp_incl_prod(1.0f - alpha, lane);
+        const float up = __shfl_up_sync(0xffffffffu, incl, 1);
+        const float T_before = T * (lane == 0 ? 1.0f : up);
+        const float w = alpha * T_before;
+        const float t = t_base + warp_incl_sum(d1, lane);
+        const uint32_t stop = __ballot_sync(0xffffffffu, valid && T_before < T_thresh);
+        const int last = stop ? (__ffs(stop) - 1) : 31;
+        if (valid && lane <= last) {
+            r = fmaf(w, cr, r); g = fmaf(w, cg, g); b = fmaf(w, cb, b);
+            d = fmaf(w, t, d); ws += w;
+        }
+        if (stop) { terminated = true; break; }
+        T *= __shfl_sync(0xffffffffu, incl, 31); t_base = __shfl_sync(0xffffffffu, t, 31);
+    }
+    r = warp_sum(r); g = warp_sum(g); b = warp_sum(b); d = warp_sum(d); ws = warp_sum(ws);
+    if (lane == 0) {
+        weights_sum[n] = ws0 + ws; depth[n] += d;
+        image[3 * (size_t)n] += r; image[3 * (size_t)n + 1] += g; image[3 * (size_t)n + 2] += b;
+        if (terminated) alive[n] = 0; else rays_t[n] = t_base;
+    }
+}
+
 // ------------------------------------------------------------------------------------------------ compaction
 namespace {
 constexpr uint32_t kCompactThreads = 256;
@@ -123,6 +174,13 @@ FOC_API int foc_composite_rays(uint32_t n_alive, uint32_t n_step, float T_thresh
     if (n_alive == 0) return 0;
     k_composite_rays<<<ceil_div(n_alive, 128), 128, 0, S(stream)>>>(n_alive, n_step, T_thresh, rays_alive, rays_t, sigmas,
                                                                   rgbs, deltas, weights_sum, depth, image);
+    FOC_LAUNCH_CHECK(); return 0;
+}
+
+FOC_API int foc_composite_window(const float* sigmas, const float* rgbs, const float* deltas, const int32_t* rays_w, uint32_t M, uint32_t N,
+                                 float T_thresh, float* rays_t, float* weights_sum, float* depth, float* image, uint8_t* alive, void* stream) {
+    if (N == 0) return 0;
+    k_composite_window<<<ceil_div(N, 4), 128, 0, S(stream)>>>(sigmas, rgbs, deltas, rays_w, M, N, T_thresh, rays_t, weights_sum, depth, image, alive);
     FOC_LAUNCH_CHECK(); return 0;
 }
 

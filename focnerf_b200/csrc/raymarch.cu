@@ -467,7 +467,7 @@ __global__ void __launch_bounds__(1024) k_scan_apply(const uint32_t* __restrict_
 //   x = clamp(o + t d);  dt = clamp(t gamma);  delta1 = (t + dt) - last_t,  last_t = previous sample's t + dt (t0 first).
 __global__ void __launch_bounds__(128) k_march_expand(const float* __restrict__ rays_o, const float* __restrict__ rays_d,
                                                       const float* __restrict__ nears, const float* __restrict__ noises,
-                                                      uint32_t N, uint32_t M, uint32_t max_steps, MarchParams p,
+                                                      uint32_t N, uint32_t M, uint32_t max_steps, uint32_t start, MarchParams p,
                                                       const int32_t* __restrict__ rays, const float* __restrict__ tbuf,
                                                       float* __restrict__ xyzs, float* __restrict__ dirs, float* __restrict__ deltas) {
     pdl_sync();
@@ -493,11 +493,11 @@ __global__ void __launch_bounds__(128) k_march_expand(const float* __restrict__ 
     const float dx = __ldg(rays_d + 3 * (size_t)n), dy = __ldg(rays_d + 3 * (size_t)n + 1), dz = __ldg(rays_d + 3 * (size_t)n + 2);
     const float near = __ldg(nears + n);
     const float t0 = ffma(step_dt(p, near), __ldg(noises + n), near);
-    const float* tb = tbuf + (size_t)n * max_steps;
+    const float* tb = tbuf + (size_t)n * max_steps + start;          // start > 0: a later depth window of the same records
     for (uint32_t s = lane; s < num; s += 32) {
         const float t = __ldg(tb + s);
         float last = t0;
-        if (s > 0) { const float tp = __ldg(tb + s - 1); last = fadd(tp, step_dt(p, tp)); }
+        if (s + start > 0) { const float tp = __ldg(tb + (ptrdiff_t)s - 1); last = fadd(tp, step_dt(p, tp)); }
         const float dt = step_dt(p, t), tn = fadd(t, dt);
         const size_t i = (size_t)off + s;
         xyzs[3 * i] = clampf(ffma(t, dx, ox), -p.bound, p.bound);
@@ -581,6 +581,8 @@ FOC_API size_t foc_march_rays_train_scratch_bytes(uint32_t N, uint32_t max_steps
 // small N (a training batch) is latency-bound: one warp per CTA spreads the rays over all SMs
 static inline uint32_t march_block(uint32_t n) { return n <= (uint32_t)kNumSMs * 32u * 8u ? 32u : 128u; }
 
+static int scan_counts(const uint32_t* counts, uint32_t N, int32_t* rays, int32_t* counter, uint32_t* block_sums, cudaStream_t st);
+
 // record + scan: rays[n] = (n, offset, count), counter[0] += total, counter[1] += N; the recorded parameters stay in `scratch`
 FOC_API int foc_march_rays_count(const float* rays_o, const float* rays_d, const uint8_t* grid, float bound, float dt_gamma,
                                  uint32_t max_steps, uint32_t N, uint32_t C, uint32_t H, const float* nears, const float* fars,
@@ -598,16 +600,7 @@ FOC_API int foc_march_rays_count(const float* rays_o, const float* rays_d, const
     else
         k_march_record<32><<<ceil_div(N, 128), 128, 0, S(stream)>>>(rays_o, rays_d, nears, fars, noises, N, max_steps, p, counts, tbuf);
     FOC_LAUNCH_CHECK();
-    if (N <= 8 * kScanBlock) {
-        foc::launch(k_march_scan, 1, 1024, 0, S(stream), counts, N, rays, counter);
-    } else {
-        uint32_t* block_sums = reinterpret_cast<uint32_t*>(static_cast<uint8_t*>(scratch) + march_block_sums_offset(N));
-        const uint32_t nb = ceil_div(N, kScanBlock);
-        k_scan_partial<<<nb, 1024, 0, S(stream)>>>(counts, N, block_sums);
-        k_scan_tops<<<1, 1024, 0, S(stream)>>>(block_sums, nb, N, counter);
-        k_scan_apply<<<nb, 1024, 0, S(stream)>>>(counts, N, block_sums, rays);
-    }
-    FOC_LAUNCH_CHECK(); return 0;
+    return scan_counts(counts, N, rays, counter, reinterpret_cast<uint32_t*>(static_cast<uint8_t*>(scratch) + march_block_sums_offset(N)), S(stream));
 }
 
 // expand the records of foc_march_rays_count (same scratch, same rays) into samples; rays whose slice would pass M write nothing
@@ -618,7 +611,51 @@ FOC_API int foc_march_rays_expand(const float* rays_o, const float* rays_d, floa
     if (C == 0 || C > 8 || H == 0 || H > 1024) return FOC_ERR_UNSUPPORTED;
     const MarchParams p = make_march_params(nullptr, bound, dt_gamma, max_steps, C, H);
     const float* tbuf = reinterpret_cast<const float*>(static_cast<const uint8_t*>(scratch) + march_counts_bytes(N));
-    foc::launch(k_march_expand, ceil_div(N, 4), 128, 0, S(stream), rays_o, rays_d, nears, noises, N, M, max_steps, p, rays, tbuf, xyzs, dirs, deltas);
+    foc::launch(k_march_expand, ceil_div(N, 4), 128, 0, S(stream), rays_o, rays_d, nears, noises, N, M, max_steps, 0u, p, rays, tbuf, xyzs, dirs, deltas);
+    FOC_LAUNCH_CHECK(); return 0;
+}
+
+// ---- depth windows over the records of foc_march_rays_count (render: early termination without a host-driven loop)
+__global__ void __launch_bounds__(256) k_window_counts(const uint32_t* __restrict__ counts, const uint8_t* __restrict__ alive,
+                                                       uint32_t N, uint32_t start, uint32_t width, uint32_t* __restrict__ wcounts) {
+    const uint32_t n = blockIdx.x * blockDim.x + threadIdx.x;
+    if (n >= N) return;
+    const uint32_t c = counts[n];
+    uint32_t w = c > start ? min(c - start, width) : 0u;
+    if (alive && !alive[n]) w = 0u;
+    wcounts[n] = w;
+}
+
+static int scan_counts(const uint32_t* counts, uint32_t N, int32_t* rays, int32_t* counter, uint32_t* block_sums, cudaStream_t st) {
+    if (N <= 8 * kScanBlock) {
+        foc::launch(k_march_scan, 1, 1024, 0, st, counts, N, rays, counter);
+    } else {
+        const uint32_t nb = ceil_div(N, kScanBlock);
+        k_scan_partial<<<nb, 1024, 0, st>>>(counts, N, block_sums);
+        k_scan_tops<<<1, 1024, 0, st>>>(block_sums, nb, N, counter);
+        k_scan_apply<<<nb, 1024, 0, st>>>(counts, N, block_sums, rays);
+    }
+    FOC_LAUNCH_CHECK(); return 0;
+}
+
+FOC_API int foc_march_window_count(void* scratch, uint32_t N, uint32_t start, uint32_t width, const uint8_t* alive,
+                                   uint32_t* wcounts, int32_t* rays_w, int32_t* counter, void* stream) {
+    if (N == 0) return 0;
+    const uint32_t* counts = static_cast<const uint32_t*>(scratch);
+    uint32_t* block_sums = reinterpret_cast<uint32_t*>(static_cast<uint8_t*>(scratch) + march_block_sums_offset(N));
+    k_window_counts<<<ceil_div(N, 256), 256, 0, S(stream)>>>(counts, alive, N, start, width, wcounts);
+    FOC_LAUNCH_CHECK();
+    return scan_counts(wcounts, N, rays_w, counter, block_sums, S(stream));
+}
+
+FOC_API int foc_march_window_expand(const float* rays_o, const float* rays_d, float bound, float dt_gamma, uint32_t max_steps, uint32_t N,
+                                    uint32_t C, uint32_t H, uint32_t M, uint32_t start, const float* nears, const int32_t* rays_w,
+                                    const float* noises, const void* scratch, float* xyzs, float* dirs, float* deltas, void* stream) {
+    if (N == 0) return 0;
+    if (C == 0 || C > 8 || H == 0 || H > 1024 || start >= max_steps) return FOC_ERR_UNSUPPORTED;
+    const MarchParams p = make_march_params(nullptr, bound, dt_gamma, max_steps, C, H);
+    const float* tbuf = reinterpret_cast<const float*>(static_cast<const uint8_t*>(scratch) + march_counts_bytes(N));
+    foc::launch(k_march_expand, ceil_div(N, 4), 128, 0, S(stream), rays_o, rays_d, nears, noises, N, M, max_steps, start, p, rays_w, tbuf, xyzs, dirs, deltas);
     FOC_LAUNCH_CHECK(); return 0;
 }
 

@@ -92,6 +92,26 @@ class _Backend:
                                           ptr(noises), ptr(scratch), ptr(xyzs), ptr(dirs), ptr(deltas), stream()), "march_rays_expand")
 
     @staticmethod
+    def march_window_count(scratch, N, start, width, alive, wcounts, rays_w, counter):
+        require_cuda(scratch, wcounts, rays_w, counter)
+        check(lib().foc_march_window_count(ptr(scratch), N, start, width, ptr(alive), ptr(wcounts), ptr(rays_w), ptr(counter), stream()),
+              "march_window_count")
+
+    @staticmethod
+    def march_window_expand(rays_o, rays_d, bound, dt_gamma, max_steps, N, C, H, M, start, nears, rays_w, noises, scratch, xyzs, dirs, deltas):
+        require_cuda(rays_o, rays_d, nears, rays_w, noises, scratch, xyzs, dirs, deltas)
+        check(lib().foc_march_window_expand(ptr(rays_o), ptr(rays_d), bound, dt_gamma, max_steps, N, C, H, M, start, ptr(nears), ptr(rays_w),
+                                            ptr(noises), ptr(scratch), ptr(xyzs), ptr(dirs), ptr(deltas), stream()), "march_window_expand")
+
+    @staticmethod
+    def composite_window(sigmas, rgbs, deltas, rays_w, M, N, T_thresh, rays_t, weights_sum, depth, image, alive):
+        require_cuda(sigmas, rgbs, deltas, rays_w, rays_t, weights_sum, depth, image, alive)
+        for t, nm in ((sigmas, "sigmas"), (rgbs, "rgbs"), (deltas, "deltas")):
+            _f32c(t, nm)
+        check(lib().foc_composite_window(ptr(sigmas), ptr(rgbs), ptr(deltas), ptr(rays_w), M, N, T_thresh, ptr(rays_t), ptr(weights_sum),
+                                         ptr(depth), ptr(image), ptr(alive), stream()), "composite_window")
+
+    @staticmethod
     def composite_mse_forward(sigmas, rgbs, deltas, rays, gt, bg, M, N, T_thresh, weights_sum, depth, image, err, loss):
         require_cuda(sigmas, rgbs, deltas, rays, gt, weights_sum, depth, image, err, loss)
         for t, nm in ((sigmas, "sigmas"), (rgbs, "rgbs"), (deltas, "deltas"), (gt, "gt")):

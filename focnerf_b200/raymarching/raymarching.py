@@ -253,6 +253,63 @@ def march_rays_all(rays_o, rays_d, bound, density_bitfield, C, H, nears, fars, a
     return xyzs, dirs, deltas, rays
 
 
+class WindowedMarch:
+    """Not in the reference: the render loop of legacy/nerf/renderer.py:337-366 (march_rays -> field -> composite_rays, <= 8 samples per
+    ray and iteration, a boolean-mask compaction and a host sync each time) as a few DEPTH WINDOWS over one recorded march.
+
+    __init__ walks every ray once (foc_march_rays_count: the parameters of all occupied steps stay in scratch).  window(start, width)
+    hands out samples [start, start + width) of every ray that is still alive, ray-ordered and exactly sized (one 4-byte host read),
+    composite(...) applies K10's recurrence to them, carrying weights_sum / depth / image / rays_t in place and clearing `alive` for
+    terminated rays -- so the field is never evaluated behind a ray's termination point by more than one window."""
+
+    def __init__(self, rays_o, rays_d, bound, density_bitfield, C, H, nears, fars, dt_gamma=0, max_steps=1024, align=128):
+        self.rays_o, self.rays_d = _cuda(rays_o).float().contiguous().view(-1, 3), _cuda(rays_d).float().contiguous().view(-1, 3)
+        self.N, dev = self.rays_o.shape[0], self.rays_o.device
+        self.args = (float(bound), float(dt_gamma), int(max_steps), int(C), int(H))
+        self.nears, self.align = nears, align
+        from .._lib import lib
+        N = self.N
+        self.scratch = torch.empty(max(1, lib().foc_march_rays_train_scratch_bytes(N, max_steps)), dtype=torch.uint8, device=dev)
+        self.rays = torch.empty(N, 3, dtype=torch.int32, device=dev)          # whole-ray (id, offset, count)
+        self.rays_w = torch.empty(N, 3, dtype=torch.int32, device=dev)        # current window
+        self.wcounts = torch.empty(N, dtype=torch.int32, device=dev)
+        self.counter = torch.zeros(2, dtype=torch.int32, device=dev)
+        self.noises = torch.zeros(N, dtype=torch.float32, device=dev)
+        self.alive = torch.ones(N, dtype=torch.uint8, device=dev)
+        self.rays_t = nears.clone()
+        self.weights_sum = torch.zeros(N, dtype=torch.float32, device=dev)
+        self.depth = torch.zeros(N, dtype=torch.float32, device=dev)
+        self.image = torch.zeros(N, 3, dtype=torch.float32, device=dev)
+        self.M = 0
+        b, g, ms, C, H = self.args
+        _backend.march_rays_count(self.rays_o, self.rays_d, _cuda(density_bitfield).contiguous(), b, g, ms, N, C, H, nears, fars, self.rays,
+                                  self.counter, self.noises, self.scratch)
+
+    @torch.no_grad()
+    def window(self, start, width):
+        """-> (xyzs [M,3], dirs [M,3], deltas [M,2]) of the window, or None when no alive ray has samples left."""
+        b, g, ms, C, H = self.args
+        dev = self.rays_o.device
+        self.counter.zero_()
+        _backend.march_window_count(self.scratch, self.N, int(start), int(width), self.alive, self.wcounts, self.rays_w, self.counter)
+        total = int(self.counter[0].item())
+        if total == 0:
+            return None
+        M = self.M = _pad_up(total, self.align)
+        xyzs = torch.empty(M, 3, dtype=torch.float32, device=dev)
+        dirs = torch.empty(M, 3, dtype=torch.float32, device=dev)
+        deltas = torch.empty(M, 2, dtype=torch.float32, device=dev)
+        _backend.march_window_expand(self.rays_o, self.rays_d, b, g, ms, self.N, C, H, M, int(start), self.nears, self.rays_w, self.noises,
+                                     self.scratch, xyzs, dirs, deltas)
+        return xyzs, dirs, deltas
+
+    @torch.no_grad()
+    def composite(self, sigmas, rgbs, deltas, T_thresh=1e-4):
+        sigmas, rgbs = sigmas.float().contiguous(), rgbs.float().contiguous()
+        _backend.composite_window(sigmas, rgbs, deltas, self.rays_w, self.M, self.N, float(T_thresh), self.rays_t, self.weights_sum,
+                                  self.depth, self.image, self.alive)
+
+
 def compact_alive(rays_alive, n_alive=None):
     """Device-side replacement for `rays_alive[rays_alive >= 0]` (legacy/nerf/renderer.py:363).
 

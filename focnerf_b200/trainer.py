@@ -292,7 +292,8 @@ class Trainer:
 
     # ------------------------------------------------------------------------------------------------ inference
     @torch.no_grad()
-    def render(self, rays_o, rays_d, bg_color=1.0, T_thresh=1e-4, device_compaction=True, mode="single_pass", exchange=None):
+    def render(self, rays_o, rays_d, bg_color=1.0, T_thresh=1e-4, device_compaction=True, mode="single_pass", exchange=None,
+               windows=(48, 976)):
         """run_cuda, inference branch (legacy/nerf/renderer.py:331-372).
 
         mode="loop": the reference's caller-owned loop (march_rays -> field -> composite_rays, n_step = min(N // n_alive, 8)).
@@ -303,6 +304,9 @@ class Trainer:
           into exactly-sized ray-ordered buffers (march_rays_all: one 4-byte host read per frame), one field evaluation, one
           compositor launch with the same early termination.  Samples behind the termination point are evaluated and
           discarded -- the tensor pipe and HBM are far from saturated, the launch/sync chain was the bound.
+        mode="windowed": the loop's early termination without its host-driven iterations -- the march is recorded once, then each
+          depth window (`windows` = samples per ray: the first 48, then the rest) is expanded for the rays still alive, evaluated and
+          composited with K10's recurrence (raymarching.WindowedMarch).  One 4-byte host read per window.
         The epilogue (background mix, depth normalisation) is one kernel writing [r, g, b, depth, weights_sum] rows; the
         returned image / depth / weights_sum are views of that buffer.
         exchange (peer.FrameExchange, multi-GPU): rays_o / rays_d are this rank's share (`exchange.my_rays()`) of the frame; the
@@ -322,6 +326,23 @@ class Trainer:
                 peer.render_finish(image, depth, weights_sum, nears, fars, bg_color, from_first, out)
             return frame[:, :3], frame[:, 3], frame[:, 4]
 
+        if mode == "windowed":
+            wm = raymarching.WindowedMarch(rays_o, rays_d, self.bound, self.density_bitfield, self.cascade, self.grid_size, nears, fars,
+                                           self.dt_gamma, self.max_steps)
+            field = self.model.forward_fused if self.fused and self.fp16 else self.model
+            start = 0
+            for width in windows:
+                width = min(width, self.max_steps - start)
+                if width <= 0:
+                    break
+                w = wm.window(start, width)
+                if w is None:
+                    break
+                with torch.autocast("cuda", dtype=torch.float16, enabled=self.fp16):
+                    sigmas, rgbs = field(w[0], w[1])
+                wm.composite(sigmas, rgbs, w[2], T_thresh)
+                start += width
+            return finish(wm.image, wm.depth, wm.weights_sum, False)
         if mode == "single_pass":
             xyzs, dirs, deltas, rays = raymarching.march_rays_all(rays_o, rays_d, self.bound, self.density_bitfield, self.cascade,
                                                                   self.grid_size, nears, fars, 128, self.dt_gamma, self.max_steps)

@@ -59,6 +59,21 @@ int foc_march_rays_expand(const float *rays_o, const float *rays_d, float bound,
                           uint32_t C, uint32_t H, uint32_t M, const float *nears, const int32_t *rays, const float *noises,
                           const void *scratch, float *xyzs, float *dirs, float *deltas, void *stream);
 
+/* Depth-windowed render (no reference counterpart: replaces the host-driven march_rays / composite_rays loop of
+ * legacy/nerf/renderer.py:337-366 by a few windows over the samples recorded by foc_march_rays_count, same scratch):
+ * window_count    : rays_w[n] = (n, offset, min(count[n] - start, width)) for rays with alive[n] != 0 (alive == NULL: every ray), count 0
+ *                   otherwise; counter[0] += total, counter[1] += N.  wcounts [N] u32 is caller-owned scratch.
+ * window_expand   : foc_march_rays_expand for the records [start, start + count_w) of every ray.
+ * composite_window: K10's recurrence (composite_rays, raymarching.h:18, raymarching.cu:819-905) over each ray's window slice, state
+ *                   carried in place in rays_t / weights_sum / depth / image [N,*]; alive[n] = 0 once the ray terminated. */
+int foc_march_window_count(void *scratch, uint32_t N, uint32_t start, uint32_t width, const uint8_t *alive, uint32_t *wcounts,
+                           int32_t *rays_w, int32_t *counter, void *stream);
+int foc_march_window_expand(const float *rays_o, const float *rays_d, float bound, float dt_gamma, uint32_t max_steps, uint32_t N,
+                            uint32_t C, uint32_t H, uint32_t M, uint32_t start, const float *nears, const int32_t *rays_w,
+                            const float *noises, const void *scratch, float *xyzs, float *dirs, float *deltas, void *stream);
+int foc_composite_window(const float *sigmas, const float *rgbs, const float *deltas, const int32_t *rays_w, uint32_t M, uint32_t N,
+                         float T_thresh, float *rays_t, float *weights_sum, float *depth, float *image, uint8_t *alive, void *stream);
+
 /* replaces composite_rays_train_forward / _backward, raymarching.h:14-15 (raymarching.cu:501-577, 602-682) */
 int foc_composite_rays_train_forward(const float *sigmas, const float *rgbs, const float *deltas, const int32_t *rays,
                                      uint32_t M, uint32_t N, float T_thresh, float *weights_sum, float *depth,

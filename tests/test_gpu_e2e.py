@@ -61,6 +61,26 @@ def test_render_single_pass_matches_loop():
         assert torch.allclose(x, y, atol=tol, rtol=0), float((x - y).abs().max())
 
 
+@pytest.mark.parametrize("windows", [(48, 976), (8, 24, 64, 928), (1024,)])
+def test_render_windowed_matches_loop(windows):
+    """Depth-windowed render (recorded march, K10 recurrence per window, alive flags) reproduces the reference-style loop."""
+    scene, tr = _trainer()
+    for it in range(48):
+        o, d = cases.camera_rays(4096, 300 + it)
+        o, d = torch.from_numpy(o).cuda(), torch.from_numpy(d).cuda()
+        tr.train_step(o, d, scene.render_gt(o, d))
+        if (it + 1) % 16 == 0:
+            tr.update_mean_count()
+    o, d = cases.camera_rays(30000, 9)
+    o, d = torch.from_numpy(o).cuda(), torch.from_numpy(d).cuda()
+    a = tr.render(o, d, mode="windowed", windows=windows)
+    b = tr.render(o, d, mode="loop")
+    assert float(b[2].max()) > 0.5
+    for x, y in zip(a, b):
+        x, y = torch.nan_to_num(x), torch.nan_to_num(y)
+        assert torch.allclose(x, y, atol=2e-3, rtol=0), float((x - y).abs().max())
+
+
 def test_forward_fused_matches_forward():
     """field_glue.cu path == the module-by-module wiring of network_ff.py:51-74, values and parameter gradients."""
     from focnerf_b200.network import NeRFNetwork

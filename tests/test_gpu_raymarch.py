@@ -159,3 +159,41 @@ def test_compact_alive():
         exp = v[v >= 0]
         assert int(n_out.item()) == exp.numel()
         assert torch.equal(out[:exp.numel()], exp)
+
+
+@pytest.mark.parametrize("n_rays,bound,dt_gamma", [(3000, 1.0, 0.0), (40000, 1.0, 0.0), (2000, 2.0, 1.0 / 128)])
+def test_depth_windows_partition_the_march(n_rays, bound, dt_gamma):
+    """WindowedMarch: the windows [0,16), [16,40), [40,max) of every ray, concatenated, are bitwise the ray's samples from
+    march_rays_all; a ray marked dead gets no samples; offsets are the exclusive scan of the window counts."""
+    from focnerf_b200 import raymarching
+    c = cases.march_case(n_rays, 31, bound, dt_gamma=dt_gamma)
+    n_rays = c["rays_o"].shape[0]                                     # + the adversarial rays
+    T = lambda a: torch.from_numpy(np.ascontiguousarray(a)).cuda()
+    o, d, nears, fars, bits = T(c["rays_o"]), T(c["rays_d"]), T(c["nears"]), T(c["fars"]), T(c["bitfield"])
+    x, dr, dl, rays = raymarching.march_rays_all(o, d, c["bound"], bits, c["cascade"], c["H"], nears, fars, 128, c["dt_gamma"], c["max_steps"])
+    rays = rays.cpu().numpy(); x = x.cpu().numpy(); dl = dl.cpu().numpy()
+    wm = raymarching.WindowedMarch(o, d, c["bound"], bits, c["cascade"], c["H"], nears, fars, c["dt_gamma"], c["max_steps"])
+    assert np.array_equal(wm.rays.cpu().numpy(), rays)
+    dead = np.zeros(n_rays, bool); dead[::7] = True
+    taken = np.zeros(n_rays, np.int64)
+    for start, width in ((0, 16), (16, 24), (40, c["max_steps"] - 40)):
+        if start == 16:
+            wm.alive[torch.from_numpy(dead).cuda()] = 0
+        w = wm.window(start, width)
+        rw = wm.rays_w.cpu().numpy()
+        exp = np.clip(rays[:, 2] - start, 0, width)
+        if start >= 16:
+            exp[dead] = 0
+        assert np.array_equal(rw[:, 2], exp)
+        assert np.array_equal(rw[:, 1], np.concatenate([[0], np.cumsum(exp)[:-1]]))
+        if w is None:
+            assert exp.sum() == 0
+            continue
+        wx, wd, wdl = (t.cpu().numpy() for t in w)
+        assert wx.shape[0] >= exp.sum() and wx.shape[0] % 128 == 0
+        assert not wdl[int(exp.sum()):].any()                          # padding rows read as zero
+        src = np.concatenate([np.arange(rays[n, 1] + start, rays[n, 1] + start + exp[n]) for n in np.nonzero(exp)[0]])
+        assert np.array_equal(wx[:len(src)].view(np.uint32), x[src].view(np.uint32))
+        assert np.array_equal(wdl[:len(src)].view(np.uint32), dl[src].view(np.uint32))
+        taken += exp
+    assert np.array_equal(taken[~dead], rays[~dead, 2])

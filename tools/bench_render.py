@@ -1,0 +1,53 @@
+"""Time Trainer.render modes on one GPU: single_pass vs depth-windowed (several window schedules) vs the reference-style loop.
+  python tools/bench_render.py [train_steps]"""
+import os
+import sys
+import time
+
+import torch
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+for p in (ROOT, os.path.join(ROOT, "tests")):
+    sys.path.insert(0, p)
+import cases  # noqa: E402
+import bench  # noqa: E402
+from focnerf_b200 import synthetic  # noqa: E402
+from focnerf_b200.trainer import Trainer  # noqa: E402
+
+
+def main(steps):
+    dev = torch.device("cuda", 0)
+    scene, cascade, grid, bits, thresh = cases.scene_bitfield(1.0)
+    tr = Trainer(bound=1.0, density_grid=torch.from_numpy(grid), device=dev, seed=0, use_graph=True)
+    pool_dev, _ = bench.make_pool(scene, bench.POOL, bench.RAYS_PER_GPU, 1000, dev)
+    for i in range(steps):
+        tr.train_step(*pool_dev[i % bench.POOL])
+        if tr.local_step % 16 == 0:
+            tr.update_mean_count()
+    pose = synthetic.ring_poses(8, radius=2.2, seed=123)[3]
+    o, d = synthetic.get_rays(pose, synthetic.intrinsics(800, 800), 800, 800)
+    o, d = o.to(dev), d.to(dev)
+    ref = None
+    for name, kw in [("single_pass", dict(mode="single_pass")),
+                     ("windowed 48+976", dict(mode="windowed", windows=(48, 976))),
+                     ("windowed 32+992", dict(mode="windowed", windows=(32, 992))),
+                     ("windowed 64+960", dict(mode="windowed", windows=(64, 960))),
+                     ("windowed 24+48+952", dict(mode="windowed", windows=(24, 48, 952))),
+                     ("windowed 32+64+928", dict(mode="windowed", windows=(32, 64, 928))),
+                     ("windowed 16+32+64+912", dict(mode="windowed", windows=(16, 32, 64, 912))),
+                     ("loop", dict(mode="loop"))]:
+        out = tr.render(o, d, **kw)
+        torch.cuda.synchronize()
+        t = time.perf_counter()
+        for _ in range(3):
+            out = tr.render(o, d, **kw)
+        torch.cuda.synchronize()
+        ms = (time.perf_counter() - t) / 3 * 1e3
+        img = torch.nan_to_num(out[0]).clone()
+        if ref is None:
+            ref = img
+        print(f"{name:28s} {ms:8.2f} ms/frame  {0.64 / ms * 1e3:7.1f} Mrays/s   max|img - single_pass| = {float((img - ref).abs().max()):.2e}", flush=True)
+
+
+if __name__ == "__main__":
+    main(int(sys.argv[1]) if len(sys.argv) > 1 else 1100)
