@@ -464,6 +464,11 @@ def run_ours(args):
     }
     if world == 1:
         out["cpu_baseline"] = cpu_baseline(scene, bits, cascade)
+        # configs[0] (north_star: "the reference's PyTorch-only renderer path is timed on the box's own host cores in the same
+        # run, with core count stated, as a reported baseline"): NeRFRenderer.run restated on torch CPU ops, 4096 rays x 128 samples
+        from oracle import torch_renderer
+        ro, rd = cases.camera_rays(RAYS_PER_GPU, 5)
+        out["cpu_torch_renderer"] = torch_renderer.time_cpu(ro, rd, num_steps=128, runs=5, warmup=2)
     print(json.dumps(out))
     shutdown()
 

@@ -108,6 +108,47 @@ class _ffmlp_forward(Function):
 ffmlp_forward = _ffmlp_forward.apply
 
 
+class _ffmlp_forward_side(Function):
+    """Not in the reference: the same kernels with the weights' fp16 side buffers (FFMLP.enable_fp16_side_buffers).  `shadow16`
+    is the fp16 copy of the weights the optimiser keeps current (no per-step cast of the fp32 Parameter); the weight gradient is
+    written straight into `grad16` (no half -> float copy, no AccumulateGrad).  `weights` (the fp32 Parameter) only anchors the
+    autograd graph; its gradient is returned as None."""
+
+    @staticmethod
+    def forward(ctx, inputs, weights, shadow16, grad16, input_dim, output_dim, hidden_dim, num_layers, activation, output_activation,
+                inference=False, calc_grad_inputs=False):
+        require_cuda(inputs, shadow16)
+        if inputs.dtype != torch.float16:
+            inputs = inputs.to(torch.float16)
+        inputs = inputs.contiguous()
+        B = inputs.shape[0]
+        outputs = torch.empty(B, output_dim, device=inputs.device, dtype=torch.float16)
+        if not inference:
+            forward_buffer = torch.empty(num_layers, B, hidden_dim, device=inputs.device, dtype=torch.float16)
+            _backend.ffmlp_forward(inputs, shadow16, B, input_dim, output_dim, hidden_dim, num_layers, activation, output_activation,
+                                   forward_buffer, outputs)
+            ctx.save_for_backward(inputs, shadow16, forward_buffer)
+            ctx.grad16 = grad16
+            ctx.dims = (input_dim, output_dim, hidden_dim, num_layers, activation, output_activation, calc_grad_inputs)
+        else:
+            _backend.ffmlp_inference(inputs, shadow16, B, input_dim, output_dim, hidden_dim, num_layers, activation, output_activation,
+                                     None, outputs)
+        return outputs
+
+    @staticmethod
+    def backward(ctx, grad):
+        B = grad.shape[0]
+        grad = grad.contiguous()
+        if grad.dtype != torch.float16:
+            grad = grad.to(torch.float16)
+        inputs, shadow16, forward_buffer = ctx.saved_tensors
+        input_dim, output_dim, hidden_dim, num_layers, activation, output_activation, calc_grad_inputs = ctx.dims
+        grad_inputs = torch.empty_like(inputs) if calc_grad_inputs else None
+        _backend.ffmlp_backward(grad, inputs, shadow16, forward_buffer, B, input_dim, output_dim, hidden_dim, num_layers,
+                                activation, output_activation, calc_grad_inputs, None, grad_inputs, ctx.grad16)
+        return (grad_inputs if calc_grad_inputs else None), None, None, None, None, None, None, None, None, None, None, None
+
+
 def convert_activation(act):
     return {'relu': 0, 'exponential': 1, 'sine': 2, 'sigmoid': 3, 'squareplus': 4, 'softplus': 5}.get(act, 6)
 
@@ -136,6 +177,30 @@ class FFMLP(nn.Module):
 
     def cleanup(self):
         _backend.free_splitk()
+
+    def enable_fp16_side_buffers(self, grad16=None, shadow16=None):
+        """Not in the reference.  (grad16, shadow16), both flat half tensors of the weights' size: `call_fused` then reads the
+        weights from `shadow16` and writes their gradient into `grad16`; `weights.grad` stays None.  The owner (an optimiser such
+        as focnerf_b200.optim.ScaledAdam, via attach()) must refresh shadow16 after every update."""
+        for t in (grad16, shadow16):
+            if t is not None and (t.dtype != torch.half or t.numel() != self.weights.numel() or not t.is_contiguous()):
+                raise RuntimeError("fp16 side buffers must be contiguous half tensors of the weights' size")
+        if shadow16 is None:
+            shadow16 = torch.empty_like(self.weights, dtype=torch.half)
+        shadow16.copy_(self.weights.detach())
+        if grad16 is None:
+            grad16 = torch.zeros_like(shadow16)
+        self._shadow16, self._grad16 = shadow16, grad16
+        return grad16, shadow16
+
+    def call_fused(self, inputs, calc_grad_inputs):
+        """The kernels on a batch that is already a multiple of 128 rows (no padding cat), through the side buffers when enabled."""
+        if getattr(self, "_shadow16", None) is not None and torch.is_autocast_enabled():
+            return _ffmlp_forward_side.apply(inputs, self.weights, self._shadow16, self._grad16, self.input_dim, self.padded_output_dim,
+                                             self.hidden_dim, self.num_layers, self.activation, self.output_activation, not self.training,
+                                             calc_grad_inputs)
+        return ffmlp_forward(inputs, self.weights, self.input_dim, self.padded_output_dim, self.hidden_dim, self.num_layers, self.activation,
+                             self.output_activation, not self.training, calc_grad_inputs)
 
     def __repr__(self):
         return (f"FFMLP: input_dim={self.input_dim} output_dim={self.output_dim} hidden_dim={self.hidden_dim} "

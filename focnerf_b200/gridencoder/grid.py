@@ -10,6 +10,8 @@ library for the point-major [B,L,C] layout, which IS the [B, L*C] tensor the cal
 identical to the reference's `outputs.permute(1,0,2).reshape(B, L*C)` without that copy (grid.py:57), and
 backward reads the incoming [B, L*C] gradient in place instead of permuting it to [L,B,C] (grid.py:73).
 """
+import math
+
 import numpy as np
 import torch
 import torch.nn as nn
@@ -196,7 +198,12 @@ class GridEncoder(nn.Module):
                 f"align_corners={self.align_corners} interpolation={self.interpolation}")
 
     def forward(self, inputs, bound=1):
-        inputs = (inputs + bound) / (2 * bound)                    # [-bound, bound] -> [0, 1]
+        if math.frexp(float(bound))[0] == 0.5 and inputs.dtype == torch.float32:
+            # power-of-two bound: x / (2 bound) is exact, so 0.5 + x / (2 bound) rounds exactly like (x + bound) / (2 bound)
+            # (grid.py:149) -- the same bits from one elementwise launch instead of two
+            inputs = torch.rsub(inputs, 0.5, alpha=-1.0 / (2.0 * float(bound)))
+        else:
+            inputs = (inputs + bound) / (2 * bound)                # [-bound, bound] -> [0, 1]
         prefix_shape = list(inputs.shape[:-1])
         inputs = inputs.view(-1, self.input_dim)
         outputs = grid_encode(inputs, self.embeddings, self.offsets, self.per_level_scale, self.base_resolution,

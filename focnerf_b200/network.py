@@ -41,18 +41,15 @@ class NeRFNetwork(nn.Module):
         """Same function as forward() for a batch whose size is a multiple of 128 (every march output is), with the
         elementwise wiring fused (field_glue.cu) and the FFMLP kernels called without the module's zero-row padding cat
         (ffmlp.py:157-159 exists only to reach a multiple of 128).  Must run under fp16 autocast, like forward()."""
-        from .ffmlp import ffmlp_forward
         from .field_glue import field_mid, rgb_sigmoid
         B = x.shape[0]
         if B % 128 != 0 or self.sigma_net.hidden_dim != 64 or self.in_dim != 32 or self.in_dim_color != 32:
             return self.forward(x, d)
         sn, cn = self.sigma_net, self.color_net
         enc = self.encoder(x, bound=self.bound)
-        h = ffmlp_forward(enc, sn.weights, sn.input_dim, sn.padded_output_dim, sn.hidden_dim, sn.num_layers, sn.activation,
-                          sn.output_activation, not self.training, enc.requires_grad)
+        h = sn.call_fused(enc, enc.requires_grad)
         sigma, cin = field_mid(h, d)
-        hc = ffmlp_forward(cin, cn.weights, cn.input_dim, cn.padded_output_dim, cn.hidden_dim, cn.num_layers, cn.activation,
-                           cn.output_activation, not self.training, cin.requires_grad)
+        hc = cn.call_fused(cin, cin.requires_grad)
         return sigma, rgb_sigmoid(hc)
 
     def density(self, x):

@@ -228,16 +228,19 @@ class PeerAdam(ScaledAdam):
                                       self.reduced.data_ptr(), 0, n, 0, 0))
         for p, off in zip(self.tail, self.tail_off):
             i = [k for k, q in enumerate(self.params) if q is p][0]
+            s16 = self._side.get(id(p), (None, None))[1]
             rows.append(FocAdamTensor(p.data_ptr(), self.exp_avg[i].data_ptr(), self.exp_avg_sq[i].data_ptr(),
-                                      self.reduced_tail.data_ptr() + 4 * off, 0, p.numel(), 0, 0))
+                                      self.reduced_tail.data_ptr() + 4 * off, 0 if s16 is None else s16.data_ptr(), p.numel(), 0, 0))
         return rows
 
     @torch.no_grad()
     def step(self):
         l, st = lib(), stream()
         for p, off in zip(self.tail, self.tail_off):           # stage the small gradients where the peers can read them
-            if p.grad is not None:
-                self.tail_grad[off:off + p.numel()].copy_(p.grad.reshape(-1))
+            g16 = self._side.get(id(p), (None, None))[0]
+            g = g16 if g16 is not None else p.grad
+            if g is not None:
+                self.tail_grad[off:off + p.numel()].copy_(g.reshape(-1))
         fi = None if self.scale is None else self.found_inf
         self.arena.barrier()                                   # every rank's gradients are complete
         check(l.foc_dp_reduce(ctypes.byref(self._reduce_args), st), "dp_reduce")
@@ -278,3 +281,7 @@ class PeerAdam(ScaledAdam):
 
     def refresh_shadows(self):
         self.shadow16.copy_(self.table.detach())
+        for p in self.tail:
+            s16 = self._side.get(id(p), (None, None))[1]
+            if s16 is not None:
+                s16.copy_(p.detach())

@@ -180,6 +180,7 @@ class _composite_rays_train_mse(Function):
         ctx.save_for_backward(sigmas, rgbs, deltas, rays, gt, weights_sum, image)
         ctx.dims = (M, N, T_thresh, float(bg_color))
         ctx.mark_non_differentiable(weights_sum, depth, image)
+        ctx.set_materialize_grads(False)              # no zero tensors for the three non-differentiable outputs in backward
         return loss.view(()), image, weights_sum, depth
 
     @staticmethod

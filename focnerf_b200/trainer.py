@@ -73,6 +73,10 @@ class Trainer:
                 if fp16:
                     g16, s16 = self.model.encoder.enable_fp16_side_buffers()
                     self.optimizer.attach(self.model.encoder.embeddings, grad16=g16, shadow16=s16)
+            if fp16 and fused:                        # the MLP weights too: no per-step casts, gradients written in place
+                for net in (self.model.sigma_net, self.model.color_net):
+                    g16, s16 = net.enable_fp16_side_buffers()
+                    self.optimizer.attach(net.weights, grad16=g16, shadow16=s16)
             self.scaler = None
         else:
             self.optimizer = torch.optim.Adam(self.model.get_params(lr), betas=(0.9, 0.99), eps=1e-15, fused=True, capturable=use_graph)
@@ -176,7 +180,11 @@ class Trainer:
                     after_march()
                 image, _, _ = self.render_train(rays_o, rays_d, bg_color, counter=counter, mean_count=mean_count)
                 loss = torch.nn.functional.mse_loss(image, gt_rgb)
-        self.optimizer.scale_loss(loss).backward()
+        scale = getattr(self.optimizer, "scale", None)
+        if scale is not None and loss.dim() == 0 and loss.dtype == scale.dtype:
+            loss.backward(gradient=scale.view(()))     # d(scale * loss): the device scalar itself is the seed gradient (no mul / fill launches)
+        else:
+            self.optimizer.scale_loss(loss).backward()
         if self.grad_sync is not None:                 # data-parallel: all-reduce the (scaled) gradients over NCCL
             self.grad_sync()
         return loss

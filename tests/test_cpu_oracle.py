@@ -152,3 +152,30 @@ def test_foc_composite_selection_rule():
     img2, _, ws2 = oracle.foc_composite(sw[0], sw[1], on, of, 1.0)
     np.testing.assert_allclose(ws2, ws, rtol=1e-6)
     assert np.all(img >= 0) and np.all(img <= 1)
+
+
+def test_torch_renderer_restatement_matches_the_c_oracle():
+    """oracle/torch_renderer.py (configs[0], the reference's PyTorch-only path on CPU): its torch restatements of the two CUDA-only
+    operators agree with the C oracle, and its K = 1 render equals the oracle's FOC composite of the same densities / colours."""
+    import torch
+    import foc_eager
+    import oracle
+    from oracle import torch_renderer as tr
+    o, d = cases.camera_rays(300, 4)
+    aabb = np.array([-1] * 3 + [1] * 3, np.float32)
+    n, f = oracle.near_far_from_aabb(o, d, aabb, 0.2)
+    to, td, ta = torch.from_numpy(o), torch.from_numpy(d), torch.from_numpy(aabb)
+    tn, tf = tr.near_far(to, td, ta)
+    assert np.array_equal(tn.numpy(), n) and np.array_equal(tf.numpy(), f)
+    x = np.random.RandomState(0).randn(257, 3).astype(np.float32)
+    np.testing.assert_allclose(tr.freq_encode(torch.from_numpy(x), 4).numpy(), oracle.freq_encode_forward(x, 4), atol=2e-6, rtol=0)
+    torch.manual_seed(1)
+    model = tr.FieldNetwork().eval()
+    with torch.no_grad():
+        sig, rgb = foc_eager.run_object(model, tr.near_far, to, td, ta, 32)
+        img, dep, ws = tr.render(model, to, td, ta, 32)
+    hit = n < 1e30
+    oi, od, ow = oracle.foc_composite(sig.numpy()[None], rgb.numpy()[None], n, f, 1.0)
+    np.testing.assert_allclose(img.numpy()[hit], oi[hit, :3], atol=2e-5, rtol=0)
+    np.testing.assert_allclose(ws.numpy()[hit], ow[hit], atol=2e-5, rtol=0)
+    np.testing.assert_allclose(dep.numpy()[hit], od[hit], atol=2e-5, rtol=0)

@@ -46,8 +46,33 @@ def main(steps):
         img = torch.nan_to_num(out[0]).clone()
         if ref is None:
             ref = img
+        if os.environ.get("FOC_RENDER_BREAKDOWN") == "1" and name in ("single_pass", "windowed 48+976"):
+            breakdown(lambda: tr.render(o, d, **kw), name)
         print(f"{name:28s} {ms:8.2f} ms/frame  {0.64 / ms * 1e3:7.1f} Mrays/s   max|img - single_pass| = {float((img - ref).abs().max()):.2e}", flush=True)
 
 
+def breakdown(fn, title):
+    from torch.profiler import ProfilerActivity, profile
+    fn()
+    torch.cuda.synchronize()
+    with profile(activities=[ProfilerActivity.CUDA, ProfilerActivity.CPU]) as prof:
+        fn()
+        torch.cuda.synchronize()
+    print(f"==== {title}")
+    print(prof.key_averages().table(sort_by="cuda_time_total", row_limit=14, max_name_column_width=70))
+
+
+def multi_breakdown():
+    dev = torch.device("cuda", 0)
+    from focnerf_b200.multiobject import MultiObjectRenderer
+    from focnerf_b200.network import NeRFNetwork
+    o, d = bench.multi_rays(device=dev)
+    aabb = torch.tensor([-1.0] * 3 + [1.0] * 3, device=dev)
+    r = MultiObjectRenderer(bench.multi_objects(lambda: NeRFNetwork(bound=1.0), 4, dev), aabb, num_steps=512)
+    breakdown(lambda: r.render(o[:65536], d[:65536], chunk=16384), "multi-object, 65536 rays x 4 objects x 512 samples")
+
+
 if __name__ == "__main__":
+    if os.environ.get("FOC_RENDER_BREAKDOWN") == "1":
+        multi_breakdown()
     main(int(sys.argv[1]) if len(sys.argv) > 1 else 1100)
