@@ -63,7 +63,7 @@ struct BwdSmem {
     __host__ __device__ static uint32_t off_w_out(int L) { return off_w_h(L, L - 1); }                                       // [16 o, 64 j], 2 KB
     __host__ __device__ static uint32_t off_w_in(int L) { return off_w_out(L) + 2048u; }                                     // [64 o, IN i]
     __host__ __device__ static uint32_t off_bars(int L) { return off_w_in(L) + ((kHidden * IN * 2u + 1023u) & ~1023u); }
-    __host__ __device__ static uint32_t total(int L) { return off_bars(L) + 64 + 1024; }
+    __host__ __device__ static uint32_t total(int L) { return off_bars(L) + 128 + 1024; }
 };
 
 template <int IN, int ACT>
@@ -75,15 +75,17 @@ k_mlp_bwd(const __grid_constant__ CUtensorMap tm_fb, const __grid_constant__ CUt
     uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~(uintptr_t)1023);
     const int L = (int)p.num_layers, n_hmm = L - 1;
     uint64_t* bars = reinterpret_cast<uint64_t*>(smem + SM::off_bars(L));
-    uint64_t* bar_ld = bars;
-    uint64_t* bar_mma = bars + 1;
-    uint64_t* bar_w = bars + 2;
-    uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(bars + 3);
+    uint64_t* bar_act = bars;                     // [L] one per stored-activation tile + [L] = the input tile X: each buffer is
+    uint64_t* bar_x = bars + L;                   // refilled for the CTA's NEXT tile as soon as its last reader of this tile is done
+    uint64_t* bar_mma = bars + kMaxLayers + 1;
+    uint64_t* bar_w = bars + kMaxLayers + 2;
+    uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(bars + kMaxLayers + 3);
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
 
     if (threadIdx.x == 0) {
         tma_prefetch_desc(&tm_fb); tma_prefetch_desc(&tm_in); tma_prefetch_desc(&tm_win); tma_prefetch_desc(&tm_w);
-        mbar_init(bar_ld, 1); mbar_init(bar_mma, 1); mbar_init(bar_w, 1);
+        for (int l = 0; l <= L; ++l) mbar_init(bar_act + l, 1);
+        mbar_init(bar_mma, 1); mbar_init(bar_w, 1);
         fence_barrier_init();
     }
     if (warp == 0) tmem_alloc(tmem_slot, p.tmem_cols);
@@ -103,6 +105,12 @@ k_mlp_bwd(const __grid_constant__ CUtensorMap tm_fb, const __grid_constant__ CUt
         tma_load_2d(smem + SM::off_w_in(L), &tm_win, bar_w, 0, 0);
         for (int r16 = 0; r16 < n_hmm * 4 + 1; ++r16)
             tma_load_2d(smem + SM::off_w_h(L, 0) + r16 * 2048, &tm_w, bar_w, 0, r16 * 16);
+        for (int l = 0; l < L; ++l) {                                // the CTA's first tile
+            mbar_expect_tx(bar_act + l, kTileBytes);
+            tma_load_2d(smem + SM::off_act(l), &tm_fb, bar_act + l, 0, (int32_t)((size_t)l * p.B + (size_t)blockIdx.x * kTile));
+        }
+        mbar_expect_tx(bar_x, SM::kXBytes);
+        tma_load_2d(smem + SM::off_x(L), &tm_in, bar_x, 0, (int32_t)(blockIdx.x * kTile));
     }
 
     // TMEM columns: [0,64) dgrad D | dW_0 (IN) | dW_1..dW_{L-1} (64 each) | dW_L^T (16)
@@ -114,27 +122,30 @@ k_mlp_bwd(const __grid_constant__ CUtensorMap tm_fb, const __grid_constant__ CUt
     const uint32_t row = (uint32_t)(warp * 32 + lane);
     const uint32_t t_lane = tmem + ((uint32_t)(warp * 32) << 16);
     uint32_t ld_phase = 0, mma_phase = 0, acc_w = 0;      // acc_w: 0 on the CTA's first tile (overwrite), 1 afterwards
+    uint4 gn0 = make_uint4(0, 0, 0, 0), gn1 = gn0;        // this thread's row of the NEXT tile's output gradient, prefetched
+    if (blockIdx.x < p.num_tiles) {
+        const uint4* g = reinterpret_cast<const uint4*>(p.grad + ((size_t)blockIdx.x * kTile + row) * kOutPad);
+        gn0 = __ldg(g); gn1 = __ldg(g + 1);
+    }
 
     for (uint32_t tile = blockIdx.x; tile < p.num_tiles; tile += gridDim.x) {
         const size_t grow = (size_t)tile * kTile + row;
-        if (threadIdx.x == 0) {
-            mbar_expect_tx(bar_ld, (uint32_t)L * kTileBytes + SM::kXBytes);
-            for (int l = 0; l < L; ++l)
-                tma_load_2d(smem + SM::off_act(l), &tm_fb, bar_ld, 0, (int32_t)((size_t)l * p.B + (size_t)tile * kTile));
-            tma_load_2d(smem + SM::off_x(L), &tm_in, bar_ld, 0, (int32_t)(tile * kTile));
-        }
+        const uint32_t next_tile = tile + gridDim.x;
+        const bool has_next = next_tile < p.num_tiles;
         {   // G tile: this thread's row, 16 halfs = 2 chunks, into the 128-byte-pitch swizzled layout
-            const uint4* g = reinterpret_cast<const uint4*>(p.grad + grow * kOutPad);
-            const uint4 g0 = __ldg(g), g1 = __ldg(g + 1);
-            *reinterpret_cast<uint4*>(smem + SM::off_gz(L) + sw128_off(row, 0)) = g0;
-            *reinterpret_cast<uint4*>(smem + SM::off_gz(L) + sw128_off(row, 1)) = g1;
+            *reinterpret_cast<uint4*>(smem + SM::off_gz(L) + sw128_off(row, 0)) = gn0;
+            *reinterpret_cast<uint4*>(smem + SM::off_gz(L) + sw128_off(row, 1)) = gn1;
+            if (has_next) {
+                const uint4* g = reinterpret_cast<const uint4*>(p.grad + ((size_t)next_tile * kTile + row) * kOutPad);
+                gn0 = __ldg(g); gn1 = __ldg(g + 1);
+            }
         }
         fence_proxy_async_smem();
         tc_fence_before();
         __syncthreads();
         if (threadIdx.x == 0) {
             if (acc_w == 0) mbar_wait(bar_w, 0);
-            mbar_wait(bar_ld, ld_phase);
+            mbar_wait(bar_act + (L - 1), ld_phase);
             tc_fence_after();
             // dA_{L-1} = G . W_L  (K = 16 outputs = the 16 rows of the W_out tile)
             umma_f16(tmem, umma_desc(s_gz, 16, 1024, SWZ_128B), umma_desc(smem_u32(smem + SM::off_w_out(L)), 16, 1024, SWZ_128B), id_dgrad_h, 0);
@@ -146,14 +157,12 @@ k_mlp_bwd(const __grid_constant__ CUtensorMap tm_fb, const __grid_constant__ CUt
                          id_wg_out, acc_w | (k > 0));
             umma_commit(bar_mma);
         }
-        // every thread reads the TMA-written activation tiles with generic loads below, so every thread must itself
-        // observe the load barrier's phase (acquire), not just the MMA-issuing thread
-        mbar_wait(bar_ld, ld_phase);
-        ld_phase ^= 1u;
-
         for (int l = L - 1; l >= 0; --l) {
             // ---- epilogue: dZ_l = dA_l (.) act'(A_l)  -> fp16 -> GZ tile
             mbar_wait(bar_mma, mma_phase); mma_phase ^= 1u;
+            // every thread reads the TMA-written activation tile with generic loads below, so every thread must itself
+            // observe its load barrier's phase (acquire), not just the MMA-issuing thread
+            mbar_wait(bar_act + l, ld_phase);
             tc_fence_after();
             uint32_t acc[4][16];
             #pragma unroll
@@ -190,6 +199,13 @@ k_mlp_bwd(const __grid_constant__ CUtensorMap tm_fb, const __grid_constant__ CUt
             tc_fence_before();
             __syncthreads();
             if (threadIdx.x == 0) {
+                // A_l has had its last reader of this tile (dW_{l+1} completed before this epilogue began, the epilogue's own
+                // reads are behind the barrier above): refill the buffer with the next tile's A_l while this tile goes on
+                if (has_next) {
+                    mbar_expect_tx(bar_act + l, kTileBytes);
+                    tma_load_2d(smem + SM::off_act(l), &tm_fb, bar_act + l, 0, (int32_t)((size_t)l * p.B + (size_t)next_tile * kTile));
+                }
+                if (l > 0) mbar_wait(bar_act + (l - 1), ld_phase); else mbar_wait(bar_x, ld_phase);
                 tc_fence_after();
                 if (l > 0) {
                     const uint32_t s_prev = smem_u32(smem + SM::off_act(l - 1));
@@ -238,6 +254,11 @@ k_mlp_bwd(const __grid_constant__ CUtensorMap tm_fb, const __grid_constant__ CUt
                 dst[c] = make_uint4(w[0], w[1], w[2], w[3]);
             }
         }
+        if (threadIdx.x == 0 && has_next) {            // X's last reader (dW_0 / dX) is done
+            mbar_expect_tx(bar_x, SM::kXBytes);
+            tma_load_2d(smem + SM::off_x(L), &tm_in, bar_x, 0, (int32_t)(next_tile * kTile));
+        }
+        ld_phase ^= 1u;
         tc_fence_before();
         __syncthreads();
         acc_w = 1;

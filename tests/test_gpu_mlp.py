@@ -33,7 +33,7 @@ def _oracle(c, calc_grad_inputs=True, fb_for_backward=None):
     return dict(out=out.astype(np.float32), fb=fb.astype(np.float32), grad_weights=gw, grad_inputs=None if gi is None else gi.astype(np.float32))
 
 
-@pytest.mark.parametrize("input_dim,num_layers,B", [(32, 2, 128), (32, 2, 1280), (32, 3, 1280), (64, 2, 640), (32, 3, 128 * 700)])
+@pytest.mark.parametrize("input_dim,num_layers,B", [(32, 2, 128), (32, 2, 1280), (32, 3, 1280), (64, 2, 640), (32, 3, 128 * 700), (32, 2, 128 * 1001)])
 def test_mlp_vs_oracle(input_dim, num_layers, B):
     c = cases.mlp_case(B, input_dim, 16, num_layers)
     got = runners.mlp_fwd_bwd(ours(), c)
