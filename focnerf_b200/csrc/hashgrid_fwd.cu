@@ -50,38 +50,11 @@ __device__ __forceinline__ void store_row(T* p, const float (&v)[C]) {
     }
 }
 
-template <typename T, int D, int C, int LAYOUT>
-__global__ void __launch_bounds__(256)
-k_grid_fwd(const float* __restrict__ inputs, const T* __restrict__ table, const int32_t* __restrict__ offsets,
-           T* __restrict__ outputs, uint32_t B, uint32_t L, float S, uint32_t H, T* __restrict__ dy_dx,
-           uint32_t gridtype, bool align_corners, uint32_t interp) {
-    pdl_sync();
-    uint32_t b, level;
-    if constexpr (LAYOUT == 0) { b = blockIdx.x * blockDim.x + threadIdx.x; level = blockIdx.y; if (b >= B) return; }
-    else {
-        const uint64_t t = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x;
-        if (t >= (uint64_t)B * L) return;
-        split_index(t, L, b, level);
-    }
-    T* out = LAYOUT == 0 ? outputs + ((size_t)level * B + b) * C : outputs + ((size_t)b * L + level) * C;
-    T* dyo = dy_dx ? dy_dx + (((size_t)b * L + level) * D) * C : nullptr;       // [B, L, D, C]
-
-    float x[D];
-    #pragma unroll
-    for (int d = 0; d < D; ++d) x[d] = __ldg(inputs + (size_t)b * D + d);
-    if (grid_oob<D>(x)) {                                                        // gridencoder.cu:110-135
-        float z[C];
-        #pragma unroll
-        for (int c = 0; c < C; ++c) z[c] = 0.f;
-        store_row<T, C>(out, z);
-        if (dyo) { for (int i = 0; i < D * C; ++i) Elem<T>::st(dyo + i, 0.f); }
-        return;
-    }
-    const GridLevel lv = grid_level(offsets, level, S, H);
-    const GridIndexer<D> gidx(gridtype, align_corners, lv.hashmap_size, lv.resolution);
-    const T* tab = table + (size_t)lv.offset * C;
-    float pos[D], pder[D];
-    uint32_t pg[D];
+// one (point, level): locate the cell, gather its 2^D corner rows, blend them in the reference's order -> res[C]
+template <typename T, int D, int C>
+__device__ __forceinline__ void encode_level(const float (&x)[D], const T* __restrict__ tab, const GridLevel& lv, const GridIndexer<D>& gidx,
+                                             bool align_corners, uint32_t interp, float (&pos)[D], float (&pder)[D], uint32_t (&pg)[D],
+                                             float (&res)[C]) {
     grid_locate<D>(x, lv.scale, align_corners, interp, pos, pder, pg);
 
     // gather: all corner rows first (independent loads), then the ordered accumulation of the reference
@@ -113,7 +86,6 @@ k_grid_fwd(const float* __restrict__ inputs, const T* __restrict__ table, const 
         RowVec<T, C>::ld(tab + (size_t)row[0] * C, rows[idx]);
         RowVec<T, C>::ld(tab + (size_t)row[1] * C, rows[idx + 1]);
     }
-    float res[C];
     if constexpr (sizeof(T) == 2 && C % 2 == 0) {
         // c10::Half `results += w * g`: the product is rounded to half, the sum is formed in float and rounded to half
         // (hashgrid.cuh Elem<__half>::acc).  A native fp16 add rounds the exact sum once; rounding through fp32 first is
@@ -139,6 +111,94 @@ k_grid_fwd(const float* __restrict__ inputs, const T* __restrict__ table, const 
             for (int c = 0; c < C; ++c) res[c] = Elem<T>::acc(res[c], w[idx], rows[idx][c]);
         }
     }
+}
+
+// Layout 1 without dy_dx, the hot configuration: a CTA takes 64 consecutive points x all L levels.  Lanes of a warp hold
+// 32 CONSECUTIVE POINTS OF ONE LEVEL (neighbouring samples of a ray share cells on the coarse and middle levels, so a
+// gather request touches few distinct sectors; with levels across the lanes every request touched >= 16), each thread
+// walks levels (warp >> 1) + 4k for its point, and the [64, L*C] tile leaves through shared memory as full rows.
+// ncu (800x800 frame, 23 M points): the point-major mapping was bound by l1tex__data_pipe_lsu_wavefronts (73 %).
+constexpr int kTilePts = 64;
+
+template <typename T, int D, int C>
+__global__ void __launch_bounds__(256)
+k_grid_fwd_tile(const float* __restrict__ inputs, const T* __restrict__ table, const int32_t* __restrict__ offsets,
+                T* __restrict__ outputs, uint32_t B, uint32_t L, float S, uint32_t H, uint32_t gridtype, bool align_corners, uint32_t interp) {
+    pdl_sync();
+    extern __shared__ __align__(16) uint8_t tile_raw[];
+    // [64][L*C (+ one 4-byte pad word when a row element is exactly one word: the fp16 C = 2 table -> conflict-free banks)]
+    constexpr bool kPad = sizeof(T) * C == 4;
+    const uint32_t lane = threadIdx.x & 31u, warp = threadIdx.x >> 5;
+    const uint32_t pt = (warp & 1u) * 32u + lane;
+    const uint32_t b0 = blockIdx.x * kTilePts, b = b0 + pt;
+    const uint32_t row_elems = L * C;
+    const uint32_t row_stride = row_elems + (kPad ? 4 / sizeof(T) : 0);  // in elements
+    T* tile = reinterpret_cast<T*>(tile_raw);
+    if (b < B) {
+        float x[D];
+        #pragma unroll
+        for (int d = 0; d < D; ++d) x[d] = __ldg(inputs + (size_t)b * D + d);
+        const bool oob = grid_oob<D>(x);                               // gridencoder.cu:110-135
+        for (uint32_t level = warp >> 1; level < L; level += 4) {
+            float res[C];
+            if (oob) {
+                #pragma unroll
+                for (int c = 0; c < C; ++c) res[c] = 0.f;
+            } else {
+                const GridLevel lv = grid_level(offsets, level, S, H);
+                const GridIndexer<D> gidx(gridtype, align_corners, lv.hashmap_size, lv.resolution);
+                float pos[D], pder[D];
+                uint32_t pg[D];
+                encode_level<T, D, C>(x, table + (size_t)lv.offset * C, lv, gidx, align_corners, interp, pos, pder, pg, res);
+            }
+            store_row<T, C>(tile + (size_t)pt * row_stride + level * C, res);
+        }
+    }
+    __syncthreads();
+    // the tile is a contiguous run of the [B, L*C] output: consecutive threads store consecutive words
+    const uint32_t npts = min((uint32_t)kTilePts, B - b0);
+    if constexpr (kPad) {
+        const uint32_t* tw = reinterpret_cast<const uint32_t*>(tile_raw);
+        uint32_t* dst = reinterpret_cast<uint32_t*>(outputs + (size_t)b0 * row_elems);      // row_elems * sizeof(T) = 4 L bytes: word aligned
+        for (uint32_t i = threadIdx.x; i < npts * L; i += 256) { const uint32_t r = i / L, c = i - r * L; dst[i] = tw[r * (L + 1) + c]; }
+    } else {
+        for (uint32_t i = threadIdx.x; i < npts * row_elems; i += 256) outputs[(size_t)b0 * row_elems + i] = tile[i];
+    }
+}
+
+template <typename T, int D, int C, int LAYOUT>
+__global__ void __launch_bounds__(256)
+k_grid_fwd(const float* __restrict__ inputs, const T* __restrict__ table, const int32_t* __restrict__ offsets,
+           T* __restrict__ outputs, uint32_t B, uint32_t L, float S, uint32_t H, T* __restrict__ dy_dx,
+           uint32_t gridtype, bool align_corners, uint32_t interp) {
+    pdl_sync();
+    uint32_t b, level;
+    if constexpr (LAYOUT == 0) { b = blockIdx.x * blockDim.x + threadIdx.x; level = blockIdx.y; if (b >= B) return; }
+    else {
+        const uint64_t t = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x;
+        if (t >= (uint64_t)B * L) return;
+        split_index(t, L, b, level);
+    }
+    T* out = LAYOUT == 0 ? outputs + ((size_t)level * B + b) * C : outputs + ((size_t)b * L + level) * C;
+    T* dyo = dy_dx ? dy_dx + (((size_t)b * L + level) * D) * C : nullptr;       // [B, L, D, C]
+
+    float x[D];
+    #pragma unroll
+    for (int d = 0; d < D; ++d) x[d] = __ldg(inputs + (size_t)b * D + d);
+    if (grid_oob<D>(x)) {                                                        // gridencoder.cu:110-135
+        float z[C];
+        #pragma unroll
+        for (int c = 0; c < C; ++c) z[c] = 0.f;
+        store_row<T, C>(out, z);
+        if (dyo) { for (int i = 0; i < D * C; ++i) Elem<T>::st(dyo + i, 0.f); }
+        return;
+    }
+    const GridLevel lv = grid_level(offsets, level, S, H);
+    const GridIndexer<D> gidx(gridtype, align_corners, lv.hashmap_size, lv.resolution);
+    const T* tab = table + (size_t)lv.offset * C;
+    float pos[D], pder[D], res[C];
+    uint32_t pg[D];
+    encode_level<T, D, C>(x, tab, lv, gidx, align_corners, interp, pos, pder, pg, res);
     store_row<T, C>(out, res);
 
     if (!dyo) return;
@@ -184,6 +244,9 @@ int launch_fwd(const float* inputs, const void* table, const int32_t* offsets, v
     if (layout == 0) {
         dim3 grid(ceil_div(B, 256), L);
         foc::launch(k_grid_fwd<T, D, C, 0>, grid, 256, 0, st, inputs, (const T*)table, offsets, (T*)outputs, B, L, S, H, (T*)dy_dx, gridtype, ac, interp);
+    } else if (!dy_dx && (size_t)kTilePts * (L * C * sizeof(T) + 4) <= 48 * 1024) {
+        foc::launch(k_grid_fwd_tile<T, D, C>, ceil_div(B, (uint32_t)kTilePts), 256, (size_t)kTilePts * (L * C * sizeof(T) + 4), st, inputs, (const T*)table, offsets,
+                    (T*)outputs, B, L, S, H, gridtype, ac, interp);
     } else {
         const uint64_t total = (uint64_t)B * L;
         foc::launch(k_grid_fwd<T, D, C, 1>, (uint32_t)((total + 255) / 256), 256, 0, st, inputs, (const T*)table, offsets, (T*)outputs, B, L, S, H, (T*)dy_dx, gridtype, ac, interp);
