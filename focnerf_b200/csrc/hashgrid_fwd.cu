@@ -113,12 +113,89 @@ __device__ __forceinline__ void encode_level(const float (&x)[D], const T* __res
     }
 }
 
+// Per-level constants of the tile kernel, resolved once per CTA (grid_level + GridIndexer cost ~45 instructions per use).
+template <int D>
+struct LevelParams {
+    float scale;
+    uint32_t offset, and_mask, hashed, need_mod, hashmap_size, resolution;
+    uint32_t st[D];
+};
+
+// encode_level for a level whose lanes all take the same path (the tile kernel: the level is warp-uniform), index terms
+// formed once per dimension: (p + 1) * k = p * k + k in the wrapping 32-bit arithmetic of gridencoder.cu:50-84, so the 2^D corner
+// indices are D multiplies + D adds + (D - 1) combines each, instead of 2 D multiplies each.  Same indices, same float
+// operations in the same order, same bits out.
+template <typename T, int D, int C, bool HASHED>
+__device__ __forceinline__ void encode_level_uniform(const float (&x)[D], const T* __restrict__ tab, const LevelParams<D>& P,
+                                                     bool align_corners, uint32_t interp, float (&res)[C]) {
+    constexpr uint32_t primes[7] = {1u, 2654435761u, 805459861u, 3674653429u, 2097192037u, 1434869437u, 2165219737u};
+    float pos[D], pder[D];
+    uint32_t pg[D];
+    grid_locate<D>(x, P.scale, align_corners, interp, pos, pder, pg);
+    uint32_t term[D][2];
+    float wd[D][2];
+    #pragma unroll
+    for (int d = 0; d < D; ++d) {
+        const uint32_t k = HASHED ? primes[d] : P.st[d];
+        term[d][0] = pg[d] * k; term[d][1] = term[d][0] + k;
+        wd[d][0] = __fsub_rn(1.0f, pos[d]); wd[d][1] = pos[d];
+    }
+    float w[1 << D], rows[1 << D][C];
+    #pragma unroll
+    for (int idx = 0; idx < (1 << D); idx += 2) {
+        uint32_t row[2];
+        #pragma unroll
+        for (int s = 0; s < 2; ++s) {
+            float wt = wd[0][(idx + s) & 1];                             // 1 * w_0 is exact: the reference's running product starts at 1
+            uint32_t r = term[0][(idx + s) & 1];
+            #pragma unroll
+            for (int d = 1; d < D; ++d) {
+                const int bit = ((idx + s) >> d) & 1;
+                wt = __fmul_rn(wt, wd[d][bit]);
+                r = HASHED ? (r ^ term[d][bit]) : (r + term[d][bit]);
+            }
+            w[idx + s] = wt; row[s] = r & P.and_mask;
+        }
+        if constexpr (sizeof(T) == 2 && C == 2) {
+            if (row[1] == row[0] + 1 && (row[0] & 1u) == 0) {
+                const uint2 u = __ldg(reinterpret_cast<const uint2*>(tab + (size_t)row[0] * 2));
+                const __half2 a = *reinterpret_cast<const __half2*>(&u.x), b = *reinterpret_cast<const __half2*>(&u.y);
+                rows[idx][0] = __low2float(a); rows[idx][1] = __high2float(a); rows[idx + 1][0] = __low2float(b); rows[idx + 1][1] = __high2float(b);
+                continue;
+            }
+        }
+        RowVec<T, C>::ld(tab + (size_t)row[0] * C, rows[idx]);
+        RowVec<T, C>::ld(tab + (size_t)row[1] * C, rows[idx + 1]);
+    }
+    if constexpr (sizeof(T) == 2 && C % 2 == 0) {
+        __half2 r2[C / 2];
+        #pragma unroll
+        for (int c = 0; c < C / 2; ++c) r2[c] = __floats2half2_rn(0.f, 0.f);
+        #pragma unroll
+        for (int idx = 0; idx < (1 << D); ++idx) {
+            #pragma unroll
+            for (int c = 0; c < C / 2; ++c)
+                r2[c] = __hadd2(r2[c], __floats2half2_rn(__fmul_rn(w[idx], rows[idx][2 * c]), __fmul_rn(w[idx], rows[idx][2 * c + 1])));
+        }
+        #pragma unroll
+        for (int c = 0; c < C / 2; ++c) { res[2 * c] = __low2float(r2[c]); res[2 * c + 1] = __high2float(r2[c]); }
+    } else {
+        #pragma unroll
+        for (int c = 0; c < C; ++c) res[c] = 0.f;
+        #pragma unroll
+        for (int idx = 0; idx < (1 << D); ++idx) {
+            #pragma unroll
+            for (int c = 0; c < C; ++c) res[c] = Elem<T>::acc(res[c], w[idx], rows[idx][c]);
+        }
+    }
+}
+
 // Layout 1 without dy_dx, the hot configuration: a CTA takes 64 consecutive points x all L levels.  Lanes of a warp hold
 // 32 CONSECUTIVE POINTS OF ONE LEVEL (neighbouring samples of a ray share cells on the coarse and middle levels, so a
 // gather request touches few distinct sectors; with levels across the lanes every request touched >= 16), each thread
 // walks levels (warp >> 1) + 4k for its point, and the [64, L*C] tile leaves through shared memory as full rows.
 // ncu (800x800 frame, 23 M points): the point-major mapping was bound by l1tex__data_pipe_lsu_wavefronts (73 %).
-constexpr int kTilePts = 64;
+constexpr int kTilePts = 64, kTileMaxLevels = 32;
 
 template <typename T, int D, int C>
 __global__ void __launch_bounds__(256)
@@ -134,6 +211,17 @@ k_grid_fwd_tile(const float* __restrict__ inputs, const T* __restrict__ table, c
     const uint32_t row_elems = L * C;
     const uint32_t row_stride = row_elems + (kPad ? 4 / sizeof(T) : 0);  // in elements
     T* tile = reinterpret_cast<T*>(tile_raw);
+    __shared__ LevelParams<D> s_lv[kTileMaxLevels];
+    if (threadIdx.x < L) {
+        const GridLevel lv = grid_level(offsets, threadIdx.x, S, H);
+        const GridIndexer<D> gi(gridtype, align_corners, lv.hashmap_size, lv.resolution);
+        LevelParams<D>& P = s_lv[threadIdx.x];
+        P.scale = lv.scale; P.offset = lv.offset; P.and_mask = gi.and_mask; P.hashed = gi.hashed; P.need_mod = gi.need_mod;
+        P.hashmap_size = lv.hashmap_size; P.resolution = lv.resolution;
+        #pragma unroll
+        for (int d = 0; d < D; ++d) P.st[d] = gi.st[d];
+    }
+    __syncthreads();
     if (b < B) {
         float x[D];
         #pragma unroll
@@ -145,11 +233,16 @@ k_grid_fwd_tile(const float* __restrict__ inputs, const T* __restrict__ table, c
                 #pragma unroll
                 for (int c = 0; c < C; ++c) res[c] = 0.f;
             } else {
-                const GridLevel lv = grid_level(offsets, level, S, H);
-                const GridIndexer<D> gidx(gridtype, align_corners, lv.hashmap_size, lv.resolution);
-                float pos[D], pder[D];
-                uint32_t pg[D];
-                encode_level<T, D, C>(x, table + (size_t)lv.offset * C, lv, gidx, align_corners, interp, pos, pder, pg, res);
+                const LevelParams<D>& P = s_lv[level];
+                const T* tab = table + (size_t)P.offset * C;
+                if (P.need_mod) {                                        // tiled grids / odd table sizes: the general indexer
+                    GridLevel lv; lv.scale = P.scale; lv.resolution = P.resolution; lv.hashmap_size = P.hashmap_size; lv.offset = P.offset;
+                    const GridIndexer<D> gidx(gridtype, align_corners, lv.hashmap_size, lv.resolution);
+                    float pos[D], pder[D];
+                    uint32_t pg[D];
+                    encode_level<T, D, C>(x, tab, lv, gidx, align_corners, interp, pos, pder, pg, res);
+                } else if (P.hashed) encode_level_uniform<T, D, C, true>(x, tab, P, align_corners, interp, res);
+                else encode_level_uniform<T, D, C, false>(x, tab, P, align_corners, interp, res);
             }
             store_row<T, C>(tile + (size_t)pt * row_stride + level * C, res);
         }
@@ -244,7 +337,7 @@ int launch_fwd(const float* inputs, const void* table, const int32_t* offsets, v
     if (layout == 0) {
         dim3 grid(ceil_div(B, 256), L);
         foc::launch(k_grid_fwd<T, D, C, 0>, grid, 256, 0, st, inputs, (const T*)table, offsets, (T*)outputs, B, L, S, H, (T*)dy_dx, gridtype, ac, interp);
-    } else if (!dy_dx && (size_t)kTilePts * (L * C * sizeof(T) + 4) <= 48 * 1024) {
+    } else if (!dy_dx && L <= (uint32_t)kTileMaxLevels && (size_t)kTilePts * (L * C * sizeof(T) + 4) <= 40 * 1024) {
         foc::launch(k_grid_fwd_tile<T, D, C>, ceil_div(B, (uint32_t)kTilePts), 256, (size_t)kTilePts * (L * C * sizeof(T) + 4), st, inputs, (const T*)table, offsets,
                     (T*)outputs, B, L, S, H, gridtype, ac, interp);
     } else {
