@@ -251,12 +251,72 @@ struct MarchSeq {
         uint16_t samp[kSeqChunk];        // C: indices of the occupied cells the walk visited, in order
     };
 };
+// ---- conservative whole-ray rejection for frame-sized marches (render): most rays of a frame cross the box without touching an
+// occupied cell, and the exact walk costs ~5000 warp instructions per ray whatever it finds.  A 32^3 "any bit set" map per cascade
+// level, dilated by one coarse cell, is built from the bitfield (Morton order: a coarse cell is (H/32)^3 CONSECUTIVE bits), and a
+// warp samples its ray no farther apart than one coarse cell per coordinate: every point of the ray then lies in a sample's coarse
+// cell or one of its 26 neighbours, so "no dilated cell hit on any level" proves that no probe of the exact walk can find an
+// occupied cell -> count 0 without generating the sequence.  Rays that may hit take the exact path unchanged (bit-exact results).
+constexpr uint32_t kCoarse = 32, kCoarseCells = kCoarse * kCoarse * kCoarse;
+
+__global__ void __launch_bounds__(256) k_coarse_any(const uint8_t* __restrict__ grid, uint32_t C, uint32_t H, uint8_t* __restrict__ any) {
+    const uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= C * kCoarseCells) return;
+    const uint32_t c = i / kCoarseCells, m = i - c * kCoarseCells;
+    const uint32_t f = H / kCoarse, bytes = f * f * f / 8;                   // H a power of two >= 64: bytes = 1, 8, 64, ...
+    const uint8_t* src = grid + (size_t)c * ((size_t)H * H * H / 8) + (size_t)m * bytes;
+    uint32_t acc = 0;
+    for (uint32_t k = 0; k < bytes; ++k) acc |= src[k];
+    any[i] = acc != 0;
+}
+
+__global__ void __launch_bounds__(256) k_coarse_dilate(const uint8_t* __restrict__ any, uint32_t C, uint32_t* __restrict__ dil) {
+    const uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;               // (c, Z, Y, X), X fastest: a warp = one word of the map
+    if (i >= C * kCoarseCells) return;
+    const uint32_t c = i / kCoarseCells, q = i - c * kCoarseCells;
+    const int X = (int)(q & 31u), Y = (int)((q >> 5) & 31u), Z = (int)(q >> 10);
+    bool occ = false;
+    for (int dz = -1; dz <= 1; ++dz) for (int dy = -1; dy <= 1; ++dy) for (int dx = -1; dx <= 1; ++dx) {
+        const int x = X + dx, y = Y + dy, z = Z + dz;
+        if ((unsigned)x < kCoarse && (unsigned)y < kCoarse && (unsigned)z < kCoarse)
+            occ |= any[(size_t)c * kCoarseCells + morton3((uint32_t)x, (uint32_t)y, (uint32_t)z)] != 0;
+    }
+    const uint32_t word = __ballot_sync(0xffffffffu, occ);
+    if ((threadIdx.x & 31u) == 0) dil[i >> 5] = word;
+}
+
+// warp-collective; false only when the ray provably meets no occupied cell on any cascade level
+__device__ __forceinline__ bool warp_ray_may_hit(const MarchParams& p, const Ray& r, float near, const uint32_t* __restrict__ dil, uint32_t lane) {
+    const float dmax = fmaxf(fabsf(r.dx), fmaxf(fabsf(r.dy), fabsf(r.dz)));
+    const float span = r.far - near;
+    const float step = (2.0f * fminf(1.0f, p.bound) / (float)kCoarse) / dmax;       // <= one finest-level coarse cell per coordinate
+    const float fn = ceilf(span / step);
+    if (!(span >= 0.0f) || !(step > 0.0f) || !(fn < 4000.0f)) return true;             // degenerate: let the exact walk decide
+    const uint32_t n = (uint32_t)fn + 1u;
+    for (uint32_t base = 0; base < n; base += 32) {
+        const float t = fminf(near + (float)(base + lane) * step, r.far);
+        const float x = clampf(fmaf(t, r.dx, r.ox), -p.bound, p.bound), y = clampf(fmaf(t, r.dy, r.oy), -p.bound, p.bound),
+                    z = clampf(fmaf(t, r.dz, r.oz), -p.bound, p.bound);
+        bool hit = false;
+        for (int c = 0; c < p.C; ++c) {
+            const float rb = 1.0f / fminf(__uint_as_float((uint32_t)(127 + c) << 23), p.bound);
+            const int X = (int)clampf((x * rb + 1.0f) * (0.5f * kCoarse), 0.0f, (float)(kCoarse - 1));
+            const int Y = (int)clampf((y * rb + 1.0f) * (0.5f * kCoarse), 0.0f, (float)(kCoarse - 1));
+            const int Z = (int)clampf((z * rb + 1.0f) * (0.5f * kCoarse), 0.0f, (float)(kCoarse - 1));
+            hit |= (__ldg(dil + (size_t)c * (kCoarseCells / 32) + (uint32_t)(Y + 32 * Z)) >> X) & 1u;
+        }
+        if (__any_sync(0xffffffffu, hit)) return true;
+    }
+    return false;
+}
+
 __device__ __forceinline__ int seq_pos(int k) { return k + (k >> kSeqShift); }
 
 __global__ void __launch_bounds__(32 * kSeqWarps) k_march_record_const(const float* __restrict__ rays_o, const float* __restrict__ rays_d,
                                                             const float* __restrict__ nears, const float* __restrict__ fars,
                                                             const float* __restrict__ noises, uint32_t N, uint32_t max_steps,
-                                                            MarchParams p, uint32_t* __restrict__ counts, float* __restrict__ tbuf) {
+                                                            MarchParams p, uint32_t* __restrict__ counts, float* __restrict__ tbuf,
+                                                            const uint32_t* __restrict__ dil) {
     pdl_sync();
     __shared__ MarchSeq seq[kSeqWarps];
     const uint32_t lane = threadIdx.x & 31u, n = blockIdx.x * (uint32_t)kSeqWarps + (threadIdx.x >> 5);
@@ -265,6 +325,7 @@ __global__ void __launch_bounds__(32 * kSeqWarps) k_march_record_const(const flo
     const uint32_t full = 0xffffffffu;
     const Ray r = load_ray(rays_o, rays_d, n, __ldg(fars + n));
     const float near = __ldg(nears + n);
+    if (dil != nullptr && !warp_ray_may_hit(p, r, near, dil, lane)) { if (lane == 0) counts[n] = 0; return; }
     const float d = step_dt(p, 1.0f);                                // clamp(t * 0) for every finite t
     float t_start = ffma(d, __ldg(noises + n), near);
     float* tb = tbuf + (size_t)n * max_steps;
@@ -571,9 +632,12 @@ FOC_API int foc_packbits(const float* grid, uint32_t N, float density_thresh, ui
 
 // scratch = counts [N] u32 (rounded up to 256 B) + block sums of the multi-block scan + recorded sample parameters [N, max_steps] f32
 static inline size_t march_block_sums_offset(uint32_t N) { return (((size_t)N * sizeof(uint32_t)) + 255) & ~(size_t)255; }
-static inline size_t march_counts_bytes(uint32_t N) {
+static inline size_t march_coarse_offset(uint32_t N) {
     return march_block_sums_offset(N) + ((((size_t)ceil_div(N, kScanBlock) + 1) * sizeof(uint32_t) + 255) & ~(size_t)255);
 }
+constexpr uint32_t kRejectMinRays = 16384;          // below this the march is one latency-bound wave: the pre-test would only add launches
+constexpr size_t kCoarseBytes = 8 * ((size_t)kCoarseCells + kCoarseCells / 8);      // C <= 8: any-bytes + dilated bits
+static inline size_t march_counts_bytes(uint32_t N) { return march_coarse_offset(N) + (N >= kRejectMinRays ? kCoarseBytes : 0); }
 FOC_API size_t foc_march_rays_train_scratch_bytes(uint32_t N, uint32_t max_steps) {
     return march_counts_bytes(N) + (size_t)N * max_steps * sizeof(float);
 }
@@ -593,8 +657,18 @@ FOC_API int foc_march_rays_count(const float* rays_o, const float* rays_d, const
     uint32_t* counts = static_cast<uint32_t*>(scratch);
     float* tbuf = reinterpret_cast<float*>(static_cast<uint8_t*>(scratch) + march_counts_bytes(N));
     // constant step: warp-per-ray parallel walk; else serial walk, 4 rays per warp for small batches (see ray_of_thread)
-    if (dt_gamma == 0.0f)
-        foc::launch(k_march_record_const, ceil_div(N, (uint32_t)kSeqWarps), 32 * kSeqWarps, 0, S(stream), rays_o, rays_d, nears, fars, noises, N, max_steps, p, counts, tbuf);
+    if (dt_gamma == 0.0f) {
+        const uint32_t* dil = nullptr;
+        if (N >= kRejectMinRays && H >= 64 && (H & (H - 1)) == 0) {      // frame-sized call: build the dilated coarse occupancy first
+            uint8_t* any = static_cast<uint8_t*>(scratch) + march_coarse_offset(N);
+            uint32_t* d32 = reinterpret_cast<uint32_t*>(any + 8 * (size_t)kCoarseCells);
+            k_coarse_any<<<ceil_div(C * kCoarseCells, 256), 256, 0, S(stream)>>>(grid, C, H, any);
+            k_coarse_dilate<<<ceil_div(C * kCoarseCells, 256), 256, 0, S(stream)>>>(any, C, d32);
+            FOC_LAUNCH_CHECK();
+            dil = d32;
+        }
+        foc::launch(k_march_record_const, ceil_div(N, (uint32_t)kSeqWarps), 32 * kSeqWarps, 0, S(stream), rays_o, rays_d, nears, fars, noises, N, max_steps, p, counts, tbuf, dil);
+    }
     else if (N <= (uint32_t)kNumSMs * 32u * 8u)
         k_march_record<4><<<ceil_div(ceil_div(N, 4) * 32, 128), 128, 0, S(stream)>>>(rays_o, rays_d, nears, fars, noises, N, max_steps, p, counts, tbuf);
     else

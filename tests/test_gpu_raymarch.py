@@ -72,8 +72,9 @@ def test_march_large_batch_multi_block_scan():
     assert np.array_equal(got["offsets"], np.concatenate([[0], np.cumsum(got["counts"])[:-1]]))
     assert int(got["counter"][0]) == int(got["counts"].sum()) <= n * 128 and int(got["counter"][1]) == n
     pos = 0
-    for s0 in range(0, n, 30000):
-        sub = {k: (v[s0:s0 + 30000] if isinstance(v, np.ndarray) and v.shape[:1] == (n,) else v) for k, v in c.items()}
+    # pieces below 16384 rays also run WITHOUT the conservative coarse-occupancy ray rejection that frame-sized calls use
+    for s0 in range(0, n, 15000):
+        sub = {k: (v[s0:s0 + 15000] if isinstance(v, np.ndarray) and v.shape[:1] == (n,) else v) for k, v in c.items()}
         m = sub["rays_o"].shape[0]
         part = runners.march_train(ours(), sub, M=m * 160)
         assert np.array_equal(part["counts"], got["counts"][s0:s0 + m])

@@ -27,6 +27,21 @@ def main(steps):
     pose = synthetic.ring_poses(8, radius=2.2, seed=123)[3]
     o, d = synthetic.get_rays(pose, synthetic.intrinsics(800, 800), 800, 800)
     o, d = o.to(dev), d.to(dev)
+    if os.environ.get("FOC_RENDER_SHARE"):                      # one rank's share of the frame at world = N, on this GPU alone
+        from focnerf_b200.dist import cyclic_tile
+        from focnerf_b200 import peer
+        n_world = int(os.environ["FOC_RENDER_SHARE"])
+        idx = cyclic_tile(800 * 800, 0, n_world).to(dev)
+        oo, dd = o[idx].contiguous(), d[idx].contiguous()
+        for _ in range(2):
+            tr.render(oo, dd)
+        torch.cuda.synchronize()
+        t = time.perf_counter()
+        for _ in range(10):
+            tr.render(oo, dd)
+        torch.cuda.synchronize()
+        print(f"1/{n_world} share ({oo.shape[0]} rays): {(time.perf_counter() - t) / 10 * 1e3:.3f} ms/frame (whole frame / {n_world} would be the ideal)")
+        breakdown(lambda: tr.render(oo, dd), f"1/{n_world} share of the frame, single_pass")
     ref = None
     for name, kw in [("single_pass", dict(mode="single_pass")),
                      ("windowed 48+976", dict(mode="windowed", windows=(48, 976))),
