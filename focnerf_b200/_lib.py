@@ -106,7 +106,7 @@ class KernelTimer:
 
     # kernels launched by one call of each entry point (see the C ABI implementations in csrc/)
     LAUNCHES = {"foc_march_rays_train": 3, "foc_compact_alive": 2, "foc_ffmlp_backward": 2, "foc_sample_uniform": 2,
-                "foc_grid_encode_backward": 2}
+                "foc_grid_encode_backward": 1}
 
     def __init__(self, names=()):
         self.names, self.events, self.calls, self._orig = tuple(names), {}, {}, {}

@@ -5,6 +5,7 @@
 // (k_grid_bwd_scatter).  Both use VECTOR reductions that return nothing (`red.global.add.noftz.f16x2` for the fp16 C=2
 // table, `red.global.add.v2.f32` for fp32), so the L2 atomic units do the read-modify-write and the SM never waits.
 // Order of accumulation is arbitrary, as in the reference: parity for this kernel is tolerance-based.
+#include <cstdlib>
 #include "hashgrid.cuh"
 
 using namespace foc;
@@ -69,12 +70,9 @@ __device__ __forceinline__ void red_row(T* p, const float (&v)[C]) {
 // one sample ([B,L,C] gradients are then read contiguously).  Cells are smaller than the sample spacing here, every
 // update is a different row: nothing to combine, the scatter goes straight to the L2 reduction units.
 template <typename T, int D, int C, int LAYOUT>
-__global__ void __launch_bounds__(256)
-k_grid_bwd_scatter(const T* __restrict__ grad, const float* __restrict__ inputs, const int32_t* __restrict__ offsets,
+__device__ __forceinline__ void scatter_body(uint64_t t, const T* __restrict__ grad, const float* __restrict__ inputs, const int32_t* __restrict__ offsets,
                    T* __restrict__ grad_table, uint32_t B, uint32_t L, float S, uint32_t H, uint32_t gridtype, bool align_corners,
                    uint32_t interp, uint32_t level0, uint32_t nl) {
-    pdl_sync();
-    const uint64_t t = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x;
     if (t >= (uint64_t)B * nl) return;
     uint32_t b, level;
     split_index(t, nl, b, level);
@@ -127,6 +125,16 @@ k_grid_bwd_scatter(const T* __restrict__ grad, const float* __restrict__ inputs,
     }
 }
 
+template <typename T, int D, int C, int LAYOUT>
+__global__ void __launch_bounds__(256)
+k_grid_bwd_scatter(const T* __restrict__ grad, const float* __restrict__ inputs, const int32_t* __restrict__ offsets,
+                   T* __restrict__ grad_table, uint32_t B, uint32_t L, float S, uint32_t H, uint32_t gridtype, bool align_corners,
+                   uint32_t interp, uint32_t level0, uint32_t nl) {
+    pdl_sync();
+    scatter_body<T, D, C, LAYOUT>((uint64_t)blockIdx.x * blockDim.x + threadIdx.x, grad, inputs, offsets, grad_table, B, L, S, H, gridtype,
+                                  align_corners, interp, level0, nl);
+}
+
 // K12 for the COARSE levels: one thread walks kRun consecutive samples of one level and keeps the 2^D corner sums of the
 // current cell in registers, issuing reductions only when the cell changes.  Samples arrive in ray order (the march
 // writes each ray's samples contiguously, ~0.0017 apart in the unit cube), so at resolution 16..64 a thread sees 1-3
@@ -135,13 +143,10 @@ k_grid_bwd_scatter(const T* __restrict__ grad, const float* __restrict__ inputs,
 constexpr int kRun = 16;
 
 template <typename T, int D, int C, int LAYOUT>
-__global__ void __launch_bounds__(128)
-k_grid_bwd_runs(const T* __restrict__ grad, const float* __restrict__ inputs, const int32_t* __restrict__ offsets,
-                T* __restrict__ grad_table, uint32_t B, uint32_t L, float S, uint32_t H, uint32_t gridtype, bool align_corners,
-                uint32_t interp) {
-    pdl_sync();
-    const uint32_t level = blockIdx.y;
-    const uint32_t b0 = (blockIdx.x * blockDim.x + threadIdx.x) * (uint32_t)kRun;
+__device__ __forceinline__ void runs_body(uint32_t level, uint32_t run, const T* __restrict__ grad, const float* __restrict__ inputs,
+                const int32_t* __restrict__ offsets, T* __restrict__ grad_table, uint32_t B, uint32_t L, float S, uint32_t H, uint32_t gridtype,
+                bool align_corners, uint32_t interp) {
+    const uint32_t b0 = run * (uint32_t)kRun;
     if (b0 >= B) return;
     const GridLevel lv = grid_level(offsets, level, S, H);
     const GridIndexer<D> gidx(gridtype, align_corners, lv.hashmap_size, lv.resolution);
@@ -280,6 +285,35 @@ k_grad_tv(const float* __restrict__ inputs, const float* __restrict__ table, flo
     red_row<float, C>(grad + ((size_t)lv.offset + row0) * C, v);
 }
 
+template <typename T, int D, int C, int LAYOUT>
+__global__ void __launch_bounds__(128)
+k_grid_bwd_runs(const T* __restrict__ grad, const float* __restrict__ inputs, const int32_t* __restrict__ offsets,
+                T* __restrict__ grad_table, uint32_t B, uint32_t L, float S, uint32_t H, uint32_t gridtype, bool align_corners,
+                uint32_t interp) {
+    pdl_sync();
+    runs_body<T, D, C, LAYOUT>(blockIdx.y, blockIdx.x * blockDim.x + threadIdx.x, grad, inputs, offsets, grad_table, B, L, S, H, gridtype,
+                               align_corners, interp);
+}
+
+// Both halves in ONE launch: the first `run_ctas` CTAs walk the coarse levels' runs (few, latency-bound threads: 21 % occupancy
+// alone), the rest scatter the fine levels (bound by the L2 reduction units).  Launched one after the other they cost 30 + 50 us;
+// side by side the runs hide under the scatter.  The levels are disjoint table slices, so no ordering is needed between them.
+template <typename T, int D, int C, int LAYOUT>
+__global__ void __launch_bounds__(256, 4)
+k_grid_bwd_fused(const T* __restrict__ grad, const float* __restrict__ inputs, const int32_t* __restrict__ offsets,
+                 T* __restrict__ grad_table, uint32_t B, uint32_t L, float S, uint32_t H, uint32_t gridtype, bool align_corners,
+                 uint32_t interp, uint32_t n_coarse, uint32_t run_ctas_per_level) {
+    pdl_sync();
+    const uint32_t run_ctas = run_ctas_per_level * n_coarse;
+    if (blockIdx.x < run_ctas) {
+        const uint32_t level = blockIdx.x / run_ctas_per_level, blk = blockIdx.x - level * run_ctas_per_level;
+        runs_body<T, D, C, LAYOUT>(level, blk * 256u + threadIdx.x, grad, inputs, offsets, grad_table, B, L, S, H, gridtype, align_corners, interp);
+    } else {
+        scatter_body<T, D, C, LAYOUT>((uint64_t)(blockIdx.x - run_ctas) * 256u + threadIdx.x, grad, inputs, offsets, grad_table, B, L, S, H, gridtype,
+                                      align_corners, interp, n_coarse, L - n_coarse);
+    }
+}
+
 // levels whose resolution is <= kCoarseRes go through the per-thread runs (measured on B200, 156k ray-ordered samples:
 // 162 us all-scatter -> 89 us with the split at 128; 16 -> 148, 64 -> 97, 256 -> 89, 512 -> 93, all levels -> 127)
 constexpr uint32_t kCoarseRes = 128;
@@ -289,6 +323,14 @@ int launch_bwd_layout(const void* grad, const float* inputs, const int32_t* offs
                       float S, uint32_t H, uint32_t gridtype, bool ac, uint32_t interp, cudaStream_t st) {
     uint32_t n_coarse = 0;                                           // same level resolution rule as grid_level()
     while (n_coarse < L && (uint32_t)ceilf(exp2f((float)n_coarse * S) * (float)H - 1.0f) + 1u <= kCoarseRes) ++n_coarse;
+    if (n_coarse > 0 && n_coarse < L && std::getenv("FOC_GRID_BWD_SPLIT") == nullptr) {
+        const uint32_t rpl = ceil_div(ceil_div(B, (uint32_t)kRun), 256u);
+        const uint64_t sc = ((uint64_t)B * (L - n_coarse) + 255) / 256;
+        foc::launch(k_grid_bwd_fused<T, D, C, LAYOUT>, (uint32_t)(rpl * n_coarse + sc), 256, 0, st, (const T*)grad, inputs, offsets, (T*)grad_table, B, L, S, H,
+                    gridtype, ac, interp, n_coarse, rpl);
+        FOC_LAUNCH_CHECK();
+        return 0;
+    }
     if (n_coarse > 0) {
         dim3 rgrid(ceil_div(ceil_div(B, (uint32_t)kRun), 128u), n_coarse);
         foc::launch(k_grid_bwd_runs<T, D, C, LAYOUT>, rgrid, 128, 0, st, (const T*)grad, inputs, offsets, (T*)grad_table, B, L, S, H, gridtype, ac, interp);
