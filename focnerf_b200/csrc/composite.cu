@@ -128,8 +128,27 @@ k_composite_train_bwd(const float* __restrict__ grad_weights_sum, const float* _
 //           registers.  With `ordered` (slices in ascending ray order, what foc_march_rays_train produces) the kernel also
 //           zero-fills every gradient row it does not own a value for -- past the termination sample, the rows of dropped
 //           rays and the padding rows [total, M) -- so the caller need not pre-zero the buffers.
+// HC = true: the colour operand is the colour network's raw output hc [M,16] f16 and rgb = half(sigmoid(hc[0..2])) is formed here
+// with k_rgb_fwd's operations (field_glue.cu) -- the rgb [M,3] tensor and its launch disappear; the backward then emits
+// grad_hc [M,16] f16 directly (k_rgb_bwd's operations).  Same bits as the three-kernel sequence.
+template <bool HC>
+__device__ __forceinline__ void load_colour(const void* __restrict__ colours, size_t i, float& cr, float& cg, float& cb) {
+    if constexpr (HC) {
+        const uint2 v = __ldg(reinterpret_cast<const uint2*>(static_cast<const __half*>(colours) + i * 16));
+        const __half* hv = reinterpret_cast<const __half*>(&v);
+        cr = __half2float(__float2half_rn(1.0f / (1.0f + expf(-__half2float(hv[0])))));
+        cg = __half2float(__float2half_rn(1.0f / (1.0f + expf(-__half2float(hv[1])))));
+        cb = __half2float(__float2half_rn(1.0f / (1.0f + expf(-__half2float(hv[2])))));
+    } else {
+        const float* rgbs = static_cast<const float*>(colours);
+        cr = __ldg(rgbs + 3 * i); cg = __ldg(rgbs + 3 * i + 1); cb = __ldg(rgbs + 3 * i + 2);
+    }
+}
+__device__ __forceinline__ uint32_t pack_h2(float a, float b) { const __half2 h = __floats2half2_rn(a, b); return *reinterpret_cast<const uint32_t*>(&h); }
+
+template <bool HC>
 __global__ void __launch_bounds__(32 * kCompWarpsPerCta)
-k_composite_mse_fwd(const float* __restrict__ sigmas, const float* __restrict__ rgbs, const float* __restrict__ deltas,
+k_composite_mse_fwd(const float* __restrict__ sigmas, const void* __restrict__ rgbs, const float* __restrict__ deltas,
                     const int32_t* __restrict__ rays, const float* __restrict__ gt, float bg, uint32_t M, uint32_t N, float T_thresh,
                     float* __restrict__ weights_sum, float* __restrict__ depth, float* __restrict__ image, float* __restrict__ err) {
     pdl_sync();
@@ -150,7 +169,7 @@ k_composite_mse_fwd(const float* __restrict__ sigmas, const float* __restrict__ 
                 const float2 dl = __ldg(reinterpret_cast<const float2*>(deltas) + i);
                 alpha = 1.0f - __expf(-__ldg(sigmas + i) * dl.x);
                 d1 = dl.y;
-                cr = __ldg(rgbs + 3 * i); cg = __ldg(rgbs + 3 * i + 1); cb = __ldg(rgbs + 3 * i + 2);
+                load_colour<HC>(rgbs, i, cr, cg, cb);
             }
             const float incl = warp_incl_prod(1.0f - alpha, lane);
             const float w = alpha * (T * excl_from_incl_prod(incl, lane));
@@ -191,11 +210,14 @@ __global__ void __launch_bounds__(1024) k_mse_finish(const float* __restrict__ e
     }
 }
 
+template <bool HC>
 __global__ void __launch_bounds__(32 * kCompWarpsPerCta)
 k_composite_mse_bwd(const float* __restrict__ grad_loss, const float* __restrict__ gt, float bg,
-                    const float* __restrict__ sigmas, const float* __restrict__ rgbs, const float* __restrict__ deltas,
+                    const float* __restrict__ sigmas, const void* __restrict__ rgbs, const float* __restrict__ deltas,
                     const int32_t* __restrict__ rays, const float* __restrict__ weights_sum, const float* __restrict__ image,
-                    uint32_t M, uint32_t N, float T_thresh, int ordered, float* __restrict__ grad_sigmas, float* __restrict__ grad_rgbs) {
+                    uint32_t M, uint32_t N, float T_thresh, int ordered, float* __restrict__ grad_sigmas, void* __restrict__ grad_colours) {
+    float* grad_rgbs = static_cast<float*>(grad_colours);            // HC = false: [M,3] f32
+    uint4* grad_hc = static_cast<uint4*>(grad_colours);              // HC = true : [M,16] f16 = two 16-byte words per row
     pdl_sync();
     const int lane = threadIdx.x & 31;
     const uint32_t n = blockIdx.x * kCompWarpsPerCta + (threadIdx.x >> 5);
@@ -204,7 +226,9 @@ k_composite_mse_bwd(const float* __restrict__ grad_loss, const float* __restrict
                    cnt = (uint32_t)__ldg(rays + 3 * (size_t)n + 2);
     auto zero_rows = [&](uint64_t lo, uint64_t hi) {                  // rows [lo, hi) of both gradient arrays
         for (uint64_t i = lo + lane; i < hi; i += 32) {
-            grad_sigmas[i] = 0.f; grad_rgbs[3 * i] = 0.f; grad_rgbs[3 * i + 1] = 0.f; grad_rgbs[3 * i + 2] = 0.f;
+            grad_sigmas[i] = 0.f;
+            if constexpr (HC) { grad_hc[2 * i] = make_uint4(0u, 0u, 0u, 0u); grad_hc[2 * i + 1] = make_uint4(0u, 0u, 0u, 0u); }
+            else { grad_rgbs[3 * i] = 0.f; grad_rgbs[3 * i + 1] = 0.f; grad_rgbs[3 * i + 2] = 0.f; }
         }
     };
     const bool kept = (uint64_t)off + cnt <= M;
@@ -230,7 +254,7 @@ k_composite_mse_bwd(const float* __restrict__ grad_loss, const float* __restrict
         if (valid) {
             d0 = __ldg(deltas + 2 * i);
             alpha = 1.0f - __expf(-__ldg(sigmas + i) * d0);
-            cr = __ldg(rgbs + 3 * i); cg = __ldg(rgbs + 3 * i + 1); cb = __ldg(rgbs + 3 * i + 2);
+            load_colour<HC>(rgbs, i, cr, cg, cb);
         }
         const float incl = warp_incl_prod(1.0f - alpha, lane);
         const float w = alpha * (T * excl_from_incl_prod(incl, lane));
@@ -239,7 +263,11 @@ k_composite_mse_bwd(const float* __restrict__ grad_loss, const float* __restrict
         const uint32_t stop = __ballot_sync(0xffffffffu, valid && T_after < T_thresh);
         const int last = stop ? (__ffs(stop) - 1) : 31;
         if (valid && lane <= last) {
-            grad_rgbs[3 * i] = gr * w; grad_rgbs[3 * i + 1] = gg * w; grad_rgbs[3 * i + 2] = gb * w;
+            if constexpr (HC) {                                        // k_rgb_bwd: the gradient of a half tensor is half; d sigmoid = y (1 - y)
+                const float g0 = __half2float(__float2half_rn(gr * w)) * (1.0f - cr) * cr, g1 = __half2float(__float2half_rn(gg * w)) * (1.0f - cg) * cg,
+                            g2 = __half2float(__float2half_rn(gb * w)) * (1.0f - cb) * cb;
+                grad_hc[2 * i] = make_uint4(pack_h2(g0, g1), pack_h2(g2, 0.f), 0u, 0u); grad_hc[2 * i + 1] = make_uint4(0u, 0u, 0u, 0u);
+            } else { grad_rgbs[3 * i] = gr * w; grad_rgbs[3 * i + 1] = gg * w; grad_rgbs[3 * i + 2] = gb * w; }
             grad_sigmas[i] = d0 * (gr * (T_after * cr - (rf - pr)) + gg * (T_after * cg - (gf - pg)) +
                                    gb * (T_after * cb - (bf - pb)) + ws_term);
         }
@@ -275,8 +303,8 @@ FOC_API int foc_composite_mse_forward(const float* sigmas, const float* rgbs, co
                                       float bg, uint32_t M, uint32_t N, float T_thresh, float* weights_sum, float* depth, float* image,
                                       float* err, float* loss, void* stream) {
     if (N == 0) return 0;
-    foc::launch(k_composite_mse_fwd, ceil_div(N, kCompWarpsPerCta), 32 * kCompWarpsPerCta, 0, S(stream), 
-        sigmas, rgbs, deltas, rays, gt, bg, M, N, T_thresh, weights_sum, depth, image, err);
+    foc::launch(k_composite_mse_fwd<false>, ceil_div(N, kCompWarpsPerCta), 32 * kCompWarpsPerCta, 0, S(stream),
+        sigmas, (const void*)rgbs, deltas, rays, gt, bg, M, N, T_thresh, weights_sum, depth, image, err);
     FOC_LAUNCH_CHECK();
     foc::launch(k_mse_finish, 1, 1024, 0, S(stream), err, N, loss);
     FOC_LAUNCH_CHECK(); return 0;
@@ -286,7 +314,28 @@ FOC_API int foc_composite_mse_backward(const float* grad_loss, const float* gt, 
                                        const float* deltas, const int32_t* rays, const float* weights_sum, const float* image, uint32_t M,
                                        uint32_t N, float T_thresh, int ordered, float* grad_sigmas, float* grad_rgbs, void* stream) {
     if (N == 0) return 0;
-    foc::launch(k_composite_mse_bwd, ceil_div(N, kCompWarpsPerCta), 32 * kCompWarpsPerCta, 0, S(stream), 
-        grad_loss, gt, bg, sigmas, rgbs, deltas, rays, weights_sum, image, M, N, T_thresh, ordered, grad_sigmas, grad_rgbs);
+    foc::launch(k_composite_mse_bwd<false>, ceil_div(N, kCompWarpsPerCta), 32 * kCompWarpsPerCta, 0, S(stream),
+        grad_loss, gt, bg, sigmas, (const void*)rgbs, deltas, rays, weights_sum, image, M, N, T_thresh, ordered, grad_sigmas, (void*)grad_rgbs);
+    FOC_LAUNCH_CHECK(); return 0;
+}
+
+FOC_API int foc_composite_mse_hc_forward(const float* sigmas, const uint16_t* hc, const float* deltas, const int32_t* rays, const float* gt,
+                                         float bg, uint32_t M, uint32_t N, float T_thresh, float* weights_sum, float* depth, float* image,
+                                         float* err, float* loss, void* stream) {
+    if (N == 0) return 0;
+    foc::launch(k_composite_mse_fwd<true>, ceil_div(N, kCompWarpsPerCta), 32 * kCompWarpsPerCta, 0, S(stream),
+        sigmas, (const void*)hc, deltas, rays, gt, bg, M, N, T_thresh, weights_sum, depth, image, err);
+    FOC_LAUNCH_CHECK();
+    foc::launch(k_mse_finish, 1, 1024, 0, S(stream), err, N, loss);
+    FOC_LAUNCH_CHECK(); return 0;
+}
+
+FOC_API int foc_composite_mse_hc_backward(const float* grad_loss, const float* gt, float bg, const float* sigmas, const uint16_t* hc,
+                                          const float* deltas, const int32_t* rays, const float* weights_sum, const float* image, uint32_t M,
+                                          uint32_t N, float T_thresh, float* grad_sigmas, uint16_t* grad_hc, void* stream) {
+    if (N == 0) return 0;
+    if ((reinterpret_cast<uintptr_t>(hc) & 7u) || (reinterpret_cast<uintptr_t>(grad_hc) & 15u)) return FOC_ERR_UNSUPPORTED;
+    foc::launch(k_composite_mse_bwd<true>, ceil_div(N, kCompWarpsPerCta), 32 * kCompWarpsPerCta, 0, S(stream),
+        grad_loss, gt, bg, sigmas, (const void*)hc, deltas, rays, weights_sum, image, M, N, T_thresh, 1, grad_sigmas, (void*)grad_hc);
     FOC_LAUNCH_CHECK(); return 0;
 }

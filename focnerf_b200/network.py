@@ -37,20 +37,23 @@ class NeRFNetwork(nn.Module):
         rgb = torch.sigmoid(h)
         return sigma, rgb
 
-    def forward_fused(self, x, d):
+    def forward_fused(self, x, d, raw_colour=False):
         """Same function as forward() for a batch whose size is a multiple of 128 (every march output is), with the
         elementwise wiring fused (field_glue.cu) and the FFMLP kernels called without the module's zero-row padding cat
-        (ffmlp.py:157-159 exists only to reach a multiple of 128).  Must run under fp16 autocast, like forward()."""
+        (ffmlp.py:157-159 exists only to reach a multiple of 128).  Must run under fp16 autocast, like forward().
+        raw_colour=True returns (sigma, hc [B,16] f16) for raymarching.composite_rays_train_mse_hc, which applies the sigmoid itself."""
         from .field_glue import field_mid, rgb_sigmoid
         B = x.shape[0]
         if B % 128 != 0 or self.sigma_net.hidden_dim != 64 or self.in_dim != 32 or self.in_dim_color != 32:
+            if raw_colour:
+                raise RuntimeError("forward_fused(raw_colour=True) needs a batch that is a multiple of 128 and the 32 -> 64 -> 16 FOC networks")
             return self.forward(x, d)
         sn, cn = self.sigma_net, self.color_net
         enc = self.encoder(x, bound=self.bound)
         h = sn.call_fused(enc, enc.requires_grad)
         sigma, cin = field_mid(h, d)
         hc = cn.call_fused(cin, cin.requires_grad)
-        return sigma, rgb_sigmoid(hc)
+        return (sigma, hc) if raw_colour else (sigma, rgb_sigmoid(hc))
 
     def density(self, x):
         x = self.encoder(x, bound=self.bound)

@@ -128,6 +128,23 @@ class _Backend:
               "composite_mse_backward")
 
     @staticmethod
+    def composite_mse_hc_forward(sigmas, hc, deltas, rays, gt, bg, M, N, T_thresh, weights_sum, depth, image, err, loss):
+        require_cuda(sigmas, hc, deltas, rays, gt, weights_sum, depth, image, err, loss)
+        for t, nm in ((sigmas, "sigmas"), (deltas, "deltas"), (gt, "gt")):
+            _f32c(t, nm)
+        if hc.dtype != torch.float16 or not hc.is_contiguous() or hc.shape[-1] != 16:
+            raise RuntimeError("hc must be a contiguous CUDA half tensor [M, 16]")
+        check(lib().foc_composite_mse_hc_forward(ptr(sigmas), ptr(hc), ptr(deltas), ptr(rays), ptr(gt), bg, M, N, T_thresh, ptr(weights_sum),
+                                                 ptr(depth), ptr(image), ptr(err), ptr(loss), stream()), "composite_mse_hc_forward")
+
+    @staticmethod
+    def composite_mse_hc_backward(grad_loss, gt, bg, sigmas, hc, deltas, rays, weights_sum, image, M, N, T_thresh, grad_sigmas, grad_hc):
+        require_cuda(grad_loss, gt, sigmas, hc, deltas, rays, weights_sum, image, grad_sigmas, grad_hc)
+        check(lib().foc_composite_mse_hc_backward(ptr(grad_loss), ptr(gt), bg, ptr(sigmas), ptr(hc), ptr(deltas), ptr(rays), ptr(weights_sum),
+                                                  ptr(image), M, N, T_thresh, ptr(grad_sigmas), ptr(grad_hc), stream()),
+              "composite_mse_hc_backward")
+
+    @staticmethod
     def compact_alive(rays_alive, n, out, n_out):
         require_cuda(rays_alive, out, n_out)
         scratch = torch.empty(max(4, lib().foc_compact_alive_scratch_bytes(n)), dtype=torch.uint8, device=rays_alive.device)

@@ -197,6 +197,41 @@ class _composite_rays_train_mse(Function):
 composite_rays_train_mse = _composite_rays_train_mse.apply
 
 
+class _composite_rays_train_mse_hc(Function):
+    """_composite_rays_train_mse with the colour network's raw output hc [M,16] f16 as the colour operand: rgb = half(sigmoid(hc[:, :3]))
+    (nerf/network_ff.py:73) is formed inside the compositor and the backward returns grad_hc [M,16] f16 directly -- the sigmoid
+    kernels of the field network and the rgb / grad_rgb [M,3] tensors disappear, the values do not change."""
+
+    @staticmethod
+    def forward(ctx, sigmas, hc, deltas, rays, gt, bg_color=1.0, T_thresh=1e-4):
+        sigmas, gt, hc = sigmas.float().contiguous(), gt.float().contiguous(), hc.contiguous()
+        M, N = sigmas.shape[0], rays.shape[0]
+        dev = sigmas.device
+        weights_sum = torch.empty(N, dtype=torch.float32, device=dev)
+        depth = torch.empty(N, dtype=torch.float32, device=dev)
+        image = torch.empty(N, 3, dtype=torch.float32, device=dev)
+        err = torch.empty(N, dtype=torch.float32, device=dev)
+        loss = torch.empty(1, dtype=torch.float32, device=dev)
+        _backend.composite_mse_hc_forward(sigmas, hc, deltas, rays, gt, float(bg_color), M, N, T_thresh, weights_sum, depth, image, err, loss)
+        ctx.save_for_backward(sigmas, hc, deltas, rays, gt, weights_sum, image)
+        ctx.dims = (M, N, T_thresh, float(bg_color))
+        ctx.mark_non_differentiable(weights_sum, depth, image)
+        ctx.set_materialize_grads(False)
+        return loss.view(()), image, weights_sum, depth
+
+    @staticmethod
+    def backward(ctx, grad_loss, g_image, g_ws, g_depth):
+        sigmas, hc, deltas, rays, gt, weights_sum, image = ctx.saved_tensors
+        M, N, T_thresh, bg = ctx.dims
+        grad_sigmas, grad_hc = torch.empty_like(sigmas), torch.empty_like(hc)          # fully written by the kernel
+        _backend.composite_mse_hc_backward(grad_loss.float().contiguous().view(1), gt, bg, sigmas, hc, deltas, rays, weights_sum, image,
+                                           M, N, T_thresh, grad_sigmas, grad_hc)
+        return grad_sigmas, grad_hc, None, None, None, None, None
+
+
+composite_rays_train_mse_hc = _composite_rays_train_mse_hc.apply
+
+
 class _march_rays(Function):
     @staticmethod
     @_fwd32

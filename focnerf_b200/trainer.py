@@ -32,6 +32,8 @@ class Trainer:
         if density_grid is not None:
             self.set_density_grid(density_grid, density_thresh)
         self.step_counter = torch.zeros(16, 2, dtype=torch.int32, device=self.device)     # renderer.py:96-98
+        import os
+        self._fuse_rgb = os.environ.get("FOC_FUSE_RGB") == "1"
         self.mean_count, self.local_step = 0, 0
         self.grad_sync = None
         # fused: field-network wiring through field_glue.cu (same function, ~25 fewer launches per step)
@@ -165,8 +167,16 @@ class Trainer:
             self.mean_count if mean_count is None else mean_count, perturb, 128, False, self.dt_gamma, self.max_steps)
         if after_march is not None:                    # the pipelined step joins the optimiser's side stream here
             after_march()
-        sigmas, rgbs = self.model.forward_fused(xyzs, dirs)
-        loss, _, _, _ = raymarching.composite_rays_train_mse(sigmas, rgbs, deltas, rays, gt_rgb, bg_color)
+        # FOC_FUSE_RGB=1: the sigmoid of the colour net and its backward inside the compositor (composite_rays_train_mse_hc).  Same
+        # bits, three launches fewer -- and measured 4 us SLOWER per step on B200 (0.402 vs 0.398 ms): the warp-per-ray compositors
+        # are latency-bound, the three expf + divisions per sample lengthen their serial chains by more than the two bandwidth-bound
+        # sigmoid kernels cost.  Off by default.
+        if self._fuse_rgb and xyzs.shape[0] % 128 == 0:
+            sigmas, hc = self.model.forward_fused(xyzs, dirs, raw_colour=True)
+            loss, _, _, _ = raymarching.composite_rays_train_mse_hc(sigmas, hc, deltas, rays, gt_rgb, bg_color)
+        else:
+            sigmas, rgbs = self.model.forward_fused(xyzs, dirs)
+            loss, _, _, _ = raymarching.composite_rays_train_mse(sigmas, rgbs, deltas, rays, gt_rgb, bg_color)
         return loss
 
     def _forward_backward(self, rays_o, rays_d, gt_rgb, bg_color=1.0, counter=None, mean_count=None, after_march=None):

@@ -215,6 +215,15 @@ int foc_composite_mse_forward(const float *sigmas, const float *rgbs, const floa
 int foc_composite_mse_backward(const float *grad_loss, const float *gt, float bg, const float *sigmas, const float *rgbs,
                                const float *deltas, const int32_t *rays, const float *weights_sum, const float *image, uint32_t M,
                                uint32_t N, float T_thresh, int ordered, float *grad_sigmas, float *grad_rgbs, void *stream);
+/* The same pair with the colour network's raw output as the colour operand: hc [M,16] f16, rgb = half(sigmoid(hc[0..2])) formed in the
+ * compositor (replaces torch.sigmoid of nerf/network_ff.py:73 + its backward); grad_hc [M,16] f16 is written for every row (rows
+ * without a gradient and columns 3..15 are zero; slices must be in ascending ray order, as foc_march_rays_train produces). */
+int foc_composite_mse_hc_forward(const float *sigmas, const uint16_t *hc, const float *deltas, const int32_t *rays, const float *gt,
+                                 float bg, uint32_t M, uint32_t N, float T_thresh, float *weights_sum, float *depth, float *image,
+                                 float *err, float *loss, void *stream);
+int foc_composite_mse_hc_backward(const float *grad_loss, const float *gt, float bg, const float *sigmas, const uint16_t *hc,
+                                  const float *deltas, const int32_t *rays, const float *weights_sum, const float *image, uint32_t M,
+                                  uint32_t N, float T_thresh, float *grad_sigmas, uint16_t *grad_hc, void *stream);
 
 /* ---------------------------------------------------------------- optimiser step of the path
  * Dense Adam + dynamic loss scaling, replacing torch.optim.Adam(betas, eps) + torch.amp.GradScaler as the reference's

@@ -148,3 +148,31 @@ def test_composite_mse_matches_unfused():
         for a, b in zip(ga, (sig.grad, rgb.grad)):
             assert torch.isfinite(b).all()
             assert torch.allclose(a, b, rtol=1e-4, atol=1e-6 * float(a.abs().max())), float((a - b).abs().max())
+
+
+def test_composite_mse_hc_equals_sigmoid_then_mse():
+    """composite_rays_train_mse_hc(sigma, hc) == composite_rays_train_mse(sigma, rgb_sigmoid(hc)): same loss / image bits, the same
+    grad_sigma bits and the same grad_hc bits (columns 3..15 and rows without a gradient are zero)."""
+    from focnerf_b200 import raymarching as rm
+    from focnerf_b200.field_glue import rgb_sigmoid
+    c = cases.composite_case(600, 8)
+    rays = c["rays"].copy()
+    dev = "cuda"
+    M, N = c["sigmas"].shape[0], rays.shape[0]
+    g = torch.Generator(device=dev).manual_seed(11)
+    deltas, rays_t = torch.from_numpy(c["deltas"]).to(dev), torch.from_numpy(rays).to(dev)
+    gt = torch.rand(N, 3, device=dev, generator=g)
+    hc0 = (torch.randn(M, 16, device=dev, generator=g) * 2).half()
+    for bg, seed_grad in ((1.0, 1024.0), (0.3, 65536.0)):
+        sig_a = torch.from_numpy(c["sigmas"]).to(dev).requires_grad_(True)
+        hc_a = hc0.clone().requires_grad_(True)
+        loss_a, image_a, ws_a, depth_a = rm.composite_rays_train_mse(sig_a, rgb_sigmoid(hc_a), deltas, rays_t, gt, bg)
+        loss_a.backward(gradient=torch.tensor(seed_grad, device=dev))
+        sig_b = torch.from_numpy(c["sigmas"]).to(dev).requires_grad_(True)
+        hc_b = hc0.clone().requires_grad_(True)
+        loss_b, image_b, ws_b, depth_b = rm.composite_rays_train_mse_hc(sig_b, hc_b, deltas, rays_t, gt, bg)
+        loss_b.backward(gradient=torch.tensor(seed_grad, device=dev))
+        assert torch.equal(loss_a, loss_b) and torch.equal(image_a, image_b) and torch.equal(ws_a, ws_b) and torch.equal(depth_a, depth_b)
+        assert torch.equal(sig_a.grad, sig_b.grad)
+        assert hc_b.grad.dtype == torch.float16 and torch.equal(hc_a.grad, hc_b.grad)
+        assert float(hc_b.grad[:, 3:].abs().max()) == 0.0 and float(hc_b.grad[:, :3].abs().max()) > 0.0
