@@ -123,6 +123,8 @@ class KernelTimer:
 
             def wrapper(*a, _fn=fn, _name=name, _timed=timed):
                 self.calls[_name] += 1
+                if _name == "foc_ffmlp_backward" and a[14] is None:      # grad_weights == NULL: no reduction kernel in this call
+                    self.calls["_ffmlp_backward_no_finish"] = self.calls.get("_ffmlp_backward_no_finish", 0) + 1
                 if not _timed:
                     return _fn(*a)
                 s = torch.cuda.current_stream()
@@ -147,4 +149,5 @@ class KernelTimer:
 
     def kernel_launches(self):
         skip = ("foc_abi_version", "foc_allocate_splitk", "foc_free_splitk")
-        return sum(n * self.LAUNCHES.get(k, 1) for k, n in self.calls.items() if not k.endswith("_bytes") and k not in skip)
+        total = sum(n * self.LAUNCHES.get(k, 1) for k, n in self.calls.items() if not k.endswith("_bytes") and k not in skip and not k.startswith("_"))
+        return total - self.calls.get("_ffmlp_backward_no_finish", 0)

@@ -381,6 +381,7 @@ int launch_bwd(const uint16_t* grad, const uint16_t* inputs, const uint16_t* wei
     const uint32_t grid = bwd_grid(B);
     foc::launch(k_mlp_bwd<IN, ACT>, grid, 128, smem, st, tm_fb, tm_in, tm_win, tm_w, p);
     FOC_LAUNCH_CHECK();
+    if (grad_weights == nullptr) return 0;                         // the caller reduces the partials itself (foc_ffmlp_wgrad_finish)
     foc::launch(k_mlp_wgrad_finish, ceil_div(p.num_params, 32), 256, 0, st, p.partials, grid, p.num_params, reinterpret_cast<__half*>(grad_weights));
     FOC_LAUNCH_CHECK(); return 0;
 }
@@ -390,6 +391,19 @@ int launch_bwd(const uint16_t* grad, const uint16_t* inputs, const uint16_t* wei
 FOC_API size_t foc_ffmlp_backward_scratch_bytes(uint32_t B, uint32_t input_dim, uint32_t hidden_dim, uint32_t num_layers) {
     if (hidden_dim != (uint32_t)kHidden || B % kTile != 0 || num_layers < 1) return 0;
     return (size_t)bwd_grid(B) * num_params_of(input_dim, num_layers) * sizeof(float);
+}
+
+// The second half of foc_ffmlp_backward on its own: reduce the per-CTA fp32 partials a backward call with grad_weights == NULL
+// left in `scratch` (same B, input_dim, num_layers).  Lets a caller run the reduction on another stream, beside the rest of its
+// backward pass: nothing but the optimiser reads the weight gradient.
+FOC_API int foc_ffmlp_wgrad_finish(const void* scratch, uint32_t B, uint32_t input_dim, uint32_t hidden_dim, uint32_t num_layers,
+                                   uint16_t* grad_weights, void* stream) {
+    if (B == 0) return 0;
+    if (hidden_dim != (uint32_t)kHidden || B % kTile != 0 || num_layers < 1 || !scratch || !grad_weights) return FOC_ERR_UNSUPPORTED;
+    const uint32_t n = num_params_of(input_dim, num_layers);
+    foc::launch(k_mlp_wgrad_finish, ceil_div(n, 32), 256, 0, reinterpret_cast<cudaStream_t>(stream), static_cast<const float*>(scratch), bwd_grid(B), n,
+                reinterpret_cast<__half*>(grad_weights));
+    FOC_LAUNCH_CHECK(); return 0;
 }
 
 FOC_API int foc_ffmlp_backward(const uint16_t* grad, const uint16_t* inputs, const uint16_t* weights, const uint16_t* forward_buffer,

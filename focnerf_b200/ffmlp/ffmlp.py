@@ -60,6 +60,20 @@ class _Backend:
                                        ptr(scratch), stream()), "ffmlp_backward")
 
     @staticmethod
+    def ffmlp_backward_partial(grad, inputs, weights, forward_buffer, B, input_dim, output_dim, hidden_dim, num_layers, activation,
+                               output_activation, calc_grad_inputs, grad_inputs, scratch):
+        """ffmlp_backward without the final reduction: the per-CTA fp32 partial weight gradients stay in `scratch`."""
+        _chk_half(grad, "grad"); _chk_half(inputs, "inputs"); _chk_half(weights, "weights"); _chk_half(forward_buffer, "forward_buffer")
+        check(lib().foc_ffmlp_backward(ptr(grad), ptr(inputs), ptr(weights), ptr(forward_buffer), B, input_dim, output_dim,
+                                       hidden_dim, num_layers, activation, output_activation, int(bool(calc_grad_inputs)),
+                                       None, ptr(grad_inputs) if calc_grad_inputs else None, None, ptr(scratch), stream()), "ffmlp_backward")
+
+    @staticmethod
+    def ffmlp_wgrad_finish(scratch, B, input_dim, hidden_dim, num_layers, grad_weights):
+        _chk_half(grad_weights, "grad_weights")
+        check(lib().foc_ffmlp_wgrad_finish(ptr(scratch), B, input_dim, hidden_dim, num_layers, ptr(grad_weights), stream()), "ffmlp_wgrad_finish")
+
+    @staticmethod
     def allocate_splitk(size):
         check(lib().foc_allocate_splitk(size), "allocate_splitk")
 
@@ -116,8 +130,9 @@ class _ffmlp_forward_side(Function):
 
     @staticmethod
     def forward(ctx, inputs, weights, shadow16, grad16, input_dim, output_dim, hidden_dim, num_layers, activation, output_activation,
-                inference=False, calc_grad_inputs=False):
+                inference=False, calc_grad_inputs=False, side=None):
         require_cuda(inputs, shadow16)
+        ctx.side = side
         if inputs.dtype != torch.float16:
             inputs = inputs.to(torch.float16)
         inputs = inputs.contiguous()
@@ -144,13 +159,50 @@ class _ffmlp_forward_side(Function):
         inputs, shadow16, forward_buffer = ctx.saved_tensors
         input_dim, output_dim, hidden_dim, num_layers, activation, output_activation, calc_grad_inputs = ctx.dims
         grad_inputs = torch.empty_like(inputs) if calc_grad_inputs else None
-        _backend.ffmlp_backward(grad, inputs, shadow16, forward_buffer, B, input_dim, output_dim, hidden_dim, num_layers,
-                                activation, output_activation, calc_grad_inputs, None, grad_inputs, ctx.grad16)
-        return (grad_inputs if calc_grad_inputs else None), None, None, None, None, None, None, None, None, None, None, None
+        if ctx.side is None:
+            _backend.ffmlp_backward(grad, inputs, shadow16, forward_buffer, B, input_dim, output_dim, hidden_dim, num_layers,
+                                    activation, output_activation, calc_grad_inputs, None, grad_inputs, ctx.grad16)
+        else:
+            # nothing but the optimiser reads the weight gradient: its reduction runs on a side stream, beside the rest of the backward
+            # pass (the reference ran its split-K weight-gradient GEMMs on side streams as well, ffmlp.cu:801-812)
+            scratch = ctx.side.scratch(id(ctx.grad16), lib().foc_ffmlp_backward_scratch_bytes(B, input_dim, hidden_dim, num_layers), grad.device)
+            _backend.ffmlp_backward_partial(grad, inputs, shadow16, forward_buffer, B, input_dim, output_dim, hidden_dim, num_layers,
+                                            activation, output_activation, calc_grad_inputs, grad_inputs, scratch)
+            with ctx.side.fork():
+                _backend.ffmlp_wgrad_finish(scratch, B, input_dim, hidden_dim, num_layers, ctx.grad16)
+        return (grad_inputs if calc_grad_inputs else None), None, None, None, None, None, None, None, None, None, None, None, None
 
 
 def convert_activation(act):
     return {'relu': 0, 'exponential': 1, 'sine': 2, 'sigmoid': 3, 'squareplus': 4, 'softplus': 5}.get(act, 6)
+
+
+class WgradSide:
+    """A side stream for work nothing on the step's critical path waits for (the MLP weight-gradient reductions).  fork() orders
+    the side stream after everything enqueued so far on the current stream; join() (before the optimiser) orders the current stream
+    after the side work.  Scratch buffers are persistent per user, so no allocation made on one stream is recycled under the other.
+    Plain stream / event dependencies: capturable in a CUDA graph."""
+
+    def __init__(self):
+        self.stream = torch.cuda.Stream()            # created up front: never inside a graph capture
+        self._scratch = {}
+        self._dirty = False
+
+    def scratch(self, key, nbytes, device):
+        t = self._scratch.get(key)
+        if t is None or t.numel() < nbytes:
+            t = self._scratch[key] = torch.empty(max(int(nbytes), 16), dtype=torch.uint8, device=device)
+        return t
+
+    def fork(self):
+        self.stream.wait_stream(torch.cuda.current_stream())
+        self._dirty = True
+        return torch.cuda.stream(self.stream)
+
+    def join(self):
+        if self._dirty:
+            torch.cuda.current_stream().wait_stream(self.stream)
+            self._dirty = False
 
 
 class FFMLP(nn.Module):
@@ -198,7 +250,7 @@ class FFMLP(nn.Module):
         if getattr(self, "_shadow16", None) is not None and torch.is_autocast_enabled():
             return _ffmlp_forward_side.apply(inputs, self.weights, self._shadow16, self._grad16, self.input_dim, self.padded_output_dim,
                                              self.hidden_dim, self.num_layers, self.activation, self.output_activation, not self.training,
-                                             calc_grad_inputs)
+                                             calc_grad_inputs, getattr(self, "_wgrad_side", None))
         return ffmlp_forward(inputs, self.weights, self.input_dim, self.padded_output_dim, self.hidden_dim, self.num_layers, self.activation,
                              self.output_activation, not self.training, calc_grad_inputs)
 

@@ -18,6 +18,8 @@ class Trainer:
         if not torch.cuda.is_available():
             raise RuntimeError("focnerf_b200.Trainer needs a CUDA device (there is no CPU path)")
         import math
+        import os
+        self._wgrad_side = None
         torch.manual_seed(seed)
         self.device = torch.device(device)
         self.bound, self.min_near, self.dt_gamma, self.max_steps = float(bound), min_near, dt_gamma, max_steps
@@ -32,7 +34,6 @@ class Trainer:
         if density_grid is not None:
             self.set_density_grid(density_grid, density_thresh)
         self.step_counter = torch.zeros(16, 2, dtype=torch.int32, device=self.device)     # renderer.py:96-98
-        import os
         self._fuse_rgb = os.environ.get("FOC_FUSE_RGB") == "1"
         self.mean_count, self.local_step = 0, 0
         self.grad_sync = None
@@ -76,9 +77,12 @@ class Trainer:
                     g16, s16 = self.model.encoder.enable_fp16_side_buffers()
                     self.optimizer.attach(self.model.encoder.embeddings, grad16=g16, shadow16=s16)
             if fp16 and fused:                        # the MLP weights too: no per-step casts, gradients written in place
+                from .ffmlp.ffmlp import WgradSide
+                self._wgrad_side = WgradSide() if os.environ.get("FOC_WGRAD_SIDE", "0") == "1" else None
                 for net in (self.model.sigma_net, self.model.color_net):
                     g16, s16 = net.enable_fp16_side_buffers()
                     self.optimizer.attach(net.weights, grad16=g16, shadow16=s16)
+                    net._wgrad_side = self._wgrad_side    # weight-gradient reductions beside the rest of the backward pass
             self.scaler = None
         else:
             self.optimizer = torch.optim.Adam(self.model.get_params(lr), betas=(0.9, 0.99), eps=1e-15, fused=True, capturable=use_graph)
@@ -195,6 +199,8 @@ class Trainer:
             loss.backward(gradient=scale.view(()))     # d(scale * loss): the device scalar itself is the seed gradient (no mul / fill launches)
         else:
             self.optimizer.scale_loss(loss).backward()
+        if self._wgrad_side is not None:
+            self._wgrad_side.join()                    # the optimiser (or a gradient exchange) reads the weight gradients next
         if self.grad_sync is not None:                 # data-parallel: all-reduce the (scaled) gradients over NCCL
             self.grad_sync()
         return loss

@@ -164,6 +164,10 @@ int foc_ffmlp_backward(const uint16_t *grad, const uint16_t *inputs, const uint1
                        uint32_t hidden_dim, uint32_t num_layers, uint32_t activation, uint32_t output_activation,
                        int calc_grad_inputs, uint16_t *backward_buffer, uint16_t *grad_inputs, uint16_t *grad_weights,
                        void *scratch, void *stream);
+/* grad_weights == NULL in foc_ffmlp_backward leaves the per-CTA fp32 partial weight gradients in `scratch`; this reduces them (fixed
+ * order, fp16 result) -- the reference's split-K GEMMs ran on side streams too (ffmlp.cu:801-812, 892-894); here the caller owns the stream. */
+int foc_ffmlp_wgrad_finish(const void *scratch, uint32_t B, uint32_t input_dim, uint32_t hidden_dim, uint32_t num_layers,
+                           uint16_t *grad_weights, void *stream);
 /* kept for API compatibility with ffmlp.h:12-13; no-ops (no side streams, no workspaces) */
 int foc_allocate_splitk(size_t size);
 int foc_free_splitk(void);
