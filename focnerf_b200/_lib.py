@@ -105,7 +105,7 @@ class KernelTimer:
     Launch counts per entry point (kernels per call) are declared in LAUNCHES below."""
 
     # kernels launched by one call of each entry point (see the C ABI implementations in csrc/)
-    LAUNCHES = {"foc_march_rays_train": 3, "foc_compact_alive": 2, "foc_ffmlp_backward": 2, "foc_sample_uniform": 2,
+    LAUNCHES = {"foc_march_rays_train": 2, "foc_compact_alive": 2, "foc_ffmlp_backward": 2, "foc_sample_uniform": 2,
                 "foc_grid_encode_backward": 1}
 
     def __init__(self, names=()):

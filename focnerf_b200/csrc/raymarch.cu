@@ -316,10 +316,12 @@ __global__ void __launch_bounds__(32 * kSeqWarps) k_march_record_const(const flo
                                                             const float* __restrict__ nears, const float* __restrict__ fars,
                                                             const float* __restrict__ noises, uint32_t N, uint32_t max_steps,
                                                             MarchParams p, uint32_t* __restrict__ counts, float* __restrict__ tbuf,
-                                                            const uint32_t* __restrict__ dil) {
+                                                            const uint32_t* __restrict__ dil, const int32_t* __restrict__ counter_in,
+                                                            uint32_t* __restrict__ base_slot) {
     pdl_sync();
     __shared__ MarchSeq seq[kSeqWarps];
     const uint32_t lane = threadIdx.x & 31u, n = blockIdx.x * (uint32_t)kSeqWarps + (threadIdx.x >> 5);
+    if (base_slot != nullptr && blockIdx.x == 0 && threadIdx.x == 0) *base_slot = (uint32_t)counter_in[0];   // see k_march_expand<true>
     if (n >= N) return;                                              // warp-uniform
     MarchSeq& w = seq[threadIdx.x >> 5];
     const uint32_t full = 0xffffffffu;
@@ -526,15 +528,41 @@ __global__ void __launch_bounds__(1024) k_scan_apply(const uint32_t* __restrict_
 // pass 2 (raymarching.cu:404-479), now data-parallel: ONE WARP PER RAY expands the recorded t's into samples with the
 // same float operations the serial walk would have applied, and writes its slice with coalesced 12/12/8-byte rows.
 //   x = clamp(o + t d);  dt = clamp(t gamma);  delta1 = (t + dt) - last_t,  last_t = previous sample's t + dt (t0 first).
+// SELF_SCAN (training-sized batches, foc_march_rays_train): there is no scan launch -- every CTA sums the counts of the rays before
+// its own four (<= 32 independent loads per thread at N = 4096, from L2), writes rays[n] = (n, base + prefix, count) itself, and the
+// warp of the last ray publishes counter[0] = base + total, counter[1] += N.  `base` is the counter[0] the record kernel saw on
+// entry (parked in scratch), as the reference's atomicAdd would have returned it.
+template <bool SELF_SCAN>
 __global__ void __launch_bounds__(128) k_march_expand(const float* __restrict__ rays_o, const float* __restrict__ rays_d,
                                                       const float* __restrict__ nears, const float* __restrict__ noises,
                                                       uint32_t N, uint32_t M, uint32_t max_steps, uint32_t start, MarchParams p,
-                                                      const int32_t* __restrict__ rays, const float* __restrict__ tbuf,
-                                                      float* __restrict__ xyzs, float* __restrict__ dirs, float* __restrict__ deltas) {
+                                                      int32_t* __restrict__ rays, const float* __restrict__ tbuf,
+                                                      float* __restrict__ xyzs, float* __restrict__ dirs, float* __restrict__ deltas,
+                                                      const uint32_t* __restrict__ counts, const uint32_t* __restrict__ base_slot,
+                                                      int32_t* __restrict__ counter) {
     pdl_sync();
     const uint32_t n = (blockIdx.x * blockDim.x + threadIdx.x) >> 5, lane = threadIdx.x & 31u;
-    if (n >= N) return;
-    const uint32_t off = (uint32_t)__ldg(rays + 3 * (size_t)n + 1), num = (uint32_t)__ldg(rays + 3 * (size_t)n + 2);
+    uint32_t off, num;
+    if constexpr (SELF_SCAN) {
+        __shared__ uint32_t s_part[4];
+        const uint32_t first = blockIdx.x * 4u;                         // rays before this CTA's
+        uint32_t acc = 0;
+        for (uint32_t i = threadIdx.x; i < first; i += 128) acc += __ldg(counts + i);
+        acc = __reduce_add_sync(0xffffffffu, acc);
+        if (lane == 0) s_part[threadIdx.x >> 5] = acc;
+        __syncthreads();
+        if (n >= N) return;
+        off = __ldg(base_slot) + s_part[0] + s_part[1] + s_part[2] + s_part[3];
+        for (uint32_t i = first; i < n; ++i) off += __ldg(counts + i);
+        num = __ldg(counts + n);
+        if (lane == 0) {
+            rays[3 * (size_t)n] = (int32_t)n; rays[3 * (size_t)n + 1] = (int32_t)off; rays[3 * (size_t)n + 2] = (int32_t)num;
+            if (n == N - 1) { counter[0] = (int32_t)(off + num); counter[1] += (int32_t)N; }
+        }
+    } else {
+        if (n >= N) return;
+        off = (uint32_t)__ldg(rays + 3 * (size_t)n + 1); num = (uint32_t)__ldg(rays + 3 * (size_t)n + 2);
+    }
     // Rows no ray writes must read as zero (delta == 0 marks padding for the compositors, raymarching.cu:858; the reference
     // wrapper pre-zeroes all three buffers).  Slices are in ascending ray order, so the kept rays are a prefix: the first
     // dropped ray (off <= M < off + num) owns [off, M); if nothing is dropped the last ray owns [off + num, M).
@@ -648,9 +676,12 @@ static inline uint32_t march_block(uint32_t n) { return n <= (uint32_t)kNumSMs *
 static int scan_counts(const uint32_t* counts, uint32_t N, int32_t* rays, int32_t* counter, uint32_t* block_sums, cudaStream_t st);
 
 // record + scan: rays[n] = (n, offset, count), counter[0] += total, counter[1] += N; the recorded parameters stay in `scratch`
-FOC_API int foc_march_rays_count(const float* rays_o, const float* rays_d, const uint8_t* grid, float bound, float dt_gamma,
-                                 uint32_t max_steps, uint32_t N, uint32_t C, uint32_t H, const float* nears, const float* fars,
-                                 int32_t* rays, int32_t* counter, const float* noises, void* scratch, void* stream) {
+// self_scan: leave the scan to k_march_expand<true> (the record kernel parks counter[0] in the first block-sum slot, unused at that size)
+static inline bool march_self_scan_ok(float dt_gamma, uint32_t N) { return dt_gamma == 0.0f && N <= 8 * kScanBlock; }
+
+static int march_count_impl(const float* rays_o, const float* rays_d, const uint8_t* grid, float bound, float dt_gamma,
+                            uint32_t max_steps, uint32_t N, uint32_t C, uint32_t H, const float* nears, const float* fars,
+                            int32_t* rays, int32_t* counter, const float* noises, void* scratch, void* stream, bool self_scan) {
     if (N == 0) return 0;
     if (C == 0 || C > 8 || H == 0 || H > 1024 || (uint64_t)C * H * H * H > (1ull << 24)) return FOC_ERR_UNSUPPORTED;  // fp32 cell index exact (H1)
     const MarchParams p = make_march_params(grid, bound, dt_gamma, max_steps, C, H);
@@ -667,14 +698,23 @@ FOC_API int foc_march_rays_count(const float* rays_o, const float* rays_d, const
             FOC_LAUNCH_CHECK();
             dil = d32;
         }
-        foc::launch(k_march_record_const, ceil_div(N, (uint32_t)kSeqWarps), 32 * kSeqWarps, 0, S(stream), rays_o, rays_d, nears, fars, noises, N, max_steps, p, counts, tbuf, dil);
+        uint32_t* base_slot = self_scan ? reinterpret_cast<uint32_t*>(static_cast<uint8_t*>(scratch) + march_block_sums_offset(N)) : nullptr;
+        foc::launch(k_march_record_const, ceil_div(N, (uint32_t)kSeqWarps), 32 * kSeqWarps, 0, S(stream), rays_o, rays_d, nears, fars, noises, N, max_steps, p, counts, tbuf, dil,
+                    (const int32_t*)counter, base_slot);
     }
     else if (N <= (uint32_t)kNumSMs * 32u * 8u)
         k_march_record<4><<<ceil_div(ceil_div(N, 4) * 32, 128), 128, 0, S(stream)>>>(rays_o, rays_d, nears, fars, noises, N, max_steps, p, counts, tbuf);
     else
         k_march_record<32><<<ceil_div(N, 128), 128, 0, S(stream)>>>(rays_o, rays_d, nears, fars, noises, N, max_steps, p, counts, tbuf);
     FOC_LAUNCH_CHECK();
+    if (self_scan) return 0;
     return scan_counts(counts, N, rays, counter, reinterpret_cast<uint32_t*>(static_cast<uint8_t*>(scratch) + march_block_sums_offset(N)), S(stream));
+}
+
+FOC_API int foc_march_rays_count(const float* rays_o, const float* rays_d, const uint8_t* grid, float bound, float dt_gamma,
+                                 uint32_t max_steps, uint32_t N, uint32_t C, uint32_t H, const float* nears, const float* fars,
+                                 int32_t* rays, int32_t* counter, const float* noises, void* scratch, void* stream) {
+    return march_count_impl(rays_o, rays_d, grid, bound, dt_gamma, max_steps, N, C, H, nears, fars, rays, counter, noises, scratch, stream, false);
 }
 
 // expand the records of foc_march_rays_count (same scratch, same rays) into samples; rays whose slice would pass M write nothing
@@ -685,7 +725,8 @@ FOC_API int foc_march_rays_expand(const float* rays_o, const float* rays_d, floa
     if (C == 0 || C > 8 || H == 0 || H > 1024) return FOC_ERR_UNSUPPORTED;
     const MarchParams p = make_march_params(nullptr, bound, dt_gamma, max_steps, C, H);
     const float* tbuf = reinterpret_cast<const float*>(static_cast<const uint8_t*>(scratch) + march_counts_bytes(N));
-    foc::launch(k_march_expand, ceil_div(N, 4), 128, 0, S(stream), rays_o, rays_d, nears, noises, N, M, max_steps, 0u, p, rays, tbuf, xyzs, dirs, deltas);
+    foc::launch(k_march_expand<false>, ceil_div(N, 4), 128, 0, S(stream), rays_o, rays_d, nears, noises, N, M, max_steps, 0u, p, const_cast<int32_t*>(rays), tbuf, xyzs, dirs, deltas,
+                (const uint32_t*)nullptr, (const uint32_t*)nullptr, (int32_t*)nullptr);
     FOC_LAUNCH_CHECK(); return 0;
 }
 
@@ -729,7 +770,8 @@ FOC_API int foc_march_window_expand(const float* rays_o, const float* rays_d, fl
     if (C == 0 || C > 8 || H == 0 || H > 1024 || start >= max_steps) return FOC_ERR_UNSUPPORTED;
     const MarchParams p = make_march_params(nullptr, bound, dt_gamma, max_steps, C, H);
     const float* tbuf = reinterpret_cast<const float*>(static_cast<const uint8_t*>(scratch) + march_counts_bytes(N));
-    foc::launch(k_march_expand, ceil_div(N, 4), 128, 0, S(stream), rays_o, rays_d, nears, noises, N, M, max_steps, start, p, rays_w, tbuf, xyzs, dirs, deltas);
+    foc::launch(k_march_expand<false>, ceil_div(N, 4), 128, 0, S(stream), rays_o, rays_d, nears, noises, N, M, max_steps, start, p, const_cast<int32_t*>(rays_w), tbuf, xyzs, dirs, deltas,
+                (const uint32_t*)nullptr, (const uint32_t*)nullptr, (int32_t*)nullptr);
     FOC_LAUNCH_CHECK(); return 0;
 }
 
@@ -737,6 +779,16 @@ FOC_API int foc_march_rays_train(const float* rays_o, const float* rays_d, const
                                  uint32_t max_steps, uint32_t N, uint32_t C, uint32_t H, uint32_t M, const float* nears,
                                  const float* fars, float* xyzs, float* dirs, float* deltas, int32_t* rays, int32_t* counter,
                                  const float* noises, void* scratch, void* stream) {
+    if (N != 0 && march_self_scan_ok(dt_gamma, N)) {                   // two launches: record, then an expansion that scans for itself
+        if (int rc = march_count_impl(rays_o, rays_d, grid, bound, dt_gamma, max_steps, N, C, H, nears, fars, rays, counter, noises, scratch, stream, true)) return rc;
+        const MarchParams p = make_march_params(nullptr, bound, dt_gamma, max_steps, C, H);
+        const uint32_t* counts = static_cast<const uint32_t*>(scratch);
+        const uint32_t* base_slot = reinterpret_cast<const uint32_t*>(static_cast<const uint8_t*>(scratch) + march_block_sums_offset(N));
+        const float* tbuf = reinterpret_cast<const float*>(static_cast<const uint8_t*>(scratch) + march_counts_bytes(N));
+        foc::launch(k_march_expand<true>, ceil_div(N, 4), 128, 0, S(stream), rays_o, rays_d, nears, noises, N, M, max_steps, 0u, p, rays, tbuf, xyzs, dirs, deltas,
+                    counts, base_slot, counter);
+        FOC_LAUNCH_CHECK(); return 0;
+    }
     if (int rc = foc_march_rays_count(rays_o, rays_d, grid, bound, dt_gamma, max_steps, N, C, H, nears, fars, rays, counter, noises, scratch, stream)) return rc;
     return foc_march_rays_expand(rays_o, rays_d, bound, dt_gamma, max_steps, N, C, H, M, nears, rays, noises, scratch, xyzs, dirs, deltas, stream);
 }

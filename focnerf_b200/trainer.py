@@ -302,6 +302,8 @@ class Trainer:
 
     def train_step_host(self, rays_o_h, rays_d_h, gt_rgb_h, stage):
         """End-to-end step from PINNED HOST buffers: H2D copies of the batch, the step, D2H read of the loss."""
+        if self.use_graph and self._graph is not None and self.mean_count > 0 and tuple(self._graph[2][0].shape) == tuple(rays_o_h.shape):
+            stage = self._graph[2]                     # straight into the captured step's input buffers: no device-to-device staging copies
         stage[0].copy_(rays_o_h, non_blocking=True)
         stage[1].copy_(rays_d_h, non_blocking=True)
         stage[2].copy_(gt_rgb_h, non_blocking=True)
