@@ -73,7 +73,7 @@ struct FwdSmem {
 template <int IN, int ACT>
 __global__ void __launch_bounds__(128)
 k_mlp_fwd(const __grid_constant__ CUtensorMap tm_in, const __grid_constant__ CUtensorMap tm_win,
-          const __grid_constant__ CUtensorMap tm_w, FwdParams p) {
+          const __grid_constant__ CUtensorMap tm_w, const __grid_constant__ CUtensorMap tm_fb, FwdParams p) {
     using SM = FwdSmem<IN>;
     extern __shared__ uint8_t smem_raw[];
     uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~(uintptr_t)1023);
@@ -87,6 +87,7 @@ k_mlp_fwd(const __grid_constant__ CUtensorMap tm_in, const __grid_constant__ CUt
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
     if (threadIdx.x == 0) {
         tma_prefetch_desc(&tm_in); tma_prefetch_desc(&tm_win); tma_prefetch_desc(&tm_w);
+        if (p.forward_buffer) tma_prefetch_desc(&tm_fb);
         mbar_init(bar_w, 1); mbar_init(bar_in, 1); mbar_init(bar_in + 1, 1); mbar_init(bar_mma, 1);
         fence_barrier_init();
     }
@@ -165,16 +166,14 @@ k_mlp_fwd(const __grid_constant__ CUtensorMap tm_in, const __grid_constant__ CUt
             #pragma unroll
             for (int c = 0; c < 8; ++c)
                 *reinterpret_cast<uint4*>(smem + SM::off_act() + sw128_off(row, c)) = packed[c];
-            if (p.forward_buffer) {
-                uint4* dst = reinterpret_cast<uint4*>(p.forward_buffer + ((size_t)l * p.B + grow) * kHidden);
-                #pragma unroll
-                for (int c = 0; c < 8; ++c) dst[c] = packed[c];
-            }
             fence_proxy_async_smem();
             tc_fence_before();
             __syncthreads();
             // ---- next matmul: hidden l+1, or the output layer
             if (threadIdx.x == 0) {
+                // training: the activation tile goes to forward_buffer as ONE bulk tensor store of the shared-memory tile (the layout
+                // the backward's TMA loads expect), not as 8 x 16-byte stores per thread (the LSU queue was the kernel's lg_throttle)
+                if (p.forward_buffer) { tma_store_2d(&tm_fb, smem + SM::off_act(), 0, (int32_t)((size_t)l * p.B + (size_t)tile * kTile)); bulk_commit(); }
                 tc_fence_after();
                 const bool last = (l + 1 == p.num_layers);
                 const uint32_t sb = smem_u32(smem + (last ? SM::off_wout(n_hmm) : SM::off_wh((int)l)));
@@ -182,6 +181,8 @@ k_mlp_fwd(const __grid_constant__ CUtensorMap tm_in, const __grid_constant__ CUt
                 for (int k = 0; k < kHidden / 16; ++k)
                     umma_f16(tmem, umma_desc(s_act + k * 32, 16, 1024, SWZ_128B), umma_desc(sb + k * 32, 16, 1024, SWZ_128B),
                              last ? idesc_o : idesc_h, k > 0);
+                // the tile is overwritten by the next epilogue, which starts when bar_mma flips: flip it only after the store has read
+                if (p.forward_buffer) bulk_wait_read_all();
                 umma_commit(bar_mma);
             }
         }
@@ -205,6 +206,7 @@ k_mlp_fwd(const __grid_constant__ CUtensorMap tm_in, const __grid_constant__ CUt
         tc_fence_before();
         __syncthreads();                                             // every row drained before the next tile's MMA overwrites D
     }
+    if (threadIdx.x == 0 && p.forward_buffer) bulk_wait_all();
     if (warp == 0) tmem_dealloc(tmem, 64);
 }
 
@@ -213,9 +215,13 @@ int launch_fwd(const uint16_t* inputs, const uint16_t* weights, uint32_t B, uint
                uint32_t output_activation, uint16_t* forward_buffer, uint16_t* outputs, cudaStream_t st) {
     using SM = FwdSmem<IN>;
     const int n_hmm = (int)num_layers - 1;
-    CUtensorMap tm_in, tm_win, tm_w;
+    CUtensorMap tm_in, tm_win, tm_w, tm_fb;
     int rc = make_tmap_f16_2d(&tm_in, inputs, B, IN, kTile, IN);
     if (rc) return rc;
+    if (forward_buffer) {
+        rc = make_tmap_f16_2d(&tm_fb, forward_buffer, (uint64_t)num_layers * B, kHidden, kTile, kHidden);
+        if (rc) return rc;
+    } else tm_fb = tm_in;                                              // unused by the kernel in inference
     rc = make_tmap_f16_2d(&tm_win, weights, kHidden, IN, kHidden, IN);
     if (rc) return rc;
     rc = make_tmap_f16_2d(&tm_w, weights + (size_t)kHidden * IN, (uint64_t)n_hmm * kHidden + kOutPad, kHidden, 16, kHidden);
@@ -236,7 +242,7 @@ int launch_fwd(const uint16_t* inputs, const uint16_t* weights, uint32_t B, uint
     p.num_tiles = B / kTile;
     const uint32_t ctas_per_sm = 4;                                    // 4 x 64 TMEM columns, ~4 x 45 KB shared memory
     const uint32_t grid = p.num_tiles < (uint32_t)kNumSMs * ctas_per_sm ? p.num_tiles : (uint32_t)kNumSMs * ctas_per_sm;
-    foc::launch(k_mlp_fwd<IN, ACT>, grid, 128, smem, st, tm_in, tm_win, tm_w, p);
+    foc::launch(k_mlp_fwd<IN, ACT>, grid, 128, smem, st, tm_in, tm_win, tm_w, tm_fb, p);
     FOC_LAUNCH_CHECK(); return 0;
 }
 
