@@ -136,8 +136,11 @@ __global__ void __launch_bounds__(kThreads) k_adam_step(const __grid_constant__ 
             float g[4], p[4], m[4], v[4];
             load_grad4(T, i, T.n, g);
             if (full) {
-                const float4 P = *reinterpret_cast<const float4*>(T.param + i), M = *reinterpret_cast<const float4*>(T.exp_avg + i),
-                             V = *reinterpret_cast<const float4*>(T.exp_avg_sq + i);
+                // the fp32 master values and moments stream through once per step (294 MB against a 126 MB L2): evict-first loads and
+                // stores, so that what the NEXT step gathers from / scatters into -- the fp16 shadow and the zeroed fp16 gradient written
+                // below with the default policy, 49 MB together -- is still L2-resident when its forward starts
+                const float4 P = __ldcs(reinterpret_cast<const float4*>(T.param + i)), M = __ldcs(reinterpret_cast<const float4*>(T.exp_avg + i)),
+                             V = __ldcs(reinterpret_cast<const float4*>(T.exp_avg_sq + i));
                 p[0] = P.x; p[1] = P.y; p[2] = P.z; p[3] = P.w; m[0] = M.x; m[1] = M.y; m[2] = M.z; m[3] = M.w; v[0] = V.x; v[1] = V.y; v[2] = V.z; v[3] = V.w;
             } else {
                 #pragma unroll
@@ -152,9 +155,9 @@ __global__ void __launch_bounds__(kThreads) k_adam_step(const __grid_constant__ 
                 p[k] = p[k] - step_size * (m[k] / denom);
             }
             if (full) {
-                *reinterpret_cast<float4*>(T.param + i) = make_float4(p[0], p[1], p[2], p[3]);
-                *reinterpret_cast<float4*>(T.exp_avg + i) = make_float4(m[0], m[1], m[2], m[3]);
-                *reinterpret_cast<float4*>(T.exp_avg_sq + i) = make_float4(v[0], v[1], v[2], v[3]);
+                __stcs(reinterpret_cast<float4*>(T.param + i), make_float4(p[0], p[1], p[2], p[3]));
+                __stcs(reinterpret_cast<float4*>(T.exp_avg + i), make_float4(m[0], m[1], m[2], m[3]));
+                __stcs(reinterpret_cast<float4*>(T.exp_avg_sq + i), make_float4(v[0], v[1], v[2], v[3]));
                 const __half2 a = __floats2half2_rn(p[0], p[1]), b = __floats2half2_rn(p[2], p[3]);
                 const uint2 packed = make_uint2(*reinterpret_cast<const uint32_t*>(&a), *reinterpret_cast<const uint32_t*>(&b));
                 if (PEERS && ti == PS.tensor) {
