@@ -109,3 +109,37 @@ def test_freq_and_sh_encoders():
             np.testing.assert_allclose(gi, rgi, rtol=1e-5, atol=1e-5)
     d = x / np.linalg.norm(x, axis=-1, keepdims=True)
     np.testing.assert_allclose(sh_encode(runners.T(d)).cpu().numpy(), oracle.sh4_encode(d), rtol=1e-5, atol=1e-6)
+
+
+@pytest.mark.parametrize("num_layers", [2, 3])
+def test_side_buffers_and_split_weight_gradient_reduction(num_layers):
+    """FFMLP.enable_fp16_side_buffers + call_fused (weights read from the fp16 shadow, gradient written in place) gives the bits of the
+    autograd path; with a WgradSide the reduction runs through foc_ffmlp_backward(grad_weights = NULL) + foc_ffmlp_wgrad_finish on a
+    side stream and still gives the same bits."""
+    from focnerf_b200.ffmlp import FFMLP
+    from focnerf_b200.ffmlp.ffmlp import WgradSide
+    torch.manual_seed(4)
+    B = 128 * 300
+    x0 = torch.randn(B, 32, device="cuda").half()
+    go = (torch.randn(B, 16, device="cuda") * 1e-2).half()
+    outs = []
+    for mode in ("autograd", "side_buffers", "side_stream"):
+        net = FFMLP(32, 16, 64, num_layers).cuda().train()
+        x = x0.clone().requires_grad_()
+        if mode != "autograd":
+            g16, s16 = net.enable_fp16_side_buffers()
+            if mode == "side_stream":
+                net._wgrad_side = WgradSide()
+        with torch.autocast("cuda", dtype=torch.float16):
+            y = net.call_fused(x, True)
+        y.backward(go)
+        if mode == "side_stream":
+            net._wgrad_side.join()
+        torch.cuda.synchronize()
+        gw = net.weights.grad.half() if mode == "autograd" else g16.clone()
+        if mode != "autograd":
+            assert net.weights.grad is None
+        outs.append((y.detach().clone(), x.grad.clone(), gw))
+    for o in outs[1:]:
+        for a, b in zip(outs[0], o):
+            assert torch.equal(a, b)
