@@ -111,11 +111,14 @@ __global__ void __launch_bounds__(kThreads) k_adam_step(const __grid_constant__ 
     pdl_sync();
     const bool bad = found_inf != nullptr && *found_inf != 0.0f;
     __shared__ float s_step_size, s_rsqrt_bc2, s_inv_scale;
+    // the three per-step scalars, one per warp so that the two double-precision pow() run side by side (every CTA pays this prologue)
     if (threadIdx.x == 0) {
-        const double t = (double)(*step + 1);
-        const double bc1 = 1.0 - pow((double)beta1, t), bc2 = 1.0 - pow((double)beta2, t);
+        const double bc1 = 1.0 - pow((double)beta1, (double)(*step + 1));
         s_step_size = (float)((double)*lr_p / bc1);
+    } else if (threadIdx.x == 32) {
+        const double bc2 = 1.0 - pow((double)beta2, (double)(*step + 1));
         s_rsqrt_bc2 = (float)(1.0 / sqrt(bc2));
+    } else if (threadIdx.x == 64) {
         s_inv_scale = scale ? (float)(1.0 / (double)*scale) : 1.0f;
     }
     __syncthreads();
