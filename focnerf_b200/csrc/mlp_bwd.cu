@@ -319,7 +319,7 @@ k_mlp_bwd(const __grid_constant__ CUtensorMap tm_fb, const __grid_constant__ CUt
 // Block = 32 parameters x 8 slices of the CTA range: each thread sums its slice (coalesced 128-byte rows), the 8 slice
 // sums are combined in a fixed order through shared memory -> deterministic, and 8x shorter dependent-load chains.
 __global__ void __launch_bounds__(256)
-k_mlp_wgrad_finish(const float* __restrict__ partials, uint32_t n_cta, uint32_t num_params, __half* __restrict__ grad_weights) {
+k_mlp_wgrad_finish(const float* __restrict__ partials, uint32_t n_cta, uint32_t num_params, __half* __restrict__ grad_weights, int accumulate) {
     pdl_sync();
     __shared__ float s[8][32];
     const uint32_t lane = threadIdx.x & 31, slice = threadIdx.x >> 5;
@@ -335,6 +335,7 @@ k_mlp_wgrad_finish(const float* __restrict__ partials, uint32_t n_cta, uint32_t 
         float t = 0.f;
         #pragma unroll
         for (int k = 0; k < 8; ++k) t += s[k][lane];
+        if (accumulate) t += __half2float(grad_weights[i]);       // `.grad` semantics for a persistent gradient buffer (adding to +0 is exact)
         grad_weights[i] = __float2half_rn(t);
     }
 }
@@ -382,7 +383,7 @@ int launch_bwd(const uint16_t* grad, const uint16_t* inputs, const uint16_t* wei
     foc::launch(k_mlp_bwd<IN, ACT>, grid, 128, smem, st, tm_fb, tm_in, tm_win, tm_w, p);
     FOC_LAUNCH_CHECK();
     if (grad_weights == nullptr) return 0;                         // the caller reduces the partials itself (foc_ffmlp_wgrad_finish)
-    foc::launch(k_mlp_wgrad_finish, ceil_div(p.num_params, 32), 256, 0, st, p.partials, grid, p.num_params, reinterpret_cast<__half*>(grad_weights));
+    foc::launch(k_mlp_wgrad_finish, ceil_div(p.num_params, 32), 256, 0, st, p.partials, grid, p.num_params, reinterpret_cast<__half*>(grad_weights), 0);
     FOC_LAUNCH_CHECK(); return 0;
 }
 
@@ -402,7 +403,19 @@ FOC_API int foc_ffmlp_wgrad_finish(const void* scratch, uint32_t B, uint32_t inp
     if (hidden_dim != (uint32_t)kHidden || B % kTile != 0 || num_layers < 1 || !scratch || !grad_weights) return FOC_ERR_UNSUPPORTED;
     const uint32_t n = num_params_of(input_dim, num_layers);
     foc::launch(k_mlp_wgrad_finish, ceil_div(n, 32), 256, 0, reinterpret_cast<cudaStream_t>(stream), static_cast<const float*>(scratch), bwd_grid(B), n,
-                reinterpret_cast<__half*>(grad_weights));
+                reinterpret_cast<__half*>(grad_weights), 0);
+    FOC_LAUNCH_CHECK(); return 0;
+}
+
+// foc_ffmlp_wgrad_finish that ADDS the reduced gradient to what `grad_weights` holds: the semantics of `.grad` for a persistent
+// fp16 gradient buffer that an optimiser sweep zeroes after use (two backward passes before one step accumulate).
+FOC_API int foc_ffmlp_wgrad_accumulate(const void* scratch, uint32_t B, uint32_t input_dim, uint32_t hidden_dim, uint32_t num_layers,
+                                       uint16_t* grad_weights, void* stream) {
+    if (B == 0) return 0;
+    if (hidden_dim != (uint32_t)kHidden || B % kTile != 0 || num_layers < 1 || !scratch || !grad_weights) return FOC_ERR_UNSUPPORTED;
+    const uint32_t n = num_params_of(input_dim, num_layers);
+    foc::launch(k_mlp_wgrad_finish, ceil_div(n, 32), 256, 0, reinterpret_cast<cudaStream_t>(stream), static_cast<const float*>(scratch), bwd_grid(B), n,
+                reinterpret_cast<__half*>(grad_weights), 1);
     FOC_LAUNCH_CHECK(); return 0;
 }
 

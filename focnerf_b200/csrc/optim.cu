@@ -193,10 +193,18 @@ __global__ void __launch_bounds__(kThreads) k_adam_step(const __grid_constant__ 
 }
 
 // torch.amp.GradScaler.update() (torch/amp/grad_scaler.py, amp_update_scale_cuda_kernel) + the step counter
+// lr != nullptr: also the reference's per-iteration LambdaLR (main_nerf.py:477, scheduler_update_every_step=True):
+//     lr(next iteration) = lr0 * 0.1 ** min(iteration / decay_iters, 1), iteration counted whether or not the step was skipped
 __global__ void k_scaler_update(float* __restrict__ scale, int32_t* __restrict__ growth_tracker, float* __restrict__ found_inf,
-                                int32_t* __restrict__ step, float growth, float backoff, int32_t interval) {
+                                int32_t* __restrict__ step, float growth, float backoff, int32_t interval,
+                                float* __restrict__ lr, int32_t* __restrict__ sched_iter, float lr0, float decay_iters) {
     pdl_sync();
     if (threadIdx.x != 0 || blockIdx.x != 0) return;
+    if (lr != nullptr) {
+        const int32_t it = *sched_iter + 1;
+        *sched_iter = it;
+        *lr = (float)((double)lr0 * pow(0.1, fmin((double)it / (double)decay_iters, 1.0)));
+    }
     const bool bad = found_inf != nullptr && *found_inf != 0.0f;
     if (scale != nullptr) {
         if (bad) { *scale = *scale * backoff; *growth_tracker = 0; }
@@ -270,6 +278,16 @@ FOC_API int foc_adam_step_peers(const FocAdamTensor* tensors, int count, const f
 
 FOC_API int foc_scaler_update(float* scale, int32_t* growth_tracker, float* found_inf, int32_t* step, float growth_factor,
                               float backoff_factor, int32_t growth_interval, void* stream) {
-    foc::launch(k_scaler_update, 1, 32, 0, reinterpret_cast<cudaStream_t>(stream), scale, growth_tracker, found_inf, step, growth_factor, backoff_factor, growth_interval);
+    foc::launch(k_scaler_update, 1, 32, 0, reinterpret_cast<cudaStream_t>(stream), scale, growth_tracker, found_inf, step, growth_factor, backoff_factor,
+                growth_interval, (float*)nullptr, (int32_t*)nullptr, 0.f, 1.f);
+    FOC_LAUNCH_CHECK(); return 0;
+}
+
+FOC_API int foc_scaler_update_sched(float* scale, int32_t* growth_tracker, float* found_inf, int32_t* step, float growth_factor,
+                                    float backoff_factor, int32_t growth_interval, float* lr, int32_t* sched_iter, float lr0,
+                                    float decay_iters, void* stream) {
+    if (lr == nullptr || sched_iter == nullptr || !(decay_iters > 0.f)) return FOC_ERR_UNSUPPORTED;
+    foc::launch(k_scaler_update, 1, 32, 0, reinterpret_cast<cudaStream_t>(stream), scale, growth_tracker, found_inf, step, growth_factor, backoff_factor,
+                growth_interval, lr, sched_iter, lr0, decay_iters);
     FOC_LAUNCH_CHECK(); return 0;
 }

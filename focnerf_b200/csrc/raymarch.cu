@@ -543,15 +543,18 @@ __global__ void __launch_bounds__(128) k_march_expand(const float* __restrict__ 
     pdl_sync();
     const uint32_t n = (blockIdx.x * blockDim.x + threadIdx.x) >> 5, lane = threadIdx.x & 31u;
     uint32_t off, num;
+    uint64_t total;                                                   // end of the last ray's slice: every warp knows it
     if constexpr (SELF_SCAN) {
-        __shared__ uint32_t s_part[4];
+        __shared__ uint32_t s_part[4], s_all[4];
         const uint32_t first = blockIdx.x * 4u;                         // rays before this CTA's
-        uint32_t acc = 0;
-        for (uint32_t i = threadIdx.x; i < first; i += 128) acc += __ldg(counts + i);
+        uint32_t acc = 0, all = 0;
+        for (uint32_t i = threadIdx.x; i < N; i += 128) { const uint32_t c = __ldg(counts + i); all += c; if (i < first) acc += c; }
         acc = __reduce_add_sync(0xffffffffu, acc);
-        if (lane == 0) s_part[threadIdx.x >> 5] = acc;
+        all = __reduce_add_sync(0xffffffffu, all);
+        if (lane == 0) { s_part[threadIdx.x >> 5] = acc; s_all[threadIdx.x >> 5] = all; }
         __syncthreads();
         if (n >= N) return;
+        total = (uint64_t)__ldg(base_slot) + s_all[0] + s_all[1] + s_all[2] + s_all[3];
         off = __ldg(base_slot) + s_part[0] + s_part[1] + s_part[2] + s_part[3];
         for (uint32_t i = first; i < n; ++i) off += __ldg(counts + i);
         num = __ldg(counts + n);
@@ -562,16 +565,23 @@ __global__ void __launch_bounds__(128) k_march_expand(const float* __restrict__ 
     } else {
         if (n >= N) return;
         off = (uint32_t)__ldg(rays + 3 * (size_t)n + 1); num = (uint32_t)__ldg(rays + 3 * (size_t)n + 2);
+        total = (uint64_t)(uint32_t)__ldg(rays + 3 * (size_t)(N - 1) + 1) + (uint32_t)__ldg(rays + 3 * (size_t)(N - 1) + 2);
     }
     // Rows no ray writes must read as zero (delta == 0 marks padding for the compositors, raymarching.cu:858; the reference
     // wrapper pre-zeroes all three buffers).  Slices are in ascending ray order, so the kept rays are a prefix: the first
-    // dropped ray (off <= M < off + num) owns [off, M); if nothing is dropped the last ray owns [off + num, M).
+    // dropped ray (off <= M < off + num) zeroes its own truncated slice [off, M) (< max_steps rows); when nothing is dropped the
+    // tail [total, M) is dealt to ALL warps in 32-row pieces (M = N * max_steps while mean_count <= 0 or with force_all_rays:
+    // 134 MB at 4096 rays, which one warp would take milliseconds to clear).
     {
         const bool kept = (uint64_t)off + num <= M;
-        uint64_t lo = M;
-        if (!kept && off < M) lo = off;
-        else if (kept && n == N - 1) lo = (uint64_t)off + num;
-        for (uint64_t i = lo + lane; i < M; i += 32) {
+        if (!kept && off < M) {
+            for (uint64_t i = (uint64_t)off + lane; i < M; i += 32) {
+                xyzs[3 * i] = 0.f; xyzs[3 * i + 1] = 0.f; xyzs[3 * i + 2] = 0.f;
+                dirs[3 * i] = 0.f; dirs[3 * i + 1] = 0.f; dirs[3 * i + 2] = 0.f;
+                reinterpret_cast<float2*>(deltas)[i] = make_float2(0.f, 0.f);
+            }
+        }
+        for (uint64_t i = total + (uint64_t)n * 32u + lane; i < M; i += (uint64_t)N * 32u) {
             xyzs[3 * i] = 0.f; xyzs[3 * i + 1] = 0.f; xyzs[3 * i + 2] = 0.f;
             dirs[3 * i] = 0.f; dirs[3 * i + 1] = 0.f; dirs[3 * i + 2] = 0.f;
             reinterpret_cast<float2*>(deltas)[i] = make_float2(0.f, 0.f);
@@ -677,7 +687,7 @@ static int scan_counts(const uint32_t* counts, uint32_t N, int32_t* rays, int32_
 
 // record + scan: rays[n] = (n, offset, count), counter[0] += total, counter[1] += N; the recorded parameters stay in `scratch`
 // self_scan: leave the scan to k_march_expand<true> (the record kernel parks counter[0] in the first block-sum slot, unused at that size)
-static inline bool march_self_scan_ok(float dt_gamma, uint32_t N) { return dt_gamma == 0.0f && N <= 8 * kScanBlock; }
+static inline bool march_self_scan_ok(float dt_gamma, uint32_t N) { return dt_gamma == 0.0f && N <= 8192u; }   // every CTA re-reads all N counts: beyond that the scan kernels are cheaper
 
 static int march_count_impl(const float* rays_o, const float* rays_d, const uint8_t* grid, float bound, float dt_gamma,
                             uint32_t max_steps, uint32_t N, uint32_t C, uint32_t H, const float* nears, const float* fars,

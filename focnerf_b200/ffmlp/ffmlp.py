@@ -74,6 +74,11 @@ class _Backend:
         check(lib().foc_ffmlp_wgrad_finish(ptr(scratch), B, input_dim, hidden_dim, num_layers, ptr(grad_weights), stream()), "ffmlp_wgrad_finish")
 
     @staticmethod
+    def ffmlp_wgrad_accumulate(scratch, B, input_dim, hidden_dim, num_layers, grad_weights):
+        _chk_half(grad_weights, "grad_weights")
+        check(lib().foc_ffmlp_wgrad_accumulate(ptr(scratch), B, input_dim, hidden_dim, num_layers, ptr(grad_weights), stream()), "ffmlp_wgrad_accumulate")
+
+    @staticmethod
     def allocate_splitk(size):
         check(lib().foc_allocate_splitk(size), "allocate_splitk")
 
@@ -160,8 +165,11 @@ class _ffmlp_forward_side(Function):
         input_dim, output_dim, hidden_dim, num_layers, activation, output_activation, calc_grad_inputs = ctx.dims
         grad_inputs = torch.empty_like(inputs) if calc_grad_inputs else None
         if ctx.side is None:
-            _backend.ffmlp_backward(grad, inputs, shadow16, forward_buffer, B, input_dim, output_dim, hidden_dim, num_layers,
-                                    activation, output_activation, calc_grad_inputs, None, grad_inputs, ctx.grad16)
+            # grad16 ACCUMULATES like `.grad` (the optimiser sweep zeroes it after use): two field evaluations before one step add up
+            scratch = torch.empty(lib().foc_ffmlp_backward_scratch_bytes(B, input_dim, hidden_dim, num_layers), dtype=torch.uint8, device=grad.device)
+            _backend.ffmlp_backward_partial(grad, inputs, shadow16, forward_buffer, B, input_dim, output_dim, hidden_dim, num_layers,
+                                            activation, output_activation, calc_grad_inputs, grad_inputs, scratch)
+            _backend.ffmlp_wgrad_accumulate(scratch, B, input_dim, hidden_dim, num_layers, ctx.grad16)
         else:
             # nothing but the optimiser reads the weight gradient: its reduction runs on a side stream, beside the rest of the backward
             # pass (the reference ran its split-K weight-gradient GEMMs on side streams as well, ffmlp.cu:801-812)
@@ -169,7 +177,7 @@ class _ffmlp_forward_side(Function):
             _backend.ffmlp_backward_partial(grad, inputs, shadow16, forward_buffer, B, input_dim, output_dim, hidden_dim, num_layers,
                                             activation, output_activation, calc_grad_inputs, grad_inputs, scratch)
             with ctx.side.fork():
-                _backend.ffmlp_wgrad_finish(scratch, B, input_dim, hidden_dim, num_layers, ctx.grad16)
+                _backend.ffmlp_wgrad_accumulate(scratch, B, input_dim, hidden_dim, num_layers, ctx.grad16)
         return (grad_inputs if calc_grad_inputs else None), None, None, None, None, None, None, None, None, None, None, None, None
 
 
@@ -241,14 +249,24 @@ class FFMLP(nn.Module):
             shadow16 = torch.empty_like(self.weights, dtype=torch.half)
         shadow16.copy_(self.weights.detach())
         if grad16 is None:
-            grad16 = torch.zeros_like(shadow16)
+            grad16 = torch.empty_like(shadow16)
+        grad16.zero_()                                          # the backward accumulates into it
         self._shadow16, self._grad16 = shadow16, grad16
+        self._shadow_version = self.weights._version
         return grad16, shadow16
+
+    def _current_shadow(self):
+        """See GridEncoder._current_shadow: refresh after an out-of-band write of the fp32 Parameter (load_state_dict, ...)."""
+        if self.weights._version != self._shadow_version:
+            with torch.no_grad():
+                self._shadow16.copy_(self.weights.detach())
+            self._shadow_version = self.weights._version
+        return self._shadow16
 
     def call_fused(self, inputs, calc_grad_inputs):
         """The kernels on a batch that is already a multiple of 128 rows (no padding cat), through the side buffers when enabled."""
         if getattr(self, "_shadow16", None) is not None and torch.is_autocast_enabled():
-            return _ffmlp_forward_side.apply(inputs, self.weights, self._shadow16, self._grad16, self.input_dim, self.padded_output_dim,
+            return _ffmlp_forward_side.apply(inputs, self.weights, self._current_shadow(), self._grad16, self.input_dim, self.padded_output_dim,
                                              self.hidden_dim, self.num_layers, self.activation, self.output_activation, not self.training,
                                              calc_grad_inputs, getattr(self, "_wgrad_side", None))
         return ffmlp_forward(inputs, self.weights, self.input_dim, self.padded_output_dim, self.hidden_dim, self.num_layers, self.activation,
@@ -262,14 +280,15 @@ class FFMLP(nn.Module):
         torch.manual_seed(42)
         std = math.sqrt(3 / self.hidden_dim)
         self.weights.data.uniform_(-std, std)
+        if getattr(self, "_shadow16", None) is not None:
+            self._shadow16.copy_(self.weights.detach())
 
     def forward(self, inputs):
         B, C = inputs.shape
         pad = 128 - (B % 128)                                   # always pads, by a full 128 when B % 128 == 0 (ffmlp.py:157)
         if pad > 0:
             inputs = torch.cat([inputs, torch.zeros(pad, C, dtype=inputs.dtype, device=inputs.device)], dim=0)
-        outputs = ffmlp_forward(inputs, self.weights, self.input_dim, self.padded_output_dim, self.hidden_dim, self.num_layers,
-                                self.activation, self.output_activation, not self.training, inputs.requires_grad)
+        outputs = self.call_fused(inputs, inputs.requires_grad)       # through the fp16 side buffers when an optimiser enabled them
         if B != outputs.shape[0] or self.padded_output_dim != self.output_dim:
             outputs = outputs[:B, :self.output_dim]
         return outputs

@@ -170,6 +170,8 @@ class GridEncoder(nn.Module):
     def reset_parameters(self):
         std = 1e-4
         self.embeddings.data.uniform_(-std, std)
+        if self._shadow16 is not None:
+            self._shadow16.copy_(self.embeddings.detach())
 
     def enable_fp16_side_buffers(self, grad16=None, shadow16=None):
         """Not in the reference.  Allocates (grad16, shadow16), both [offset, C] half: under fp16 autocast the forward then
@@ -189,7 +191,18 @@ class GridEncoder(nn.Module):
             grad16 = torch.empty_like(shadow16)
         grad16.zero_()
         self._shadow16, self._grad16 = shadow16, grad16
+        self._shadow_version = self.embeddings._version
         return self._grad16, self._shadow16
+
+    def _current_shadow(self):
+        """The fp16 shadow, re-derived first when the fp32 Parameter was written behind the optimiser's back (load_state_dict,
+        reset_parameters, any in-place torch op: they bump `_version`; the optimiser's own kernel writes through raw pointers and
+        refreshes the shadow itself)."""
+        if self._shadow16 is not None and self.embeddings._version != self._shadow_version:
+            with torch.no_grad():
+                self._shadow16.copy_(self.embeddings.detach())
+            self._shadow_version = self.embeddings._version
+        return self._shadow16
 
     def __repr__(self):
         return (f"GridEncoder: input_dim={self.input_dim} num_levels={self.num_levels} level_dim={self.level_dim} "
@@ -207,7 +220,7 @@ class GridEncoder(nn.Module):
         prefix_shape = list(inputs.shape[:-1])
         inputs = inputs.view(-1, self.input_dim)
         outputs = grid_encode(inputs, self.embeddings, self.offsets, self.per_level_scale, self.base_resolution,
-                              inputs.requires_grad, self.gridtype_id, self.align_corners, self.interp_id, self._shadow16, self._grad16)
+                              inputs.requires_grad, self.gridtype_id, self.align_corners, self.interp_id, self._current_shadow(), self._grad16)
         return outputs.view(prefix_shape + [self.output_dim])
 
     @torch.amp.autocast("cuda", enabled=False)                     # always fp32 (grid.py:164)

@@ -47,6 +47,8 @@ class ScaledAdam:
         self.growth_tracker = torch.zeros(1, dtype=torch.int32, device=dev)
         self.found_inf = torch.zeros(1, dtype=torch.float32, device=dev)
         self.step_count = torch.zeros(1, dtype=torch.int32, device=dev)
+        self.lr0, self.decay_iters = float(lr), None           # set_exp_decay(): the reference's per-iteration LambdaLR, on the device
+        self.sched_iter = torch.zeros(1, dtype=torch.int32, device=dev)
         self._side = {}                # id(param) -> (grad16, shadow16)
 
     # ---- wiring ---------------------------------------------------------------------------------------------------
@@ -79,6 +81,24 @@ class ScaledAdam:
     def set_lr(self, lr):
         self.lr.fill_(float(lr))
 
+    def set_exp_decay(self, iters, lr0=None):
+        """main_nerf.py:477 `LambdaLR(optimizer, lambda iter: 0.1 ** min(iter / opt.iters, 1))` stepped after every iteration
+        (scheduler_update_every_step=True): from now on step() also advances lr on the device (csrc/optim.cu k_scaler_update)."""
+        if lr0 is not None:
+            self.lr0 = float(lr0)
+        self.decay_iters = None if iters is None else float(iters)
+        self.sched_iter.zero_()
+        self.lr.fill_(self.lr0)
+
+    def _scaler_update(self, l, sc, fip, st):
+        if self.decay_iters is None:
+            check(l.foc_scaler_update(sc, self.growth_tracker.data_ptr(), fip, self.step_count.data_ptr(), self.growth_factor, self.backoff_factor,
+                                      self.growth_interval, st), "scaler_update")
+        else:
+            check(l.foc_scaler_update_sched(sc, self.growth_tracker.data_ptr(), fip, self.step_count.data_ptr(), self.growth_factor,
+                                            self.backoff_factor, self.growth_interval, self.lr.data_ptr(), self.sched_iter.data_ptr(), self.lr0,
+                                            self.decay_iters, st), "scaler_update_sched")
+
     def zero_grad(self, set_to_none=True):
         if self.persistent_grads:
             return
@@ -95,6 +115,11 @@ class ScaledAdam:
         rows = []
         for p, m, v in zip(self.params, self.exp_avg, self.exp_avg_sq):
             g16, s16 = self._side.get(id(p), (None, None))
+            if g16 is not None and p.grad is not None:
+                # an operator that does not know about the side buffer delivered this gradient through autograd: applying only
+                # grad16 would silently drop it
+                raise RuntimeError("ScaledAdam: a parameter with an attached fp16 gradient buffer also has a .grad -- some forward "
+                                   "bypassed the side buffers (call the module under fp16 autocast, or detach the buffers)")
             g = g16 if g16 is not None else p.grad
             if g is None:
                 continue
@@ -123,14 +148,14 @@ class ScaledAdam:
         for a in arrays:
             check(l.foc_adam_step(ctypes.cast(a, ctypes.c_void_p), len(a), self.lr.data_ptr(), b1, b2, self.eps, sc, fi,
                                   self.step_count.data_ptr(), st), "adam_step")
-        check(l.foc_scaler_update(sc, self.growth_tracker.data_ptr(), fi, self.step_count.data_ptr(), self.growth_factor, self.backoff_factor,
-                                  self.growth_interval, st), "scaler_update")
+        self._scaler_update(l, sc, fi, st)
 
     # ---- checkpointing (nerf/utils.py:1434-1556 saves optimizer + scaler state) -------------------------------------
     def state_dict(self):
         return {"exp_avg": [t.clone() for t in self.exp_avg], "exp_avg_sq": [t.clone() for t in self.exp_avg_sq], "lr": float(self.lr.item()),
                 "step": int(self.step_count.item()), "scale": None if self.scale is None else float(self.scale.item()),
-                "growth_tracker": int(self.growth_tracker.item()), "betas": self.betas, "eps": self.eps}
+                "growth_tracker": int(self.growth_tracker.item()), "betas": self.betas, "eps": self.eps,
+                "lr0": self.lr0, "decay_iters": self.decay_iters, "sched_iter": int(self.sched_iter.item())}
 
     def load_state_dict(self, sd):
         for dst, src in zip(self.exp_avg, sd["exp_avg"]):
@@ -138,6 +163,8 @@ class ScaledAdam:
         for dst, src in zip(self.exp_avg_sq, sd["exp_avg_sq"]):
             dst.copy_(src)
         self.lr.fill_(sd["lr"]); self.step_count.fill_(sd["step"]); self.growth_tracker.fill_(sd["growth_tracker"])
+        self.lr0, self.decay_iters = sd.get("lr0", self.lr0), sd.get("decay_iters", self.decay_iters)
+        self.sched_iter.fill_(sd.get("sched_iter", 0))
         if self.scale is not None and sd.get("scale") is not None:
             self.scale.fill_(sd["scale"])
         self.refresh_shadows()
@@ -258,8 +285,7 @@ class PeerAdam(ScaledAdam):
             check(l.foc_adam_step(ctypes.cast(arr, ctypes.c_void_p), len(rows), self.lr.data_ptr(), b1, b2, self.eps, sc, fip,
                                   self.step_count.data_ptr(), st), "adam_step")
         self.arena.barrier()                                   # every shard of the fp16 table has arrived
-        check(l.foc_scaler_update(sc, self.growth_tracker.data_ptr(), fip, self.step_count.data_ptr(), self.growth_factor, self.backoff_factor,
-                                  self.growth_interval, st), "scaler_update")
+        self._scaler_update(l, sc, fip, st)
 
     @torch.no_grad()
     def sync_master(self):

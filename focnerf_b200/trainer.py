@@ -12,9 +12,13 @@ from .network import NeRFNetwork
 
 
 class Trainer:
+    """Defaults follow the reference's recipe: lr 1e-3 (main_nerf.py:26), Adam(betas=(0.9, 0.99), eps=1e-15) (main_nerf.py:472),
+    density_thresh 10, min_near 0.2, max_steps 1024, density-grid refresh every update_extra_interval = 16 steps (main_nerf.py:33),
+    `iters` = the horizon of the per-iteration LambdaLR 0.1 ** min(iter / iters, 1) (main_nerf.py:25,477; None = constant lr)."""
+
     def __init__(self, bound=1.0, density_grid=None, density_thresh=10.0, min_near=0.2, dt_gamma=0.0, max_steps=1024,
-                 lr=1e-2, fp16=True, device="cuda", grid_size=128, seed=0, fused=True, use_graph=False, optimizer="fused", pipeline=False,
-                 data_parallel=None, group=None):
+                 lr=1e-3, fp16=True, device="cuda", grid_size=128, seed=0, fused=True, use_graph=False, optimizer="fused", pipeline=False,
+                 data_parallel=None, group=None, iters=None, update_extra_interval=16):
         if not torch.cuda.is_available():
             raise RuntimeError("focnerf_b200.Trainer needs a CUDA device (there is no CPU path)")
         import math
@@ -36,6 +40,8 @@ class Trainer:
         self.step_counter = torch.zeros(16, 2, dtype=torch.int32, device=self.device)     # renderer.py:96-98
         self._fuse_rgb = os.environ.get("FOC_FUSE_RGB") == "1"
         self.mean_count, self.local_step = 0, 0
+        self.global_step, self.update_extra_interval, self.iters, self.lr = 0, int(update_extra_interval), iters, float(lr)
+        self.lr_scheduler = None
         self.grad_sync = None
         # fused: field-network wiring through field_glue.cu (same function, ~25 fewer launches per step)
         # use_graph: replay the whole optimisation step as ONE CUDA graph once the sample-buffer size has settled
@@ -84,9 +90,13 @@ class Trainer:
                     self.optimizer.attach(net.weights, grad16=g16, shadow16=s16)
                     net._wgrad_side = self._wgrad_side    # weight-gradient reductions beside the rest of the backward pass
             self.scaler = None
+            if iters is not None:
+                self.optimizer.set_exp_decay(iters, lr)
         else:
             self.optimizer = torch.optim.Adam(self.model.get_params(lr), betas=(0.9, 0.99), eps=1e-15, fused=True, capturable=use_graph)
             self.scaler = torch.amp.GradScaler("cuda", enabled=fp16)
+            if iters is not None:
+                self.lr_scheduler = torch.optim.lr_scheduler.LambdaLR(self.optimizer, lambda it: 0.1 ** min(it / iters, 1))
         if data_parallel == "nccl":
             from . import dist as fdist
             self.grad_sync = lambda: fdist.all_reduce_mean(self.grad_tensors(), group=group)
@@ -140,6 +150,7 @@ class Trainer:
         self.iter_density += 1
         self.model.train(was_training)
         self.update_mean_count()
+        self.local_step = 0                              # renderer.py:536
 
     # ------------------------------------------------------------------------------------------------ training
     def render_train(self, rays_o, rays_d, bg_color=1.0, perturb=True, force_all_rays=False, counter=None, mean_count=None):
@@ -227,6 +238,8 @@ class Trainer:
             self.grad_sync()
         self.scaler.step(self.optimizer)
         self.scaler.update()
+        if self.lr_scheduler is not None:
+            self.lr_scheduler.step()
         return loss
 
     def _pipelined_body(self, rays_o, rays_d, gt_rgb, bg_color, counter, mean_count):
@@ -309,6 +322,77 @@ class Trainer:
         stage[2].copy_(gt_rgb_h, non_blocking=True)
         loss = self.train_step(stage[0], stage[1], stage[2])
         return float(loss.item())
+
+    # ---- the reference's training loop body (nerf/utils.py:851-870, train_one_epoch) ---------------------------------------
+    def fit_step(self, rays_o, rays_d, gt_rgb, bg_color=1.0):
+        """One iteration of train_one_epoch: refresh the density grid when `global_step % update_extra_interval == 0`
+        (nerf/utils.py:853-856, under autocast), then the optimisation step; the learning-rate schedule advances inside it."""
+        if self.global_step % self.update_extra_interval == 0:
+            self.update_extra_state()
+        self.global_step += 1
+        return self.train_step(rays_o, rays_d, gt_rgb, bg_color)
+
+    def fit_step_host(self, rays_o_h, rays_d_h, gt_rgb_h, stage):
+        """fit_step from PINNED HOST buffers, returning the loss as a Python float (the reference's loop reads `loss.item()` every
+        step, nerf/utils.py:872)."""
+        if self.global_step % self.update_extra_interval == 0:
+            self.update_extra_state()
+        self.global_step += 1
+        return self.train_step_host(rays_o_h, rays_d_h, gt_rgb_h, stage)
+
+    # ---- checkpoint interchange with the reference (nerf/utils.py:1015-1136) ------------------------------------------------
+    _RENDERER_KEYS = ("aabb_train", "aabb_infer", "density_grid", "density_bitfield", "step_counter")
+
+    def state_dict(self):
+        """The `model` entry of a reference checkpoint: NeRFNetwork IS its renderer there (network_ff.py:10), so its state_dict
+        holds the renderer buffers (renderer.py:79-99) next to `encoder.embeddings`, `encoder.offsets`, `sigma_net.weights`,
+        `color_net.weights`."""
+        self.flush()
+        if hasattr(self.optimizer, "sync_master"):
+            self.optimizer.sync_master()                 # data-parallel: complete the sharded fp32 table first (a collective)
+        sd = {"aabb_train": self.aabb.detach().clone(), "aabb_infer": self.aabb.detach().clone(), "density_grid": self.density_grid.clone(),
+              "density_bitfield": self.density_bitfield.clone(), "step_counter": self.step_counter.clone()}
+        sd.update({k: v.detach().clone() for k, v in self.model.state_dict().items()})
+        return sd
+
+    def save_checkpoint(self, path, full=False):
+        """Trainer.save_checkpoint's file format (nerf/utils.py:1020-1053): epoch / global_step / stats / mean_count / mean_density /
+        model (+ optimizer when full)."""
+        state = {"epoch": 0, "global_step": self.global_step, "stats": {}, "mean_count": self.mean_count,
+                 "mean_density": float(self.mean_density.item()), "model": self.state_dict()}
+        if full and hasattr(self.optimizer, "state_dict"):
+            state["optimizer"] = self.optimizer.state_dict()
+        torch.save(state, path)
+
+    def load_checkpoint(self, checkpoint, model_only=True):
+        """Load a checkpoint written by the reference's Trainer.save_checkpoint (or by save_checkpoint above; or a bare model
+        state_dict, nerf/utils.py:1090-1093), as Trainer.load_checkpoint does (nerf/utils.py:1077-1110): parameters with
+        strict=False, the renderer buffers, mean_count / mean_density.  Returns (missing_keys, unexpected_keys)."""
+        self.flush()
+        if not isinstance(checkpoint, dict):
+            checkpoint = torch.load(checkpoint, map_location=self.device, weights_only=False)
+        sd = checkpoint["model"] if "model" in checkpoint else checkpoint
+        own = {k: v for k, v in sd.items() if k not in self._RENDERER_KEYS}
+        missing, unexpected = self.model.load_state_dict(own, strict=False)
+        with torch.no_grad():
+            if "density_grid" in sd:                      # dropped from `best` checkpoints (nerf/utils.py:1065-1066)
+                self.density_grid.copy_(sd["density_grid"].to(self.device).view_as(self.density_grid))
+            if "density_bitfield" in sd:
+                self.density_bitfield.copy_(sd["density_bitfield"].to(self.device))
+            if "step_counter" in sd:
+                self.step_counter.copy_(sd["step_counter"].to(self.device))
+            if "aabb_train" in sd:
+                self.aabb.copy_(sd["aabb_train"].to(self.device))
+            if "mean_density" in checkpoint:
+                self.mean_density.fill_(float(checkpoint["mean_density"]))
+        if "mean_count" in checkpoint:
+            self.mean_count = int(checkpoint["mean_count"])
+        if "global_step" in checkpoint and not model_only:
+            self.global_step = int(checkpoint["global_step"])
+        if hasattr(self.optimizer, "refresh_shadows"):
+            self.optimizer.refresh_shadows()             # fp16 copies the kernels read (the modules also notice the version bump)
+        self._graph = None                                # captured shapes may no longer fit mean_count
+        return list(missing), list(unexpected)
 
     def update_mean_count(self):
         """renderer.py:533-536: mean samples of the last 16 steps (one D2H sync, every 16 steps)."""

@@ -168,6 +168,9 @@ int foc_ffmlp_backward(const uint16_t *grad, const uint16_t *inputs, const uint1
  * order, fp16 result) -- the reference's split-K GEMMs ran on side streams too (ffmlp.cu:801-812, 892-894); here the caller owns the stream. */
 int foc_ffmlp_wgrad_finish(const void *scratch, uint32_t B, uint32_t input_dim, uint32_t hidden_dim, uint32_t num_layers,
                            uint16_t *grad_weights, void *stream);
+/* same reduction, ADDED to what grad_weights holds (`.grad` semantics for a persistent gradient buffer zeroed by the optimiser sweep) */
+int foc_ffmlp_wgrad_accumulate(const void *scratch, uint32_t B, uint32_t input_dim, uint32_t hidden_dim, uint32_t num_layers,
+                               uint16_t *grad_weights, void *stream);
 /* kept for API compatibility with ffmlp.h:12-13; no-ops (no side streams, no workspaces) */
 int foc_allocate_splitk(size_t size);
 int foc_free_splitk(void);
@@ -255,6 +258,13 @@ int foc_adam_step(const FocAdamTensor *tensors, int count, const float *lr, floa
  * steps scale *= growth.  Also *step += 1 on a clean step, and *found_inf = 0.  scale may be NULL (step counter only). */
 int foc_scaler_update(float *scale, int32_t *growth_tracker, float *found_inf, int32_t *step, float growth_factor,
                       float backoff_factor, int32_t growth_interval, void *stream);
+/* foc_scaler_update + the reference's per-iteration learning-rate schedule (main_nerf.py:477: LambdaLR(optimizer, lambda iter:
+ * 0.1 ** min(iter / opt.iters, 1)) with scheduler_update_every_step=True, nerf/utils.py:869-870), on the device so that a
+ * CUDA-graph-replayed step needs no host write of lr: *sched_iter += 1 (skipped steps count, as scheduler.step() does);
+ * *lr = lr0 * 0.1 ** min(*sched_iter / decay_iters, 1). */
+int foc_scaler_update_sched(float *scale, int32_t *growth_tracker, float *found_inf, int32_t *step, float growth_factor,
+                            float backoff_factor, int32_t growth_interval, float *lr, int32_t *sched_iter, float lr0,
+                            float decay_iters, void *stream);
 
 /* ---------------------------------------------------------------- data-parallel training over NVLink peer memory
  * No reference counterpart (the reference trains on one GPU; torch DDP would all-reduce every gradient over NCCL and

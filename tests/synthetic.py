@@ -1,7 +1,8 @@
-"""Synthetic table-top scene shared by the tests and bench.py: there is no dataset in the
+"""Synthetic table-top scene shared by the tests and BOTH arms of bench.py: there is no dataset in the
 reference tree, so rays, ground-truth pixels and the occupancy grid come from an analytic field.
 
-Plain torch, device-agnostic (runs on CPU for the GPU-less tests); nothing here is on the timed path.
+Plain torch, device-agnostic (runs on CPU for the GPU-less tests); nothing here is on the timed path, and it lives outside
+the product package so that the reference arm can use it without importing focnerf_b200.
 Ray generation follows the reference's `get_rays` (nerf/utils.py:56-157: pixel centres +0.5, pinhole,
 normalised directions rotated by the camera-to-world pose).
 """
@@ -9,6 +10,21 @@ import math
 
 import numpy as np
 import torch
+
+
+# host-side Morton helpers, used only to BUILD synthetic occupancy grids (the operator `raymarching.morton3D` is a CUDA kernel)
+def _spread3(v):
+    v = v.to(torch.int64)
+    v = (v * 0x00010001) & 0xFF0000FF
+    v = (v * 0x00000101) & 0x0F00F00F
+    v = (v * 0x00000011) & 0xC30C30C3
+    v = (v * 0x00000005) & 0x49249249
+    return v
+
+
+def morton3d_torch(coords):
+    """coords [n,3] ints in [0,1024) -> int64 Morton codes (x lowest bit), as raymarching.cu:56-71."""
+    return _spread3(coords[:, 0]) | (_spread3(coords[:, 1]) << 1) | (_spread3(coords[:, 2]) << 2)
 
 
 class Scene:
@@ -60,7 +76,6 @@ class Scene:
 
     # ---- occupancy grid (Morton order, layout of NeRFRenderer.density_grid: [cascade, 128^3]) ----
     def density_grid(self, cascade, H=128, device="cpu"):
-        from .morton import morton3d_torch
         ar = torch.arange(H, device=device)
         xx, yy, zz = torch.meshgrid(ar, ar, ar, indexing="ij")
         coords = torch.stack([xx.reshape(-1), yy.reshape(-1), zz.reshape(-1)], -1)

@@ -10,7 +10,7 @@ for p in (ROOT, os.path.join(ROOT, "tests")):
     sys.path.insert(0, p)
 import cases  # noqa: E402
 import bench  # noqa: E402
-from focnerf_b200 import synthetic  # noqa: E402
+import synthetic  # noqa: E402
 from focnerf_b200.trainer import Trainer  # noqa: E402
 
 dev = torch.device("cuda", 0)
