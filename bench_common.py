@@ -4,8 +4,8 @@ Imports neither focnerf_b200 nor the reference -- `bench.py --impl reference` mu
 THE PROTOCOL (configs[1]; the reference's own recipe, main_nerf.py + legacy/nerf/utils.py:831-870)
   * model: hash grid 16 levels x 2 features, 2^19 entries, base 16, finest 2048 x bound; FFMLP 32-64-64-16 / 32-64-64-64-16 (network_ff.py)
   * 4096 rays per step (main_nerf.py:28) drawn from a pool of POOL pre-generated batches of the synthetic scene (analytic GT)
-  * Adam(lr 1e-3, betas (0.9, 0.99), eps 1e-15) (main_nerf.py:26,472), LambdaLR 0.1 ** min(iter / 30000, 1) stepped every
-    iteration (main_nerf.py:25,477), fp16 autocast + GradScaler, MSE, white background, perturb=True
+  * Adam(lr 1e-3, betas (0.9, 0.99), eps 1e-15) (main_nerf.py:26,472), LambdaLR 0.1 ** min(iter / ITERS, 1) stepped every
+    iteration (main_nerf.py:25,477; ITERS = the run length PRETRAIN), fp16 autocast + GradScaler, MSE, white background, perturb=True
   * the density grid starts EMPTY and `update_extra_state` runs whenever global_step % 16 == 0 (nerf/utils.py:853-856): the
     bitfield the marcher reads is the learnt one, and the refresh is INSIDE every timed region
   * PRETRAIN steps of exactly that loop bring the model to its steady state before anything is timed; the same PRETRAIN steps
@@ -24,9 +24,12 @@ for _p in (ROOT, os.path.join(ROOT, "tests")):
 
 RAYS_PER_GPU = 4096
 POOL = 256                      # distinct pre-generated ray batches (1 M rays): held-out views are then interpolations, seed spread < 0.1 dB
-LR, ITERS, UPDATE_EXTRA_INTERVAL = 1e-3, 30000, 16
 PRETRAIN = 1024                 # steps of the protocol before the timed region = the fixed-iteration run of the quality gate
-QUALITY_SEEDS = (0, 1, 2)
+# `--iters` = the length of the run, as the reference's recipe is used (main_nerf.py:25,477: lr decays to 0.1 x lr at the last
+# iteration and stays there).  Measured on this scene (tools/diag_seeds.py, 5 seeds): seed-to-seed sd of the held-out PSNR is 0.05 dB
+# with the schedule ending at the run length against 0.2-0.3 dB with an effectively constant lr -- a 0.1 dB gate needs the former.
+LR, ITERS, UPDATE_EXTRA_INTERVAL = 1e-3, PRETRAIN, 16
+QUALITY_SEEDS = (0, 1, 2, 3, 4)
 EVAL_RAYS = 65536
 BOUND, MIN_NEAR, DT_GAMMA, MAX_STEPS, DENSITY_THRESH, T_THRESH = 1.0, 0.2, 0.0, 1024, 10.0, 1e-4
 SHARED_CKPT = os.environ.get("FOC_SHARED_CKPT", "/tmp/foc_b200_shared_ckpt.pth")

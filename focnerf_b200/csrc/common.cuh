@@ -46,6 +46,26 @@ inline cudaError_t launch(void (*kernel)(KArgs...), dim3 grid, dim3 block, size_
 
 __host__ __device__ inline uint32_t ceil_div(uint32_t a, uint32_t b) { return (a + b - 1) / b; }
 
+// cudaFuncSetAttribute(MaxDynamicSharedMemorySize) is PER DEVICE: remember it per (kernel instantiation, device), not per process --
+// one `DynSmemOptIn` object per kernel template instantiation (a function-local static in its launcher).  A racing second thread
+// sets the same value again, which is harmless.
+struct DynSmemOptIn {
+    static constexpr int kMaxDevices = 64;
+    bool done[kMaxDevices] = {};
+    template <typename K> int ensure(K kernel, int bytes) {
+        int dev = 0;
+        cudaError_t e = cudaGetDevice(&dev);
+        if (e != cudaSuccess) return (int)e;
+        if (dev < 0 || dev >= kMaxDevices) return FOC_ERR_UNSUPPORTED;
+        if (!done[dev]) {
+            e = cudaFuncSetAttribute(kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, bytes);
+            if (e != cudaSuccess) return (int)e;
+            done[dev] = true;
+        }
+        return 0;
+    }
+};
+
 // Explicitly-rounded float ops: the marcher's integer results (sample counts, cell indices) must not
 // depend on the compiler's FMA-contraction choices, so every operation states its rounding.
 __device__ __forceinline__ float fmul(float a, float b) { return __fmul_rn(a, b); }

@@ -362,12 +362,8 @@ int launch_bwd(const uint16_t* grad, const uint16_t* inputs, const uint16_t* wei
     if (rc) return rc;
     const uint32_t smem = SM::total((int)num_layers);
     if (smem > 227 * 1024) return FOC_ERR_UNSUPPORTED;
-    static bool attr_set = false;
-    if (!attr_set) {
-        cudaError_t e = cudaFuncSetAttribute(k_mlp_bwd<IN, ACT>, cudaFuncAttributeMaxDynamicSharedMemorySize, 227 * 1024);
-        if (e != cudaSuccess) return (int)e;
-        attr_set = true;
-    }
+    static DynSmemOptIn optin;                                         // per (instantiation, device)
+    if (int rc2 = optin.ensure(k_mlp_bwd<IN, ACT>, 227 * 1024)) return rc2;
     BwdParams p;
     p.grad = reinterpret_cast<const __half*>(grad);
     p.weights = reinterpret_cast<const __half*>(weights);

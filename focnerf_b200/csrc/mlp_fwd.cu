@@ -227,12 +227,8 @@ int launch_fwd(const uint16_t* inputs, const uint16_t* weights, uint32_t B, uint
     rc = make_tmap_f16_2d(&tm_w, weights + (size_t)kHidden * IN, (uint64_t)n_hmm * kHidden + kOutPad, kHidden, 16, kHidden);
     if (rc) return rc;
     const uint32_t smem = SM::total(n_hmm);
-    static bool attr_set = false;                                      // idempotent; racing threads set the same value
-    if (!attr_set) {
-        cudaError_t e = cudaFuncSetAttribute(k_mlp_fwd<IN, ACT>, cudaFuncAttributeMaxDynamicSharedMemorySize, 96 * 1024);
-        if (e != cudaSuccess) return (int)e;
-        attr_set = true;
-    }
+    static DynSmemOptIn optin;                                         // per (instantiation, device)
+    if (int rc2 = optin.ensure(k_mlp_fwd<IN, ACT>, 96 * 1024)) return rc2;
     if (smem > 96 * 1024) return FOC_ERR_UNSUPPORTED;
     FwdParams p;
     p.inputs = reinterpret_cast<const __half*>(inputs);

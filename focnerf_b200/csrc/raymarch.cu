@@ -135,15 +135,18 @@ __global__ void __launch_bounds__(256) k_sph_from_ray(const float* __restrict__ 
     if (n >= N) return;
     const float ox = rays_o[3 * (size_t)n], oy = rays_o[3 * (size_t)n + 1], oz = rays_o[3 * (size_t)n + 2];
     const float dx = rays_d[3 * (size_t)n], dy = rays_d[3 * (size_t)n + 1], dz = rays_d[3 * (size_t)n + 2];
-    const float A = dx * dx + dy * dy + dz * dz;
-    const float B = ox * dx + oy * dy + oz * dz;
-    const float Cc = ox * ox + oy * oy + oz * oz - radius * radius;
-    const float t = (-B + sqrtf(B * B - A * Cc)) / A;
-    const float x = ox + t * dx, y = oy + t * dy, z = oz + t * dz;
-    const float theta = atan2f(sqrtf(x * x + z * z), y), phi = atan2f(z, x);
+    // roundings stated as nvcc contracts the reference's expressions (raymarching.cu:184-197, -fmad=true; read off the SASS of
+    // oracle/_ref/raymarching): `a*b + c*d + e*f` -> fma(e, f, fma(a, b, c*d)), `s - r*r` -> fma(-r, r, s), `x*x + z*z` -> fma(x, x, z*z),
+    // `2 * theta * RPI - 1` -> fma(theta + theta, RPI, -1); oracle/orc_raymarch.c spells out the same sequence
+    const float A = __fmaf_rn(dz, dz, __fmaf_rn(dx, dx, __fmul_rn(dy, dy)));
+    const float B = __fmaf_rn(oz, dz, __fmaf_rn(ox, dx, __fmul_rn(oy, dy)));
+    const float Cc = __fmaf_rn(-radius, radius, __fmaf_rn(oz, oz, __fmaf_rn(ox, ox, __fmul_rn(oy, oy))));
+    const float t = __fdiv_rn(__fadd_rn(-B, sqrtf(__fmaf_rn(B, B, -__fmul_rn(A, Cc)))), A);
+    const float x = __fmaf_rn(t, dx, ox), y = __fmaf_rn(t, dy, oy), z = __fmaf_rn(t, dz, oz);
+    const float theta = atan2f(sqrtf(__fmaf_rn(x, x, __fmul_rn(z, z))), y), phi = atan2f(z, x);
     const float RPI = 0.3183098861837907f;
-    coords[2 * (size_t)n] = 2 * theta * RPI - 1;
-    coords[2 * (size_t)n + 1] = phi * RPI;
+    coords[2 * (size_t)n] = __fmaf_rn(__fmul_rn(2.0f, theta), RPI, -1.0f);
+    coords[2 * (size_t)n + 1] = __fmul_rn(phi, RPI);
 }
 
 // K3 / K4 (raymarching.cu:214-254)

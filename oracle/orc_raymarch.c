@@ -82,12 +82,13 @@ ORC_API void orc_sph_from_ray(const float *rays_o, const float *rays_d, float ra
     const float RPI = 0.3183098861837907f;
     for (uint32_t n = 0; n < N; ++n) {
         const float *o = rays_o + 3 * n, *d = rays_d + 3 * n;
-        float A = fmaf(d[2], d[2], fmaf(d[1], d[1], d[0] * d[0]));
-        float B = fmaf(o[2], d[2], fmaf(o[1], d[1], o[0] * d[0]));
-        float Cc = fmaf(o[2], o[2], fmaf(o[1], o[1], o[0] * o[0])) - radius * radius;
-        float t = (-B + sqrtf(B * B - A * Cc)) / A;
+        /* FMA placement as nvcc contracts the reference source (read off the SASS of the reference build, see csrc/raymarch.cu) */
+        float A = fmaf(d[2], d[2], fmaf(d[0], d[0], d[1] * d[1]));
+        float B = fmaf(o[2], d[2], fmaf(o[0], d[0], o[1] * d[1]));
+        float Cc = fmaf(-radius, radius, fmaf(o[2], o[2], fmaf(o[0], o[0], o[1] * o[1])));
+        float t = (-B + sqrtf(fmaf(B, B, -(A * Cc)))) / A;
         float x = fmaf(t, d[0], o[0]), y = fmaf(t, d[1], o[1]), z = fmaf(t, d[2], o[2]);
-        float theta = atan2f(sqrtf(fmaf(z, z, x * x)), y);
+        float theta = atan2f(sqrtf(fmaf(x, x, z * z)), y);
         float phi = atan2f(z, x);
         coords[2 * n] = fmaf(2.0f * theta, RPI, -1.0f);
         coords[2 * n + 1] = phi * RPI;

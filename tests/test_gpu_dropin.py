@@ -44,8 +44,12 @@ def _ref_model(NeRFNetwork, seed=0):
 
 
 def _rel(a, b):
+    """max |a - b| / max |b| over the finite entries; non-finite entries must coincide (rays that miss the box have near = far =
+    FLT_MAX, so the reference's own `(depth - near) / (far - near)` is NaN there, in both stacks)."""
     a, b = a.detach().float().cpu().numpy().astype(np.float64), b.detach().float().cpu().numpy().astype(np.float64)
-    return float(np.abs(a - b).max() / (np.abs(b).max() + 1e-20))
+    fa, fb = np.isfinite(a), np.isfinite(b)
+    assert np.array_equal(fa, fb), "non-finite entries differ"
+    return float(np.abs(a[fa] - b[fb]).max() / (np.abs(b[fb]).max() + 1e-20))
 
 
 def test_reference_modules_resolve_to_this_package():

@@ -99,3 +99,26 @@ def test_grad_total_variation_vs_oracle():
     x01 = ((runners.T(c["inputs"]) * 2 - 1 + 1) / 2).cpu().numpy()
     acc = oracle.grad_total_variation(x01, c["embeddings"], c["offsets"], c["per_level_scale"], c["H"], 1e-3)
     assert rel(enc.embeddings.grad.cpu().numpy(), acc) <= 1e-3
+
+
+def test_grad_total_variation_vs_reference():
+    """K14 (gridencoder.cu:506-645) against the reference extension's own grad_total_variation on the same cells: both ACCUMULATE
+    into the passed gradient with fp32 atomics, so the comparison is within the fp32 accumulation-order tolerance."""
+    ref = ref_ext.load("gridencoder")
+    if ref is None:
+        pytest.skip("oracle/_ref/gridencoder not built")
+    for res in (None, 2048):                                  # power-of-two and non-integer level scales
+        c = cases.grid_case(100000, 17, with_oob=False, desired_resolution=res)
+        x, emb, off = runners.T(c["inputs"]), runners.T(c["embeddings"]), runners.T(c["offsets"])
+        B, D, C, L = x.shape[0], 3, emb.shape[1], off.shape[0] - 1
+        S, H = float(np.log2(c["per_level_scale"])), c["H"]
+        seed = torch.from_numpy(np.random.RandomState(5).normal(0, 1e-6, c["embeddings"].shape).astype(np.float32)).cuda()
+        ga, gb = seed.clone(), seed.clone()
+        ours().grad_total_variation(x, emb, ga, off, 1e-3, B, D, C, L, S, H, 0, False)
+        ref.grad_total_variation(x, emb, gb, off, 1e-3, B, D, C, L, S, H, 0, False)
+        a, b = ga.cpu().numpy(), gb.cpu().numpy()
+        assert float(np.abs(b - seed.cpu().numpy()).max()) > 0                       # the reference did add something
+        assert rel(a, b) <= 1e-4, rel(a, b)
+        # per element: |a - b| <= 1e-3 * max(|b|, eps), eps = 1e-3 of the tensor's scale (entries that cancel to ~0 carry no relative meaning)
+        eps = 1e-3 * float(np.abs(b).max())
+        assert np.all(np.abs(a - b) <= 1e-3 * np.maximum(np.abs(b), eps))
