@@ -8,9 +8,19 @@
 //   k_grid_ema       : grid = max(grid * decay, tmp) where both are valid (>= 0); per-CTA sums of max(grid, 0)  (l.522-524)
 //   k_grid_mean      : fixed-order sum of the per-CTA partials -> mean                                    (l.524)
 //   k_packbits_dev   : bit = grid > min(mean, density_thresh), threshold read from device memory          (l.529-530)
+#include <cstdio>
+#include <mutex>
+
 #include "common.cuh"
+#include "../../include/foc_b200.h"
 
 using namespace foc;
+
+// Built-in scratch of foc_density_grid_update_noalloc (file scope): one partial sum per k_grid_ema CTA of 2048 cells, 8192 floats =
+// 32 KB on every GPU that loads the library.  In HOST code this name is only a stand-in for the symbol, not a device address: the
+// address comes from cudaGetSymbolAddress (noalloc_partials() below), once per device.
+constexpr uint32_t kNoallocPartials = FOC_NOALLOC_MAX_CELLS / 2048u;
+static __device__ __align__(256) float g_noalloc_partials[kNoallocPartials];
 
 namespace {
 
@@ -82,6 +92,29 @@ k_packbits_dev(const float* __restrict__ grid, uint32_t N, const float* __restri
                             (b.x > thresh) << 4 | (b.y > thresh) << 5 | (b.z > thresh) << 6 | (b.w > thresh) << 7);
 }
 
+static_assert(kNoallocPartials == FOC_NOALLOC_MAX_CELLS / (uint32_t)(kEmaThreads * kEmaPerThread), "one slot per k_grid_ema CTA");
+
+constexpr int kMaxDevices = 64;
+std::mutex g_noalloc_mu;
+float* g_noalloc_addr[kMaxDevices] = {};                              // per device, filled on the first call made on that device
+
+// device address of g_noalloc_partials on the CURRENT device (looked up once per device); nullptr + *rc on failure
+float* noalloc_partials(int* rc) {
+    int dev = -1;
+    cudaError_t e = cudaGetDevice(&dev);
+    if (e != cudaSuccess) { *rc = (int)e; return nullptr; }
+    if (dev < 0 || dev >= kMaxDevices) { *rc = FOC_ERR_UNSUPPORTED; return nullptr; }
+    std::lock_guard<std::mutex> lock(g_noalloc_mu);
+    if (g_noalloc_addr[dev] == nullptr) {
+        void* p = nullptr;
+        e = cudaGetSymbolAddress(&p, g_noalloc_partials);
+        if (e != cudaSuccess || p == nullptr) { *rc = e != cudaSuccess ? (int)e : (int)cudaErrorInvalidSymbol; return nullptr; }
+        g_noalloc_addr[dev] = static_cast<float*>(p);
+    }
+    *rc = 0;
+    return g_noalloc_addr[dev];
+}
+
 }  // namespace
 
 static inline cudaStream_t S(void* s) { return reinterpret_cast<cudaStream_t>(s); }
@@ -105,6 +138,30 @@ FOC_API int foc_density_grid_update(float* grid, const float* tmp, uint32_t n, f
     if (n % 8 != 0 || (reinterpret_cast<uintptr_t>(grid) & 15u)) return FOC_ERR_UNSUPPORTED;
     const uint32_t blocks = ceil_div(n, (uint32_t)(kEmaThreads * kEmaPerThread));
     float* partial = static_cast<float*>(scratch);
+    k_grid_ema<<<blocks, kEmaThreads, 0, S(stream)>>>(grid, tmp, n, decay, partial);
+    FOC_LAUNCH_CHECK();
+    k_grid_mean<<<1, 1024, 0, S(stream)>>>(partial, blocks, n, mean);
+    FOC_LAUNCH_CHECK();
+    k_packbits_dev<<<ceil_div(n / 8, 256), 256, 0, S(stream)>>>(grid, n / 8, mean, density_thresh, bitfield);
+    FOC_LAUNCH_CHECK(); return 0;
+}
+
+// foc_density_grid_update with the partial sums in the library's own static device array: allocates nothing (see include/foc_b200.h).
+// k_grid_ema writes partial[b] for every CTA b < blocks and k_grid_mean reads exactly those, so the array's stale contents from an
+// earlier (possibly larger) call are never read; overlapping calls on one device would race on it.
+FOC_API int foc_density_grid_update_noalloc(float* grid, const float* tmp, uint32_t n, float decay, float density_thresh, float* mean,
+                                            uint8_t* bitfield, void* stream) {
+    if (n == 0) return 0;
+    if (n > FOC_NOALLOC_MAX_CELLS) {
+        fprintf(stderr, "foc_density_grid_update_noalloc: n = %u cells exceeds the built-in scratch (FOC_NOALLOC_MAX_CELLS = %u); "
+                        "use foc_density_grid_update with a caller-owned scratch buffer\n", n, (unsigned)FOC_NOALLOC_MAX_CELLS);
+        return FOC_ERR_TOO_LARGE;
+    }
+    if (n % 8 != 0 || (reinterpret_cast<uintptr_t>(grid) & 15u)) return FOC_ERR_UNSUPPORTED;
+    int rc = 0;
+    float* partial = noalloc_partials(&rc);
+    if (partial == nullptr) return rc;
+    const uint32_t blocks = ceil_div(n, (uint32_t)(kEmaThreads * kEmaPerThread));
     k_grid_ema<<<blocks, kEmaThreads, 0, S(stream)>>>(grid, tmp, n, decay, partial);
     FOC_LAUNCH_CHECK();
     k_grid_mean<<<1, 1024, 0, S(stream)>>>(partial, blocks, n, mean);

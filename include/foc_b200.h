@@ -22,6 +22,7 @@ extern "C" {
 #endif
 
 #define FOC_ERR_UNSUPPORTED (-1)
+#define FOC_ERR_TOO_LARGE (-2)   /* a size beyond the stated maximum of an entry point with built-in (static) scratch */
 #define FOC_ABI_VERSION 1
 
 int foc_abi_version(void);
@@ -208,6 +209,21 @@ int foc_density_cell_positions(const int32_t *indices, uint32_t n, uint32_t H, f
 size_t foc_density_grid_update_scratch_bytes(uint32_t n);
 int foc_density_grid_update(float *grid, const float *tmp, uint32_t n, float decay, float density_thresh, float *mean,
                             uint8_t *bitfield, void *scratch, void *stream);
+/* foc_density_grid_update WITHOUT a caller-supplied scratch buffer and without any allocation.  No counterpart in the reference:
+ * added for callers that cannot call cudaMalloc (code under CUDA graph capture, tight
+ * serving loops, harnesses that forbid it).  The per-CTA partial sums of the mean live in a file-scope
+ * `static __device__ __align__(256)` array inside the library: FOC_NOALLOC_MAX_CELLS / 2048 floats = 32 KB, held by every GPU that
+ * loads the library until the process exits.  Same kernels, same fixed summation order, hence the same bits as
+ * foc_density_grid_update.  Limits and rules:
+ *   - n <= FOC_NOALLOC_MAX_CELLS (8 cascades of 128^3 cells); a larger n returns FOC_ERR_TOO_LARGE and launches nothing;
+ *   - calls no cudaMalloc / cudaFree / allocating library routine; the array's device address is looked up once per device
+ *     (cudaGetSymbolAddress, with that device current) on the first call made on that device -- make that first call outside a
+ *     graph capture;
+ *   - every call on a device shares the one array and it keeps the previous call's contents; each call overwrites every slot it
+ *     later reads, so nothing needs clearing, but two calls that OVERLAP on the GPU (different streams) race: serialise them. */
+#define FOC_NOALLOC_MAX_CELLS (8u * 128u * 128u * 128u)
+int foc_density_grid_update_noalloc(float *grid, const float *tmp, uint32_t n, float decay, float density_thresh, float *mean,
+                                    uint8_t *bitfield, void *stream);
 
 /* ---------------------------------------------------------------- loss head fused into the training compositor
  * (no reference kernel: legacy/nerf/renderer.py:313-316 + nerf/utils.py:535-545 as ~14 elementwise / reduction launches)
