@@ -316,16 +316,36 @@ def run_ours(args):
         del big_pool
         loop(tr, 16, False, 0)                       # back to the 4096-ray batches (mean_count settles again)
 
-    # per-entry-point device times: the SAME step run eagerly (a graph replay cannot carry per-kernel events), with CUDA
-    # events around every C-ABI call on the launching stream.  Not part of `value`; feeds roofline + gpu_launches.
-    tr.use_graph = False
+    # per-entry-point device times.  With the CUDA graph: the step is re-captured with two EXTERNAL event-record nodes around every
+    # C-ABI call (_lib.GraphKernelTimer), so the times are those of the kernels as they run inside the replayed step that `value` times
+    # (an eager pass lets host launch gaps leak into the intervals: measured 61 us for a 13 us kernel).  Launch counts come from a short
+    # eager pass (a replay makes no Python calls to count).  Neither pass is part of `value`.
     n_prof = min(args.steps, 32)
-    loop(tr, 3, False, 400)
-    with _lib.KernelTimer(TIMED) as kt:
+    tr.use_graph = False
+    loop(tr, 2, False, 400)
+    with _lib.KernelTimer(TIMED if not use_graph else ()) as kc:
         sync_all()
-        loop(tr, n_prof, False, 500)
+        loop(tr, n_prof if not use_graph else 4, False, 500)
         sync_all()
+    launches_per_step = kc.kernel_launches() / (n_prof if not use_graph else 4)
     tr.use_graph = use_graph
+    if use_graph:
+        tr._graph = None                               # re-capture with the timer's wrappers in place
+        with _lib.GraphKernelTimer(TIMED) as kt:
+            for i in range(n_prof + 4):
+                b_ = pool_dev[(600 + i) % C.POOL]
+                kt.begin_step()
+                tr.fit_step(*b_)
+                torch.cuda.synchronize()
+                kt.collect()
+            tr._graph = None                           # the captured graph refers to the timer's events: drop it before they go
+        timing_mode = "external event-record nodes inside the graph-replayed step"
+    else:
+        kt = kc
+        kt.calls_per_step = lambda k: len(kt.events.get(k, ())) / n_prof
+        kt.timed_names = lambda: [k for k in TIMED if kt.events.get(k)]
+        timing_mode = "CUDA events around each call of an eager step"
+    loop(tr, 2, False, 700)                            # clean re-capture for the legs below
     samples_prof = float(tr.step_counter[:min(16, max(1, tr.local_step)), 0].float().mean().item()) if tr.local_step > 0 else samples
 
     # ---- render / multi-object legs -------------------------------------------------------------------------------------------------
@@ -416,10 +436,8 @@ def run_ours(args):
     traffic = ncu_traffic()
     # every timed entry point against its roofline: mean device time per call inside the eager pass, algorithmic work of one call
     per, rows = {}, {}
-    for k in TIMED:
-        if not kt.events.get(k):
-            continue
-        calls = len(kt.events[k]) / n_prof
+    for k in kt.timed_names():
+        calls = kt.calls_per_step(k)
         t_call = kt.mean_ms(k) * 1e-3
         per[k] = kt.mean_ms(k) * calls
         if k in ALG_BYTES:
@@ -441,7 +459,7 @@ def run_ours(args):
     else:
         roof = {"kernel": top, "bound": "hbm", "achieved": r_["hbm_GBs"], "peak": hbm, "unit": "GB/s", "frac": r_["hbm_frac"]}
     roof.update({"traffic": traffic.get(top), "traffic_source": "profiles/r2_traffic.json (ncu --set full, DRAM bytes per call)" if traffic.get(top) else None,
-                 "peak_source": how, "ms_per_launch": r_["ms_per_call"], "samples_per_step": samples_prof,
+                 "peak_source": how, "ms_per_launch": r_["ms_per_call"], "samples_per_step": samples_prof, "timing": timing_mode,
                  "ms_per_step_by_entry_point": {k: round(v, 4) for k, v in sorted(per.items(), key=lambda kv: -kv[1])}, "by_entry_point": rows})
     out = {
         "metric": "train rays/s", "value": total_rays / (ms * 1e-3), "unit": "rays/s", "n_gpus": world, "steps": args.steps,
@@ -455,7 +473,7 @@ def run_ours(args):
         "clocks": clk,
         "e2e": {"value": total_rays / (ms_e2e * 1e-3), "unit": "rays/s", "ms_per_step": ms_e2e / args.steps,
                 "h2d_bytes_per_step": world * C.RAYS_PER_GPU * 9 * 4, "d2h_bytes_per_step": world * 4},
-        "gpu_launches": int(round(kt.kernel_launches() / n_prof * args.steps)),
+        "gpu_launches": int(round(launches_per_step * args.steps)),
         "render_own_model": render_own if render is not render_own else None,
         "multi_object": multi, "multi_object_edit8": multi8, "density_refresh": refresh, "quality": quality, "frozen_bitfield": frozen,
         "roofline": roof,

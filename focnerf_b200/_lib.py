@@ -151,3 +151,78 @@ class KernelTimer:
         skip = ("foc_abi_version", "foc_allocate_splitk", "foc_free_splitk")
         total = sum(n * self.LAUNCHES.get(k, 1) for k, n in self.calls.items() if not k.endswith("_bytes") and k not in skip and not k.startswith("_"))
         return total - self.calls.get("_ffmlp_backward_no_finish", 0)
+
+
+class GraphKernelTimer(KernelTimer):
+    """KernelTimer for a CUDA-graph-replayed step: while a stream is being CAPTURED, every timed `foc_*` call is bracketed by two
+    external event-record nodes (foc_timer_mark), so each replay of the graph stamps them and `collect()` (after a synchronize)
+    reads the device time of every call as it ran inside the replayed step.  Calls made outside a capture are counted but not timed.
+
+        with GraphKernelTimer(names) as kt:
+            for batch in batches:
+                kt.begin_step(); trainer.train_step(*batch); torch.cuda.synchronize(); kt.collect()
+        kt.mean_ms(name), kt.calls_per_step(name)
+    """
+    SLOTS = 8192
+
+    def __enter__(self):
+        l = lib()
+        h = ctypes.c_void_p()
+        check(l.foc_timer_create(self.SLOTS, ctypes.byref(h)), "timer_create")
+        self._h, self._next, self.pairs, self._mark = h, 0, [], 0
+        self.sums, self.counts, self.steps = {}, {}, 0
+        for name in _protos:
+            fn = getattr(l, name)
+            self._orig[name] = fn
+            self.calls[name] = 0
+            if name.startswith("foc_timer_"):
+                continue
+            timed = name in self.names
+
+            def wrapper(*a, _fn=fn, _name=name, _timed=timed):
+                self.calls[_name] += 1
+                if _name == "foc_ffmlp_backward" and a[14] is None:
+                    self.calls["_ffmlp_backward_no_finish"] = self.calls.get("_ffmlp_backward_no_finish", 0) + 1
+                if not _timed or not torch.cuda.is_current_stream_capturing() or self._next + 2 > self.SLOTS:
+                    return _fn(*a)
+                st, k = stream(), self._next
+                self._next += 2
+                self._orig["foc_timer_mark"](self._h, k, st)
+                r = _fn(*a)
+                self._orig["foc_timer_mark"](self._h, k + 1, st)
+                self.pairs.append((_name, k))
+                return r
+            setattr(l, name, wrapper)
+        return self
+
+    def __exit__(self, *exc):
+        r = super().__exit__(*exc)
+        lib().foc_timer_destroy(self._h)
+        return r
+
+    def begin_step(self):
+        self._mark = len(self.pairs)
+
+    def collect(self):
+        """After the step and a synchronize.  A step that (re-)captured the graph invalidates the pairs of the previous graph."""
+        if len(self.pairs) > self._mark and self._mark > 0:
+            self.pairs = self.pairs[self._mark:]
+            self.sums, self.counts, self.steps = {}, {}, 0
+        if not self.pairs:
+            return
+        ms = ctypes.c_float()
+        for name, k in self.pairs:
+            if self._orig["foc_timer_elapsed"](self._h, k, k + 1, ctypes.byref(ms)) != 0:
+                return                                   # not stamped yet (capture without a replay)
+            self.sums[name] = self.sums.get(name, 0.0) + ms.value
+            self.counts[name] = self.counts.get(name, 0) + 1
+        self.steps += 1
+
+    def mean_ms(self, name):
+        return self.sums.get(name, 0.0) / max(1, self.counts.get(name, 0))
+
+    def calls_per_step(self, name):
+        return self.counts.get(name, 0) / max(1, self.steps)
+
+    def timed_names(self):
+        return [n for n in self.names if self.counts.get(n)]

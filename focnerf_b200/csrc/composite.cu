@@ -233,8 +233,15 @@ k_composite_mse_bwd(const float* __restrict__ grad_loss, const float* __restrict
     };
     const bool kept = (uint64_t)off + cnt <= M;
     if (ordered) {
-        if (!kept && off < M) zero_rows(off, M);                       // the FIRST dropped ray (off <= M < off + cnt) owns the rest
-        if (kept && n == N - 1) zero_rows((uint64_t)off + cnt, M);     // nothing dropped: the last ray owns the padding rows
+        if (!kept && off < M) zero_rows(off, M);                       // the FIRST dropped ray (off <= M < off + cnt) owns the rest (< max_steps rows)
+        // nothing dropped: the padding rows [total, M) -- up to a whole buffer quantum (16 k rows) when the step is replayed as a graph --
+        // are dealt to ALL warps in 32-row pieces (one warp clearing them alone was the kernel's tail)
+        const uint64_t total = (uint64_t)(uint32_t)__ldg(rays + 3 * (size_t)(N - 1) + 1) + (uint32_t)__ldg(rays + 3 * (size_t)(N - 1) + 2);
+        for (uint64_t i = total + (uint64_t)n * 32u + lane; i < M; i += (uint64_t)N * 32u) {
+            grad_sigmas[i] = 0.f;
+            if constexpr (HC) { grad_hc[2 * i] = make_uint4(0u, 0u, 0u, 0u); grad_hc[2 * i + 1] = make_uint4(0u, 0u, 0u, 0u); }
+            else { grad_rgbs[3 * i] = 0.f; grad_rgbs[3 * i + 1] = 0.f; grad_rgbs[3 * i + 2] = 0.f; }
+        }
     }
     if (cnt == 0 || !kept) return;
     const float rf = __ldg(image + 3 * (size_t)id), gf = __ldg(image + 3 * (size_t)id + 1), bf = __ldg(image + 3 * (size_t)id + 2);

@@ -47,6 +47,7 @@ class Trainer:
         # use_graph: replay the whole optimisation step as ONE CUDA graph once the sample-buffer size has settled
         self.fused, self.use_graph = fused, use_graph
         self._graph = None
+        self._refresh_graph, self._refresh_buf = None, None
         # pipeline=True (fused optimiser + graph only, opt-in): the optimiser sweep of step i-1 runs on a side stream next to
         # the march of step i (the march reads rays + bitfield, never the parameters).  `_pending` = a backward has left
         # gradients that no sweep has consumed yet; flush() applies them.  Measured on B200: 0.441 ms vs 0.443 ms per step --
@@ -108,45 +109,91 @@ class Trainer:
         thresh = min(float(g.clamp(min=0).mean()), density_thresh)
         raymarching.packbits(g, thresh, self.density_bitfield)
 
+    def _density_at(self, xyzs):
+        """sigma [m] f32 at xyzs [m,3]: `self.density(x)['sigma'] * density_scale` (renderer.py:480-481), through the fused operators when
+        m is a multiple of 128 (no zero-row padding cat)."""
+        with torch.autocast("cuda", dtype=torch.float16, enabled=self.fp16):
+            m_ = self.model
+            if self.fp16 and self.fused and xyzs.shape[0] % 128 == 0 and m_.in_dim == 32 and m_.sigma_net.hidden_dim == 64:
+                h = m_.sigma_net.call_fused(m_.encoder(xyzs, bound=m_.bound), False)
+                sig = torch.exp(h[:, 0].float())                       # trunc_exp forward (activation.py:9-11)
+            else:
+                sig = m_.density(xyzs)["sigma"].reshape(-1).float()
+        return sig * self.density_scale
+
+    def _refresh_partial_body(self, decay):
+        """The steady-state update (renderer.py:487-516) with STATIC shapes, so that it can be captured: per cascade H^3/4 uniformly
+        random cells + H^3/4 cells drawn uniformly from the occupied ones.  The reference draws the latter as
+        `nonzero(grid > 0)[randint(0, n_occ, [m])]` (a host sync for the shape); here the k-th occupied cell, k = floor(u * n_occ) with
+        u ~ U[0,1), is found by a binary search in the running count of occupied cells: the same distribution, no host read."""
+        from ._lib import check, lib, ptr, stream
+        H, n, dev = self.grid_size, self.grid_size ** 3, self.device
+        m = n // 4
+        tmp = self._refresh_buf["tmp"]
+        tmp.fill_(-1.0)
+        for cas in range(self.cascade):
+            bound_c = float(min(2 ** cas, self.bound))
+            coords = torch.randint(0, H, (m, 3), device=dev)
+            idx_rand = raymarching.morton3D(coords)
+            running = torch.cumsum((self.density_grid[cas] > 0).to(torch.int32), 0, dtype=torch.int32)
+            n_occ = running[-1:]                                                  # device scalar
+            k = torch.minimum((torch.rand(m, device=dev) * n_occ.float()).to(torch.int32), (n_occ - 1).clamp(min=0))
+            occ = torch.searchsorted(running, k + 1, out_int32=True).clamp_(max=n - 1)
+            indices = torch.cat([idx_rand, occ], 0).contiguous()
+            noise = torch.rand(2 * m, 3, device=dev)
+            xyzs = self._refresh_buf["xyzs"]
+            check(lib().foc_density_cell_positions(ptr(indices), 2 * m, H, bound_c, ptr(noise), ptr(xyzs), stream()), "density_cell_positions")
+            # a cell drawn twice keeps the LARGER of its two samples: the reference's `tmp_grid[cas, indices] = sigmas` keeps an arbitrary
+            # one (renderer.py:516); the maximum is one of them and makes the result deterministic, so data-parallel replicas that
+            # share the seed hold bit-identical grids and bitfields without a broadcast
+            tmp[cas].scatter_reduce_(0, indices.long(), self._density_at(xyzs), "amax", include_self=True)
+        total = self.cascade * n
+        check(lib().foc_density_grid_update(ptr(self.density_grid), ptr(tmp), total, decay, self.density_thresh, ptr(self.mean_density),
+                                            ptr(self.density_bitfield), ptr(self._refresh_buf["scratch"]), stream()), "density_grid_update")
+
     @torch.no_grad()
     def update_extra_state(self, decay=0.95):
         """NeRFRenderer.update_extra_state (legacy/nerf/renderer.py:445-536): re-sample the field's density at jittered cell
         positions (every cell for the first 16 calls, then H^3/4 random + H^3/4 occupied cells per cascade), EMA-max into
         the density grid, threshold at min(mean, density_thresh) into the bitfield the marcher reads.  Cells are generated in
-        Morton order on the device (no meshgrid loops) and the mean / threshold never visit the host (csrc/density_grid.cu);
-        the one host read left is torch.nonzero of the partial update, as in the reference (l.495)."""
+        Morton order on the device (no meshgrid loops) and the mean / threshold never visit the host (csrc/density_grid.cu).
+        The steady-state partial update has static shapes and, with use_graph, is replayed as ONE CUDA graph; the only host read
+        left is the reference's own `mean_count` (renderer.py:533-535)."""
         from ._lib import check, lib, ptr, stream
         self.flush()
         H, n, dev = self.grid_size, self.grid_size ** 3, self.device
-        tmp = torch.full_like(self.density_grid, -1.0)
         was_training = self.model.training
         self.model.eval()
-        for cas in range(self.cascade):
-            bound_c = float(min(2 ** cas, self.bound))
-            if self.iter_density < 16:
-                indices, m = None, n
+        if self.iter_density >= 16:
+            if self._refresh_buf is None:
+                total = self.cascade * n
+                self._refresh_buf = {"tmp": torch.empty_like(self.density_grid), "xyzs": torch.empty(n // 2, 3, dtype=torch.float32, device=dev),
+                                     "scratch": torch.empty(max(4, lib().foc_density_grid_update_scratch_bytes(total)), dtype=torch.uint8, device=dev)}
+            if self.use_graph and self.fp16 and self.fused:
+                if self._refresh_graph is None or self._refresh_graph[0] != decay:
+                    self._refresh_partial_body(decay)              # warm-up outside the capture (allocator, lazy module loads)
+                    torch.cuda.synchronize()
+                    g = torch.cuda.CUDAGraph()
+                    if self._capture_stream is None:
+                        self._capture_stream = torch.cuda.Stream(priority=-1)
+                    with torch.cuda.graph(g, stream=self._capture_stream):
+                        self._refresh_partial_body(decay)
+                    self._refresh_graph = (decay, g)
+                self._refresh_graph[1].replay()
             else:
-                m = n // 4
-                coords = torch.randint(0, H, (m, 3), device=dev)
-                idx_rand = raymarching.morton3D(coords).long()
-                occ = torch.nonzero(self.density_grid[cas] > 0).squeeze(-1)
-                if occ.numel() > 0:
-                    occ = occ[torch.randint(0, occ.shape[0], [m], dtype=torch.long, device=dev)]
-                    idx_rand = torch.cat([idx_rand, occ], 0)
-                indices, m = idx_rand.int().contiguous(), idx_rand.shape[0]
-            noise = torch.rand(m, 3, device=dev)
-            xyzs = torch.empty(m, 3, dtype=torch.float32, device=dev)
-            check(lib().foc_density_cell_positions(ptr(indices), m, H, bound_c, ptr(noise), ptr(xyzs), stream()), "density_cell_positions")
-            with torch.autocast("cuda", dtype=torch.float16, enabled=self.fp16):
-                sig = self.model.density(xyzs)["sigma"].reshape(-1).float() * self.density_scale
-            if indices is None:
-                tmp[cas] = sig
-            else:
-                tmp[cas, indices.long()] = sig
-        total = self.cascade * n
-        scratch = torch.empty(max(4, lib().foc_density_grid_update_scratch_bytes(total)), dtype=torch.uint8, device=dev)
-        check(lib().foc_density_grid_update(ptr(self.density_grid), ptr(tmp), total, decay, self.density_thresh, ptr(self.mean_density),
-                                            ptr(self.density_bitfield), ptr(scratch), stream()), "density_grid_update")
+                self._refresh_partial_body(decay)
+        else:
+            tmp = torch.full_like(self.density_grid, -1.0)
+            for cas in range(self.cascade):
+                bound_c = float(min(2 ** cas, self.bound))
+                noise = torch.rand(n, 3, device=dev)
+                xyzs = torch.empty(n, 3, dtype=torch.float32, device=dev)
+                check(lib().foc_density_cell_positions(None, n, H, bound_c, ptr(noise), ptr(xyzs), stream()), "density_cell_positions")
+                tmp[cas] = self._density_at(xyzs)
+            total = self.cascade * n
+            scratch = torch.empty(max(4, lib().foc_density_grid_update_scratch_bytes(total)), dtype=torch.uint8, device=dev)
+            check(lib().foc_density_grid_update(ptr(self.density_grid), ptr(tmp), total, decay, self.density_thresh, ptr(self.mean_density),
+                                                ptr(self.density_bitfield), ptr(scratch), stream()), "density_grid_update")
         self.iter_density += 1
         self.model.train(was_training)
         self.update_mean_count()

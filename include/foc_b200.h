@@ -27,6 +27,15 @@ extern "C" {
 
 int foc_abi_version(void);
 
+/* Measurement aid, no reference counterpart: n CUDA events; foc_timer_mark stamps slot `slot` on `stream` -- as an EXTERNAL
+ * event-record node when the stream is being captured, so that every replay of the captured graph stamps it again;
+ * foc_timer_elapsed = milliseconds between two stamped slots (after a synchronize).  bench.py brackets every library call of the
+ * graph-replayed train step with these to report per-entry-point device times. */
+int foc_timer_create(int n, void **handle);
+int foc_timer_mark(void *handle, int slot, void *stream);
+int foc_timer_elapsed(void *handle, int a, int b, float *ms);
+int foc_timer_destroy(void *handle);
+
 /* ---------------------------------------------------------------- raymarching (raymarching/src/raymarching.h:7-18) */
 
 /* replaces near_far_from_aabb, raymarching.h:7 (kernel raymarching.cu:92-145). rays_* [N,3], aabb [6], nears/fars [N] */
