@@ -39,8 +39,11 @@ ALG_BYTES_PER_PARAM = {"foc_adam_step": 30, "foc_adam_nonfinite": 2}
 N_PARAMS = 6119864 * 2 + 7168 + 11264
 # MLP entry points: FLOPs per sample and call (sigma net 32-64-64-16, colour net 32-64-64-64-16), forward; backward = 2x
 MLP_FLOPS_FWD = 36864
-MLP_BYTES = {"foc_ffmlp_forward": (352 + 480) / 2, "foc_ffmlp_backward": (416 + 544) / 2}      # per sample and call, mean of the two nets
-TIMED = list(ALG_BYTES) + list(ALG_BYTES_PER_PARAM) + ["foc_ffmlp_forward", "foc_ffmlp_backward"]
+# per sample and call: foc_ffmlp_* mean of the two nets; foc_field_forward (training) = enc 64 + dirs 12 + stored activations 5 x 128 + cin 64
+# + sigma 4 + rgb 12; foc_ffmlp_backward_head = mean of colour (24 + 64 + 384 + 64) and sigma (8 + 32 + 64 + 256 + 64)
+MLP_BYTES = {"foc_ffmlp_forward": (352 + 480) / 2, "foc_ffmlp_backward": (416 + 544) / 2, "foc_field_forward": 796, "foc_ffmlp_backward_head": (536 + 424) / 2}
+MLP_FLOPS = {"foc_ffmlp_forward": 36864, "foc_ffmlp_backward": 2 * 36864, "foc_field_forward": 36864, "foc_ffmlp_backward_head": 2 * 36864}   # per sample, all calls of a step
+TIMED = list(ALG_BYTES) + list(ALG_BYTES_PER_PARAM) + list(MLP_BYTES)
 
 
 def peaks():
@@ -448,7 +451,7 @@ def run_ours(args):
             nbytes = MLP_BYTES[k] * samples_prof
         row = {"ms_per_call": kt.mean_ms(k), "calls_per_step": calls, "hbm_GBs": nbytes / t_call / 1e9, "hbm_frac": nbytes / t_call / 1e9 / hbm}
         if k in MLP_BYTES:
-            flops = (MLP_FLOPS_FWD if k == "foc_ffmlp_forward" else 2 * MLP_FLOPS_FWD) * samples_prof / calls
+            flops = MLP_FLOPS[k] * samples_prof / calls
             row.update({"tensor_TFLOPs": flops / t_call / 1e12, "tensor_frac_of_burst": flops / t_call / 1e12 / tc_burst})
         rows[k] = {kk: round(vv, 4) for kk, vv in row.items()}
     top = max(per, key=per.get)

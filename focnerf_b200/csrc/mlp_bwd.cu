@@ -44,6 +44,16 @@ __device__ __forceinline__ float act_bwd(uint32_t a, float g, float fwd) {
 }
 
 struct BwdParams {
+    // head: how this thread's row of the [B,16] output gradient is obtained (fetch_grad_row / finish_grad_row):
+    //   0  read from `grad` [B,16] f16                                                    (the reference operator, ffmlp.h:9)
+    //   1  colour net: formed from grad_rgb [B,3] f32 and rgb [B,3] f32                   (field_glue.cu: k_rgb_bwd)
+    //   2  sigma net : formed from grad_sigma [B] f32 (or NULL), sigma [B] f32 and the colour net's grad_inputs [B,32] f16
+    //                                                                                     (field_glue.cu: k_field_mid_bwd)
+    int head;
+    const float* head_grad;      // grad_rgb / grad_sigma
+    const float* head_fwd;       // rgb / sigma
+    const __half* head_gcin;     // [B,32] (head 2)
+    float fifteen;               // 15.0f at run time: expf(+-15) must be the DEVICE's expf, as in k_field_mid_bwd, not a folded constant
     const __half* grad;          // [B, 16]
     const __half* weights;       // flat
     __half* backward_buffer;     // [num_layers, B, 64] or nullptr
@@ -51,6 +61,44 @@ struct BwdParams {
     float* partials;             // [gridDim.x, num_params] fp32
     uint32_t B, num_layers, activation, num_tiles, num_params, tmem_cols;
 };
+
+__device__ __forceinline__ uint32_t bw_pack2(float a, float b) { const __half2 h = __floats2half2_rn(a, b); return *reinterpret_cast<const uint32_t*>(&h); }
+__device__ __forceinline__ uint32_t bw_pack2h(__half a, __half b) { const __half2 h = __halves2half2(a, b); return *reinterpret_cast<const uint32_t*>(&h); }
+
+// This thread's row of the output gradient G [B,16] f16, in two steps so that the global loads of the NEXT tile's row can be in flight
+// during the current tile: fetch_grad_row only issues loads into registers, finish_grad_row does the arithmetic one tile later.
+struct RawGrad { uint4 a, b; float f[6]; };
+
+__device__ __forceinline__ void fetch_grad_row(const BwdParams& p, size_t grow, RawGrad& r) {
+    if (p.head == 0) {
+        const uint4* g = reinterpret_cast<const uint4*>(p.grad + grow * kOutPad);
+        r.a = __ldg(g); r.b = __ldg(g + 1);
+    } else if (p.head == 1) {
+        #pragma unroll
+        for (int c = 0; c < 3; ++c) { r.f[c] = __ldg(p.head_fwd + 3 * grow + c); r.f[3 + c] = __ldg(p.head_grad + 3 * grow + c); }
+    } else {
+        r.a = __ldg(reinterpret_cast<const uint4*>(p.head_gcin + grow * 32) + 2);
+        r.b = __ldg(reinterpret_cast<const uint4*>(p.head_gcin + grow * 32) + 3);
+        r.f[0] = p.head_grad ? __ldg(p.head_grad + grow) : 0.0f;
+        r.f[1] = __ldg(p.head_fwd + grow);
+    }
+}
+__device__ __forceinline__ void finish_grad_row(const BwdParams& p, const RawGrad& r, uint4& g0, uint4& g1) {
+    if (p.head == 0) { g0 = r.a; g1 = r.b; }
+    else if (p.head == 1) {                       // k_rgb_bwd: the gradient of a half tensor is half; d sigmoid = y (1 - y); columns 3..15 zero
+        float g[3];
+        #pragma unroll
+        for (int c = 0; c < 3; ++c) g[c] = __half2float(__float2half_rn(r.f[3 + c])) * (1.0f - r.f[c]) * r.f[c];
+        g0 = make_uint4(bw_pack2(g[0], g[1]), bw_pack2(g[2], 0.f), 0u, 0u);
+        g1 = make_uint4(0u, 0u, 0u, 0u);
+    } else {                                      // k_field_mid_bwd, with exp(clamp(h0, -15, 15)) == clamp(exp(h0), exp(-15), exp(15)): expf is monotonic
+        const __half* a = reinterpret_cast<const __half*>(&r.a);                               // and sigma = expf(h0) is the forward's own output
+        const __half* c = reinterpret_cast<const __half*>(&r.b);
+        const float gs = p.head_grad ? r.f[0] * fminf(expf(p.fifteen), fmaxf(expf(-p.fifteen), r.f[1])) : 0.0f;
+        g0 = make_uint4(bw_pack2h(__float2half_rn(gs), a[0]), bw_pack2h(a[1], a[2]), bw_pack2h(a[3], a[4]), bw_pack2h(a[5], a[6]));
+        g1 = make_uint4(bw_pack2h(a[7], c[0]), bw_pack2h(c[1], c[2]), bw_pack2h(c[3], c[4]), bw_pack2h(c[5], c[6]));
+    }
+}
 
 template <int IN>
 struct BwdSmem {
@@ -122,23 +170,22 @@ k_mlp_bwd(const __grid_constant__ CUtensorMap tm_fb, const __grid_constant__ CUt
     const uint32_t row = (uint32_t)(warp * 32 + lane);
     const uint32_t t_lane = tmem + ((uint32_t)(warp * 32) << 16);
     uint32_t ld_phase = 0, mma_phase = 0, acc_w = 0;      // acc_w: 0 on the CTA's first tile (overwrite), 1 afterwards
-    uint4 gn0 = make_uint4(0, 0, 0, 0), gn1 = gn0;        // this thread's row of the NEXT tile's output gradient, prefetched
-    if (blockIdx.x < p.num_tiles) {
-        const uint4* g = reinterpret_cast<const uint4*>(p.grad + ((size_t)blockIdx.x * kTile + row) * kOutPad);
-        gn0 = __ldg(g); gn1 = __ldg(g + 1);
-    }
+    RawGrad raw;                                          // this thread's row of the NEXT tile's output gradient: loads in flight, prefetched
+    raw.a = raw.b = make_uint4(0, 0, 0, 0);
+    #pragma unroll
+    for (int c = 0; c < 6; ++c) raw.f[c] = 0.f;
+    if (blockIdx.x < p.num_tiles) fetch_grad_row(p, (size_t)blockIdx.x * kTile + row, raw);
 
     for (uint32_t tile = blockIdx.x; tile < p.num_tiles; tile += gridDim.x) {
         const size_t grow = (size_t)tile * kTile + row;
         const uint32_t next_tile = tile + gridDim.x;
         const bool has_next = next_tile < p.num_tiles;
         {   // G tile: this thread's row, 16 halfs = 2 chunks, into the 128-byte-pitch swizzled layout
+            uint4 gn0, gn1;
+            finish_grad_row(p, raw, gn0, gn1);
             *reinterpret_cast<uint4*>(smem + SM::off_gz(L) + sw128_off(row, 0)) = gn0;
             *reinterpret_cast<uint4*>(smem + SM::off_gz(L) + sw128_off(row, 1)) = gn1;
-            if (has_next) {
-                const uint4* g = reinterpret_cast<const uint4*>(p.grad + ((size_t)next_tile * kTile + row) * kOutPad);
-                gn0 = __ldg(g); gn1 = __ldg(g + 1);
-            }
+            if (has_next) fetch_grad_row(p, (size_t)next_tile * kTile + row, raw);
         }
         fence_proxy_async_smem();
         tc_fence_before();
@@ -346,10 +393,12 @@ uint32_t bwd_grid(uint32_t B) {
 }
 uint32_t num_params_of(uint32_t input_dim, uint32_t num_layers) { return kHidden * (input_dim + kHidden * (num_layers - 1) + kOutPad); }
 
+struct BwdHead { int head; const float* grad; const float* fwd; const uint16_t* gcin; int accumulate; };
+
 template <int IN, int ACT>
 int launch_bwd(const uint16_t* grad, const uint16_t* inputs, const uint16_t* weights, const uint16_t* forward_buffer, uint32_t B,
                uint32_t num_layers, uint32_t activation, int calc_grad_inputs, uint16_t* backward_buffer, uint16_t* grad_inputs,
-               uint16_t* grad_weights, void* scratch, cudaStream_t st) {
+               uint16_t* grad_weights, void* scratch, cudaStream_t st, BwdHead hd = BwdHead{0, nullptr, nullptr, nullptr, 0}) {
     using SM = BwdSmem<IN>;
     CUtensorMap tm_fb, tm_in, tm_win, tm_w;
     int rc = make_tmap_f16_2d(&tm_fb, forward_buffer, (uint64_t)num_layers * B, kHidden, kTile, kHidden);
@@ -365,6 +414,7 @@ int launch_bwd(const uint16_t* grad, const uint16_t* inputs, const uint16_t* wei
     static DynSmemOptIn optin;                                         // per (instantiation, device)
     if (int rc2 = optin.ensure(k_mlp_bwd<IN, ACT>, 227 * 1024)) return rc2;
     BwdParams p;
+    p.head = hd.head; p.head_grad = hd.grad; p.head_fwd = hd.fwd; p.head_gcin = reinterpret_cast<const __half*>(hd.gcin); p.fifteen = 15.0f;
     p.grad = reinterpret_cast<const __half*>(grad);
     p.weights = reinterpret_cast<const __half*>(weights);
     p.backward_buffer = reinterpret_cast<__half*>(backward_buffer);
@@ -379,7 +429,8 @@ int launch_bwd(const uint16_t* grad, const uint16_t* inputs, const uint16_t* wei
     foc::launch(k_mlp_bwd<IN, ACT>, grid, 128, smem, st, tm_fb, tm_in, tm_win, tm_w, p);
     FOC_LAUNCH_CHECK();
     if (grad_weights == nullptr) return 0;                         // the caller reduces the partials itself (foc_ffmlp_wgrad_finish)
-    foc::launch(k_mlp_wgrad_finish, ceil_div(p.num_params, 32), 256, 0, st, p.partials, grid, p.num_params, reinterpret_cast<__half*>(grad_weights), 0);
+    foc::launch(k_mlp_wgrad_finish, ceil_div(p.num_params, 32), 256, 0, st, p.partials, grid, p.num_params, reinterpret_cast<__half*>(grad_weights),
+                hd.accumulate);
     FOC_LAUNCH_CHECK(); return 0;
 }
 
@@ -430,4 +481,22 @@ FOC_API int foc_ffmlp_backward(const uint16_t* grad, const uint16_t* inputs, con
     if (input_dim == 64) return activation == 0 ? FOC_BWD(64, 0) : activation == 6 ? FOC_BWD(64, 6) : FOC_BWD(64, -1);
 #undef FOC_BWD
     return FOC_ERR_UNSUPPORTED;
+}
+
+// foc_ffmlp_backward for the two nets of the FOC field, taking what the compositor / the colour net's backward produce instead of a
+// materialised [B,16] fp16 output gradient (no reference counterpart: network_ff.py's sigmoid / trunc_exp / slice backward kernels):
+//   head 1 (colour net): head_grad = grad_rgb [B,3] f32, head_fwd = rgb [B,3] f32                -> G = half(grad_rgb) * y (1 - y), cols 3..15 zero
+//   head 2 (sigma net) : head_grad = grad_sigma [B] f32 or NULL, head_fwd = sigma [B] f32, grad_cin [B,32] f16 (the colour net's grad_inputs)
+//                                                                                               -> G = [grad_sigma * clamp(sigma, e^-15, e^15), grad_cin[16:31]]
+// Same values as foc_rgb_sigmoid_backward / foc_field_mid_backward followed by foc_ffmlp_backward.  accumulate != 0: the reduced weight
+// gradient is ADDED to grad_weights (a persistent buffer zeroed by the optimiser sweep), else it overwrites it.  ReLU nets, hidden 64.
+FOC_API int foc_ffmlp_backward_head(int head, const float* head_grad, const float* head_fwd, const uint16_t* grad_cin, const uint16_t* inputs,
+                                    const uint16_t* weights, const uint16_t* forward_buffer, uint32_t B, uint32_t input_dim, uint32_t hidden_dim,
+                                    uint32_t num_layers, int calc_grad_inputs, uint16_t* grad_inputs, uint16_t* grad_weights, int accumulate,
+                                    void* scratch, void* stream) {
+    if (B == 0) return 0;
+    if (hidden_dim != (uint32_t)kHidden || input_dim != 32 || num_layers < 1 || num_layers > (uint32_t)kMaxLayers || B % kTile != 0 || !scratch ||
+        (head != 1 && head != 2) || head_fwd == nullptr || (head == 1 && head_grad == nullptr) || (head == 2 && grad_cin == nullptr)) return FOC_ERR_UNSUPPORTED;
+    return launch_bwd<32, 0>(nullptr, inputs, weights, forward_buffer, B, num_layers, 0u, calc_grad_inputs, nullptr, grad_inputs, grad_weights, scratch,
+                             reinterpret_cast<cudaStream_t>(stream), BwdHead{head, head_grad, head_fwd, grad_cin, accumulate});
 }

@@ -15,6 +15,8 @@ class NeRFNetwork(nn.Module):
                  num_layers_color=3, hidden_dim_color=64, bound=1, **kwargs):
         super().__init__()
         self.bound = bound
+        import os
+        self._field_fused = os.environ.get("FOC_FIELD_FUSED", "1") == "1"       # A/B switch for forward_fused's one-kernel field evaluation
         self.num_layers, self.hidden_dim, self.geo_feat_dim = num_layers, hidden_dim, geo_feat_dim
         self.encoder, self.in_dim = get_encoder(encoding, desired_resolution=2048 * bound)
         self.sigma_net = FFMLP(input_dim=self.in_dim, output_dim=1 + self.geo_feat_dim, hidden_dim=self.hidden_dim,
@@ -50,6 +52,12 @@ class NeRFNetwork(nn.Module):
             return self.forward(x, d)
         sn, cn = self.sigma_net, self.color_net
         enc = self.encoder(x, bound=self.bound)
+        if (not raw_colour and self._field_fused and torch.is_autocast_enabled() and getattr(sn, "_shadow16", None) is not None
+                and getattr(cn, "_shadow16", None) is not None and sn.activation == 0 and cn.activation == 0 and cn.hidden_dim == 64
+                and sn.num_layers <= 4 and cn.num_layers <= 4):
+            # the whole field behind the encoder as one tcgen05 kernel (csrc/field_fwd.cu), bit-identical to the four launches below
+            from .field_glue import field_eval
+            return field_eval(enc, d, sn, cn, self.training and torch.is_grad_enabled())
         h = sn.call_fused(enc, enc.requires_grad)
         sigma, cin = field_mid(h, d)
         hc = cn.call_fused(cin, cin.requires_grad)

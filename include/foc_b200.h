@@ -181,6 +181,21 @@ int foc_ffmlp_wgrad_finish(const void *scratch, uint32_t B, uint32_t input_dim, 
 /* same reduction, ADDED to what grad_weights holds (`.grad` semantics for a persistent gradient buffer zeroed by the optimiser sweep) */
 int foc_ffmlp_wgrad_accumulate(const void *scratch, uint32_t B, uint32_t input_dim, uint32_t hidden_dim, uint32_t num_layers,
                                uint16_t *grad_weights, void *stream);
+/* The FOC field behind the hash grid in one kernel (nerf/network_ff.py:51-74: sigma_net -> trunc_exp / SH-4 / cat -> color_net ->
+ * sigmoid; two ffmlp_forward calls (ffmlp.h:7) + ~10 elementwise torch kernels in the reference).  enc [B,32] f16, dirs [B,3] f32,
+ * fp16 weight blobs in the ffmlp.cu:632 layout, hidden width 64, B % 128 == 0 -> sigma [B] f32, rgb [B,3] f32.  Training: pass
+ * forward_buffer_sigma [Ls,B,64], forward_buffer_color [Lc,B,64] and cin [B,32] (all f16), which foc_ffmlp_backward_head consumes;
+ * NULL for all three = inference.  Bit-identical to foc_ffmlp_forward x 2 + foc_field_mid_forward + foc_rgb_sigmoid_forward. */
+int foc_field_forward(const uint16_t *enc, const float *dirs, const uint16_t *weights_sigma, const uint16_t *weights_color, uint32_t B,
+                      uint32_t num_layers_sigma, uint32_t num_layers_color, uint16_t *forward_buffer_sigma,
+                      uint16_t *forward_buffer_color, uint16_t *cin, float *sigma, float *rgb, void *stream);
+/* foc_ffmlp_backward for the two nets of the FOC field with the output gradient formed in the kernel's prologue (see csrc/mlp_bwd.cu):
+ * head 1 = colour net from grad_rgb / rgb [B,3] f32; head 2 = sigma net from grad_sigma (or NULL) / sigma [B] f32 and the colour net's
+ * grad_inputs grad_cin [B,32] f16.  scratch: foc_ffmlp_backward_scratch_bytes.  accumulate != 0 adds to grad_weights. */
+int foc_ffmlp_backward_head(int head, const float *head_grad, const float *head_fwd, const uint16_t *grad_cin, const uint16_t *inputs,
+                            const uint16_t *weights, const uint16_t *forward_buffer, uint32_t B, uint32_t input_dim, uint32_t hidden_dim,
+                            uint32_t num_layers, int calc_grad_inputs, uint16_t *grad_inputs, uint16_t *grad_weights, int accumulate,
+                            void *scratch, void *stream);
 /* kept for API compatibility with ffmlp.h:12-13; no-ops (no side streams, no workspaces) */
 int foc_allocate_splitk(size_t size);
 int foc_free_splitk(void);
