@@ -33,9 +33,14 @@ ALG_BYTES = {
     "foc_composite_mse_forward": 24,
     "foc_composite_mse_backward": 24 + 16,
     "foc_march_rays_train": 32,
+    # the same kernels reading their row count from device memory (graph-replayed step)
+    "foc_march_rays_train_rows": 32, "foc_grid_encode_forward_rows": 12 + 512 + 64, "foc_grid_encode_backward_rows": 12 + 64 + 512,
+    "foc_composite_mse_backward_rows": 24 + 16,
     "foc_field_mid_forward": 108, "foc_field_mid_backward": 96, "foc_rgb_sigmoid_forward": 44, "foc_rgb_sigmoid_backward": 44,
 }
 ALG_BYTES_PER_PARAM = {"foc_adam_step": 30, "foc_adam_nonfinite": 2}
+# data-parallel exchange (csrc/peer.cu): timed, no single-GPU roofline (NVLink pulls / pushes of 1/N of the table + barrier latency)
+PEER_TIMED = ["foc_dp_reduce", "foc_adam_step_peers", "foc_peer_barrier"]
 N_PARAMS = 6119864 * 2 + 7168 + 11264
 # MLP entry points: FLOPs per sample and call (sigma net 32-64-64-16, colour net 32-64-64-64-16), forward; backward = 2x
 MLP_FLOPS_FWD = 36864
@@ -43,7 +48,7 @@ MLP_FLOPS_FWD = 36864
 # + sigma 4 + rgb 12; foc_ffmlp_backward_head = mean of colour (24 + 64 + 384 + 64) and sigma (8 + 32 + 64 + 256 + 64)
 MLP_BYTES = {"foc_ffmlp_forward": (352 + 480) / 2, "foc_ffmlp_backward": (416 + 544) / 2, "foc_field_forward": 796, "foc_ffmlp_backward_head": (536 + 424) / 2}
 MLP_FLOPS = {"foc_ffmlp_forward": 36864, "foc_ffmlp_backward": 2 * 36864, "foc_field_forward": 36864, "foc_ffmlp_backward_head": 2 * 36864}   # per sample, all calls of a step
-TIMED = list(ALG_BYTES) + list(ALG_BYTES_PER_PARAM) + list(MLP_BYTES)
+TIMED = list(ALG_BYTES) + list(ALG_BYTES_PER_PARAM) + list(MLP_BYTES) + PEER_TIMED
 
 
 def peaks():
@@ -198,10 +203,13 @@ def run_ours(args):
 
     world, rank, local = int(os.environ.get("WORLD_SIZE", 1)), int(os.environ.get("RANK", 0)), int(os.environ.get("LOCAL_RANK", 0))
     torch.cuda.set_device(local)
+    out_fd = None
     if world > 1:
-        # stdout carries ONE JSON line: NCCL's banner / INFO lines (NCCL_DEBUG set by the launcher) go to stderr, where the driver reads them
-        if os.environ.get("NCCL_DEBUG") and not os.environ.get("NCCL_DEBUG_FILE"):
-            os.environ["NCCL_DEBUG_FILE"] = "/dev/stderr"
+        # stdout carries ONE JSON line, but NCCL writes its banner / INFO lines (NCCL_DEBUG set by a launcher) to fd 1 from C: point fd 1 at
+        # stderr for the whole run -- NCCL's log stays visible there, e.g. for counting ranks -- and keep the real stdout for the JSON line
+        sys.stdout.flush()
+        out_fd = os.dup(1)
+        os.dup2(2, 1)
         dist.init_process_group("nccl")
     dev = torch.device("cuda", local)
     scene, cascade, grid, bits, thresh = C.scene_and_grid()
@@ -255,10 +263,12 @@ def run_ours(args):
     if prof:
         torch.cuda.profiler.start()
     e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    captures0 = tr.capture_count
     e0.record()
     loop(tr, args.steps, False, C.PRETRAIN + warm)
     tr.flush()
     e1.record()
+    captures_timed = tr.capture_count - captures0
     sync_all()
     if prof:
         torch.cuda.profiler.stop()
@@ -443,6 +453,9 @@ def run_ours(args):
         calls = kt.calls_per_step(k)
         t_call = kt.mean_ms(k) * 1e-3
         per[k] = kt.mean_ms(k) * calls
+        if k in PEER_TIMED:
+            rows[k] = {"ms_per_call": round(kt.mean_ms(k), 4), "calls_per_step": round(calls, 4)}
+            continue
         if k in ALG_BYTES:
             nbytes = ALG_BYTES[k] * samples_prof
         elif k in ALG_BYTES_PER_PARAM:
@@ -454,7 +467,7 @@ def run_ours(args):
             flops = MLP_FLOPS[k] * samples_prof / calls
             row.update({"tensor_TFLOPs": flops / t_call / 1e12, "tensor_frac_of_burst": flops / t_call / 1e12 / tc_burst})
         rows[k] = {kk: round(vv, 4) for kk, vv in row.items()}
-    top = max(per, key=per.get)
+    top = max((k for k in per if k not in PEER_TIMED), key=per.get)
     r_ = rows[top]
     if top in MLP_BYTES:
         roof = {"kernel": top, "bound": "tensor", "achieved": r_["tensor_TFLOPs"], "peak": tc_burst, "unit": "TFLOP/s", "frac": r_["tensor_frac_of_burst"],
@@ -471,7 +484,7 @@ def run_ours(args):
         "render": render, "train_262k": big, "dp_parity": dp_parity,
         "config": {"workload": C.WORKLOAD, "rays_per_gpu": C.RAYS_PER_GPU, "samples_per_step": samples, "pretrain_steps": C.PRETRAIN,
                    "pretrain_s": pretrain_s, "pool_batches": C.POOL, "pool_build_s": t_pool, "parallelism": f"dp{world}" if world > 1 else "single",
-                   "cuda_graph": use_graph, "fused_glue": not args.no_fused, "optimizer": "torch" if args.torch_optim else "fused ScaledAdam",
+                   "cuda_graph": use_graph, "graph_captures_in_timed_region": captures_timed, "fused_glue": not args.no_fused, "optimizer": "torch" if args.torch_optim else "fused ScaledAdam",
                    "l2": "fresh ray batch every step; step working set (fp32 table + Adam moments + fp16 copy + grads ~ 260 MB) exceeds the 126 MB L2"},
         "clocks": clk,
         "e2e": {"value": total_rays / (ms_e2e * 1e-3), "unit": "rays/s", "ms_per_step": ms_e2e / args.steps,
@@ -488,7 +501,11 @@ def run_ours(args):
         from oracle import torch_renderer
         ro, rd = cases.camera_rays(C.RAYS_PER_GPU, 5)
         out["cpu_torch_renderer"] = torch_renderer.time_cpu(ro, rd, num_steps=128, runs=5, warmup=2)
-    print(json.dumps(out))
+    if out_fd is None:
+        print(json.dumps(out))
+    else:
+        sys.stdout.flush()
+        os.write(out_fd, (json.dumps(out) + "\n").encode())
     shutdown()
 
 

@@ -92,6 +92,22 @@ def check(err, what):
     raise RuntimeError(f"{what}: CUDA error {err}")
 
 
+# ---- device-side row count of a graph-replayed train step (include/foc_b200.h "device-side row counts").  The Trainer sets it around the
+# step it captures; the march wrapper publishes into it and the grid / field / compositor wrappers pass it on.  None = every row counts.
+_valid_rows = None
+
+
+def set_valid_rows(t):
+    """t: int32 [1] CUDA tensor (or None).  Returns the previous value."""
+    global _valid_rows
+    prev, _valid_rows = _valid_rows, t
+    return prev
+
+
+def valid_rows():
+    return _valid_rows
+
+
 def require_cuda(*tensors):
     for t in tensors:
         if t is not None and not t.is_cuda:

@@ -215,7 +215,8 @@ __global__ void __launch_bounds__(32 * kCompWarpsPerCta)
 k_composite_mse_bwd(const float* __restrict__ grad_loss, const float* __restrict__ gt, float bg,
                     const float* __restrict__ sigmas, const void* __restrict__ rgbs, const float* __restrict__ deltas,
                     const int32_t* __restrict__ rays, const float* __restrict__ weights_sum, const float* __restrict__ image,
-                    uint32_t M, uint32_t N, float T_thresh, int ordered, float* __restrict__ grad_sigmas, void* __restrict__ grad_colours) {
+                    uint32_t M, uint32_t N, float T_thresh, int ordered, float* __restrict__ grad_sigmas, void* __restrict__ grad_colours,
+                    const int32_t* __restrict__ n_rows) {
     float* grad_rgbs = static_cast<float*>(grad_colours);            // HC = false: [M,3] f32
     uint4* grad_hc = static_cast<uint4*>(grad_colours);              // HC = true : [M,16] f16 = two 16-byte words per row
     pdl_sync();
@@ -237,7 +238,10 @@ k_composite_mse_bwd(const float* __restrict__ grad_loss, const float* __restrict
         // nothing dropped: the padding rows [total, M) -- up to a whole buffer quantum (16 k rows) when the step is replayed as a graph --
         // are dealt to ALL warps in 32-row pieces (one warp clearing them alone was the kernel's tail)
         const uint64_t total = (uint64_t)(uint32_t)__ldg(rays + 3 * (size_t)(N - 1) + 1) + (uint32_t)__ldg(rays + 3 * (size_t)(N - 1) + 2);
-        for (uint64_t i = total + (uint64_t)n * 32u + lane; i < M; i += (uint64_t)N * 32u) {
+        // n_rows (optional, device memory): the consumers of the gradients only read the first *n_rows rows -- no need to clear beyond
+        uint64_t hi = M;
+        if (n_rows != nullptr) { const uint64_t v = (uint64_t)max(__ldg(n_rows), 0); hi = v < hi ? v : hi; }
+        for (uint64_t i = total + (uint64_t)n * 32u + lane; i < hi; i += (uint64_t)N * 32u) {
             grad_sigmas[i] = 0.f;
             if constexpr (HC) { grad_hc[2 * i] = make_uint4(0u, 0u, 0u, 0u); grad_hc[2 * i + 1] = make_uint4(0u, 0u, 0u, 0u); }
             else { grad_rgbs[3 * i] = 0.f; grad_rgbs[3 * i + 1] = 0.f; grad_rgbs[3 * i + 2] = 0.f; }
@@ -322,7 +326,19 @@ FOC_API int foc_composite_mse_backward(const float* grad_loss, const float* gt, 
                                        uint32_t N, float T_thresh, int ordered, float* grad_sigmas, float* grad_rgbs, void* stream) {
     if (N == 0) return 0;
     foc::launch(k_composite_mse_bwd<false>, ceil_div(N, kCompWarpsPerCta), 32 * kCompWarpsPerCta, 0, S(stream),
-        grad_loss, gt, bg, sigmas, (const void*)rgbs, deltas, rays, weights_sum, image, M, N, T_thresh, ordered, grad_sigmas, (void*)grad_rgbs);
+        grad_loss, gt, bg, sigmas, (const void*)rgbs, deltas, rays, weights_sum, image, M, N, T_thresh, ordered, grad_sigmas, (void*)grad_rgbs,
+        (const int32_t*)nullptr);
+    FOC_LAUNCH_CHECK(); return 0;
+}
+
+// foc_composite_mse_backward(ordered = 1) that clears the padding rows only up to *n_rows (device memory): see foc_march_rays_train_rows
+FOC_API int foc_composite_mse_backward_rows(const float* grad_loss, const float* gt, float bg, const float* sigmas, const float* rgbs,
+                                            const float* deltas, const int32_t* rays, const float* weights_sum, const float* image, uint32_t M,
+                                            uint32_t N, float T_thresh, float* grad_sigmas, float* grad_rgbs, const int32_t* n_rows, void* stream) {
+    if (N == 0) return 0;
+    if (n_rows == nullptr) return FOC_ERR_UNSUPPORTED;
+    foc::launch(k_composite_mse_bwd<false>, ceil_div(N, kCompWarpsPerCta), 32 * kCompWarpsPerCta, 0, S(stream),
+        grad_loss, gt, bg, sigmas, (const void*)rgbs, deltas, rays, weights_sum, image, M, N, T_thresh, 1, grad_sigmas, (void*)grad_rgbs, n_rows);
     FOC_LAUNCH_CHECK(); return 0;
 }
 
@@ -343,6 +359,6 @@ FOC_API int foc_composite_mse_hc_backward(const float* grad_loss, const float* g
     if (N == 0) return 0;
     if ((reinterpret_cast<uintptr_t>(hc) & 7u) || (reinterpret_cast<uintptr_t>(grad_hc) & 15u)) return FOC_ERR_UNSUPPORTED;
     foc::launch(k_composite_mse_bwd<true>, ceil_div(N, kCompWarpsPerCta), 32 * kCompWarpsPerCta, 0, S(stream),
-        grad_loss, gt, bg, sigmas, (const void*)hc, deltas, rays, weights_sum, image, M, N, T_thresh, 1, grad_sigmas, (void*)grad_hc);
+        grad_loss, gt, bg, sigmas, (const void*)hc, deltas, rays, weights_sum, image, M, N, T_thresh, 1, grad_sigmas, (void*)grad_hc, (const int32_t*)nullptr);
     FOC_LAUNCH_CHECK(); return 0;
 }

@@ -117,7 +117,68 @@ float* noalloc_partials(int* rc) {
 
 }  // namespace
 
+// NeRFRenderer.mark_untrained_grid (legacy/nerf/renderer.py:380-443): a cell no training camera sees gets density -1 and is left out of
+// the EMA and the bitfield for good.  The reference walks the grid in 64^3 blocks x cascades x pose batches of 64 from Python (meshgrid,
+// morton3D, a batched matmul and three masks per block); here one thread owns one cell (Morton index m of cascade `cas`) and tests it
+// against the poses (c2w [B,4,4] row-major, staged through shared memory) until one sees it:
+//     x_world = (2 c / (H-1) - 1) (bound_c - hgs),  hgs = bound_c / H                                  (l.406-413)
+//     x_cam   = (x_world - t) @ R                    = R^T (x_world - t) for the c2w rotation R, translation t   (l.420-421)
+//     seen    = z > 0  and  |x| < cx/fx z + 2 hgs  and  |y| < cy/fy z + 2 hgs                               (l.424-426)
+__global__ void __launch_bounds__(256)
+k_mark_untrained(const float* __restrict__ poses, uint32_t n_poses, float fx, float fy, float cx, float cy, uint32_t H, uint32_t cascade,
+                 float bound, float* __restrict__ grid, uint32_t* __restrict__ n_marked) {
+    extern __shared__ float s_pose[];                                   // [chunk, 12]: R row-major (9) + t (3)
+    const uint32_t n = H * H * H;
+    const uint64_t gid = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x;
+    const bool live = gid < (uint64_t)cascade * n;
+    const uint32_t cas = live ? (uint32_t)(gid / n) : 0u, m = live ? (uint32_t)(gid - (uint64_t)cas * n) : 0u;
+    const float bound_c = fminf((float)(1u << cas), bound), hgs = bound_c / (float)H;
+    float xw[3];
+    {
+        const uint32_t c[3] = {compact3(m), compact3(m >> 1), compact3(m >> 2)};
+        #pragma unroll
+        for (int d = 0; d < 3; ++d) xw[d] = (2.0f * (float)c[d] / (float)(H - 1) - 1.0f) * (bound_c - hgs);
+    }
+    const float kx = cx / fx, ky = cy / fy, slack = hgs * 2.0f;
+    bool seen = false;
+    constexpr uint32_t kChunk = 64;                                      // the reference's pose batch (S = 64)
+    for (uint32_t p0 = 0; p0 < n_poses; p0 += kChunk) {
+        const uint32_t np = min(kChunk, n_poses - p0);
+        __syncthreads();
+        for (uint32_t i = threadIdx.x; i < np * 12; i += blockDim.x) {
+            const uint32_t p = i / 12, e = i - p * 12;
+            s_pose[i] = e < 9 ? __ldg(poses + (size_t)(p0 + p) * 16 + (e / 3) * 4 + (e % 3)) : __ldg(poses + (size_t)(p0 + p) * 16 + (e - 9) * 4 + 3);
+        }
+        __syncthreads();
+        if (live && !seen) {
+            for (uint32_t p = 0; p < np; ++p) {
+                const float* P = s_pose + p * 12;
+                const float dx = xw[0] - P[9], dy = xw[1] - P[10], dz = xw[2] - P[11];
+                const float z = dx * P[2] + dy * P[5] + dz * P[8];
+                if (!(z > 0.0f)) continue;
+                const float x = dx * P[0] + dy * P[3] + dz * P[6], y = dx * P[1] + dy * P[4] + dz * P[7];
+                if (fabsf(x) < kx * z + slack && fabsf(y) < ky * z + slack) { seen = true; break; }
+            }
+        }
+    }
+    if (live && !seen) {
+        grid[gid] = -1.0f;
+        if (n_marked) atomicAdd(n_marked, 1u);
+    }
+}
+
 static inline cudaStream_t S(void* s) { return reinterpret_cast<cudaStream_t>(s); }
+
+// density_grid [cascade, H^3] (Morton order): cells outside every camera frustum := -1.  n_marked (optional, device, zeroed by the caller)
+// receives how many.
+FOC_API int foc_mark_untrained_grid(const float* poses, uint32_t n_poses, float fx, float fy, float cx, float cy, uint32_t H, uint32_t cascade,
+                                    float bound, float* density_grid, uint32_t* n_marked, void* stream) {
+    if (H < 2 || H > 1024 || cascade == 0 || cascade > 8 || !(fx > 0.f) || !(fy > 0.f)) return FOC_ERR_UNSUPPORTED;
+    const uint64_t total = (uint64_t)cascade * H * H * H;
+    k_mark_untrained<<<(uint32_t)((total + 255) / 256), 256, 64 * 12 * sizeof(float), S(stream)>>>(poses, n_poses, fx, fy, cx, cy, H, cascade, bound,
+                                                                                                   density_grid, n_marked);
+    FOC_LAUNCH_CHECK(); return 0;
+}
 
 FOC_API int foc_density_cell_positions(const int32_t* indices, uint32_t n, uint32_t H, float bound_c, const float* noise, float* xyzs,
                                        void* stream) {

@@ -31,6 +31,7 @@ struct FieldFwdParams {
     float* sigma;                // [B]
     float* rgb;                  // [B,3]
     uint32_t B, num_tiles, n_hmm_s, n_hmm_c, training;
+    const int32_t* n_rows;       // optional: valid leading rows (a multiple of 128), read from device memory; tiles beyond are skipped
 };
 
 // shared-memory map (offsets from the 1024-aligned base)
@@ -117,6 +118,7 @@ k_field_fwd(const __grid_constant__ CUtensorMap tm_in, const __grid_constant__ C
     const uint32_t tmem = *tmem_slot;
     pdl_sync();
 
+    if (p.n_rows != nullptr) { const uint32_t t = (uint32_t)max(__ldg(p.n_rows), 0) / kTile; p.num_tiles = t < p.num_tiles ? t : p.num_tiles; }
     const uint32_t hs = p.n_hmm_s, hc = p.n_hmm_c;
     if (threadIdx.x == 0) {                       // both nets' weights, once per CTA
         mbar_expect_tx(bar_w, 2 * kWinBytes + (hs + hc) * kWhBytes + 2 * kWoutBytes);
@@ -255,7 +257,7 @@ k_field_fwd(const __grid_constant__ CUtensorMap tm_in, const __grid_constant__ C
 
 template <bool TRAIN>
 int launch_field_fwd(const uint16_t* enc, const float* dirs, const uint16_t* w_s, const uint16_t* w_c, uint32_t B, uint32_t L_s, uint32_t L_c,
-                     uint16_t* fb_s, uint16_t* fb_c, uint16_t* cin, float* sigma, float* rgb, cudaStream_t st) {
+                     uint16_t* fb_s, uint16_t* fb_c, uint16_t* cin, float* sigma, float* rgb, const int32_t* n_rows, cudaStream_t st) {
     const uint32_t hs = L_s - 1, hc = L_c - 1;
     CUtensorMap tm_in, tm_win_s, tm_w_s, tm_win_c, tm_w_c, tm_fb_s, tm_fb_c, tm_cin;
     int rc;
@@ -274,7 +276,7 @@ int launch_field_fwd(const uint16_t* enc, const float* dirs, const uint16_t* w_s
     static DynSmemOptIn optin;
     if ((rc = optin.ensure(k_field_fwd<TRAIN>, 227 * 1024))) return rc;
     FieldFwdParams p;
-    p.dirs = dirs; p.sigma = sigma; p.rgb = rgb; p.B = B; p.num_tiles = B / kTile; p.n_hmm_s = hs; p.n_hmm_c = hc; p.training = TRAIN;
+    p.dirs = dirs; p.sigma = sigma; p.rgb = rgb; p.B = B; p.num_tiles = B / kTile; p.n_hmm_s = hs; p.n_hmm_c = hc; p.training = TRAIN; p.n_rows = n_rows;
     const uint32_t want = ceil_div(p.num_tiles, (uint32_t)kGroups);
     const uint32_t grid = want < (uint32_t)kNumSMs ? want : (uint32_t)kNumSMs;
     foc::launch(k_field_fwd<TRAIN>, grid, 128 * kGroups, L.total, st, tm_in, tm_win_s, tm_w_s, tm_win_c, tm_w_c, tm_fb_s, tm_fb_c, tm_cin, p);
@@ -285,9 +287,10 @@ int launch_field_fwd(const uint16_t* enc, const float* dirs, const uint16_t* w_s
 
 // enc [B,32] f16 (hash-grid encodings), dirs [B,3] f32, the two FFMLP weight blobs (fp16, ffmlp.cu:632 layout) -> sigma [B] f32, rgb [B,3] f32.
 // Training (fb_s != NULL): also forward_buffer_s [L_s,B,64], forward_buffer_c [L_c,B,64] and cin [B,32] f16 for the backward kernels.
+// n_rows (optional, device memory): only the first *n_rows rows (a multiple of 128) are evaluated.
 FOC_API int foc_field_forward(const uint16_t* enc, const float* dirs, const uint16_t* weights_sigma, const uint16_t* weights_color, uint32_t B,
                               uint32_t num_layers_sigma, uint32_t num_layers_color, uint16_t* forward_buffer_sigma, uint16_t* forward_buffer_color,
-                              uint16_t* cin, float* sigma, float* rgb, void* stream) {
+                              uint16_t* cin, float* sigma, float* rgb, const int32_t* n_rows, void* stream) {
     if (B == 0) return 0;
     if (B % kTile != 0 || num_layers_sigma < 1 || num_layers_color < 1 || num_layers_sigma - 1 > (uint32_t)kMaxHmm ||
         num_layers_color - 1 > (uint32_t)kMaxHmm) return FOC_ERR_UNSUPPORTED;
@@ -295,7 +298,7 @@ FOC_API int foc_field_forward(const uint16_t* enc, const float* dirs, const uint
     const bool train = forward_buffer_sigma != nullptr;
     if (train && (forward_buffer_color == nullptr || cin == nullptr)) return FOC_ERR_UNSUPPORTED;
     return train ? launch_field_fwd<true>(enc, dirs, weights_sigma, weights_color, B, num_layers_sigma, num_layers_color, forward_buffer_sigma,
-                                          forward_buffer_color, cin, sigma, rgb, st)
+                                          forward_buffer_color, cin, sigma, rgb, n_rows, st)
                  : launch_field_fwd<false>(enc, dirs, weights_sigma, weights_color, B, num_layers_sigma, num_layers_color, nullptr, nullptr, nullptr,
-                                           sigma, rgb, st);
+                                           sigma, rgb, n_rows, st);
 }

@@ -302,8 +302,11 @@ template <typename T, int D, int C, int LAYOUT>
 __global__ void __launch_bounds__(256, 4)
 k_grid_bwd_fused(const T* __restrict__ grad, const float* __restrict__ inputs, const int32_t* __restrict__ offsets,
                  T* __restrict__ grad_table, uint32_t B, uint32_t L, float S, uint32_t H, uint32_t gridtype, bool align_corners,
-                 uint32_t interp, uint32_t n_coarse, uint32_t run_ctas_per_level) {
+                 uint32_t interp, uint32_t n_coarse, uint32_t run_ctas_per_level, const int32_t* __restrict__ n_rows) {
     pdl_sync();
+    // n_rows (optional): valid leading rows, read from device memory (see hashgrid_fwd.cu); the CTA roles below are laid out for the
+    // host-side B, threads whose samples lie beyond the device-side count find nothing to do
+    if (n_rows != nullptr) { const uint32_t v = (uint32_t)max(__ldg(n_rows), 0); B = v < B ? v : B; }
     const uint32_t run_ctas = run_ctas_per_level * n_coarse;
     if (blockIdx.x < run_ctas) {
         const uint32_t level = blockIdx.x / run_ctas_per_level, blk = blockIdx.x - level * run_ctas_per_level;
@@ -320,14 +323,15 @@ constexpr uint32_t kCoarseRes = 128;
 
 template <typename T, int D, int C, int LAYOUT>
 int launch_bwd_layout(const void* grad, const float* inputs, const int32_t* offsets, void* grad_table, uint32_t B, uint32_t L,
-                      float S, uint32_t H, uint32_t gridtype, bool ac, uint32_t interp, cudaStream_t st) {
+                      float S, uint32_t H, uint32_t gridtype, bool ac, uint32_t interp, cudaStream_t st, const int32_t* n_rows = nullptr) {
     uint32_t n_coarse = 0;                                           // same level resolution rule as grid_level()
     while (n_coarse < L && (uint32_t)ceilf(exp2f((float)n_coarse * S) * (float)H - 1.0f) + 1u <= kCoarseRes) ++n_coarse;
-    if (n_coarse > 0 && n_coarse < L && std::getenv("FOC_GRID_BWD_SPLIT") == nullptr) {
+    if (n_rows != nullptr && !(n_coarse > 0 && n_coarse < L)) return FOC_ERR_UNSUPPORTED;      // device-side row count: fused kernel only
+    if (n_coarse > 0 && n_coarse < L && (n_rows != nullptr || std::getenv("FOC_GRID_BWD_SPLIT") == nullptr)) {
         const uint32_t rpl = ceil_div(ceil_div(B, (uint32_t)kRun), 256u);
         const uint64_t sc = ((uint64_t)B * (L - n_coarse) + 255) / 256;
         foc::launch(k_grid_bwd_fused<T, D, C, LAYOUT>, (uint32_t)(rpl * n_coarse + sc), 256, 0, st, (const T*)grad, inputs, offsets, (T*)grad_table, B, L, S, H,
-                    gridtype, ac, interp, n_coarse, rpl);
+                    gridtype, ac, interp, n_coarse, rpl, n_rows);
         FOC_LAUNCH_CHECK();
         return 0;
     }
@@ -347,18 +351,19 @@ int launch_bwd_layout(const void* grad, const float* inputs, const int32_t* offs
 }
 template <typename T, int D, int C>
 int launch_bwd(const void* grad, const float* inputs, const int32_t* offsets, void* grad_table, uint32_t B, uint32_t L,
-               float S, uint32_t H, uint32_t gridtype, bool ac, uint32_t interp, int layout, cudaStream_t st) {
-    return layout == 0 ? launch_bwd_layout<T, D, C, 0>(grad, inputs, offsets, grad_table, B, L, S, H, gridtype, ac, interp, st)
-                       : launch_bwd_layout<T, D, C, 1>(grad, inputs, offsets, grad_table, B, L, S, H, gridtype, ac, interp, st);
+               float S, uint32_t H, uint32_t gridtype, bool ac, uint32_t interp, int layout, cudaStream_t st, const int32_t* n_rows = nullptr) {
+    return layout == 0 ? launch_bwd_layout<T, D, C, 0>(grad, inputs, offsets, grad_table, B, L, S, H, gridtype, ac, interp, st, n_rows)
+                       : launch_bwd_layout<T, D, C, 1>(grad, inputs, offsets, grad_table, B, L, S, H, gridtype, ac, interp, st, n_rows);
 }
 template <typename T, int D>
 int dispatch_bwd(uint32_t C, const void* grad, const float* inputs, const int32_t* offsets, void* grad_table, uint32_t B,
-                 uint32_t L, float S, uint32_t H, uint32_t gridtype, bool ac, uint32_t interp, int layout, cudaStream_t st) {
+                 uint32_t L, float S, uint32_t H, uint32_t gridtype, bool ac, uint32_t interp, int layout, cudaStream_t st,
+                 const int32_t* n_rows = nullptr) {
     switch (C) {
-        case 1: return launch_bwd<T, D, 1>(grad, inputs, offsets, grad_table, B, L, S, H, gridtype, ac, interp, layout, st);
-        case 2: return launch_bwd<T, D, 2>(grad, inputs, offsets, grad_table, B, L, S, H, gridtype, ac, interp, layout, st);
-        case 4: return launch_bwd<T, D, 4>(grad, inputs, offsets, grad_table, B, L, S, H, gridtype, ac, interp, layout, st);
-        case 8: return launch_bwd<T, D, 8>(grad, inputs, offsets, grad_table, B, L, S, H, gridtype, ac, interp, layout, st);
+        case 1: return launch_bwd<T, D, 1>(grad, inputs, offsets, grad_table, B, L, S, H, gridtype, ac, interp, layout, st, n_rows);
+        case 2: return launch_bwd<T, D, 2>(grad, inputs, offsets, grad_table, B, L, S, H, gridtype, ac, interp, layout, st, n_rows);
+        case 4: return launch_bwd<T, D, 4>(grad, inputs, offsets, grad_table, B, L, S, H, gridtype, ac, interp, layout, st, n_rows);
+        case 8: return launch_bwd<T, D, 8>(grad, inputs, offsets, grad_table, B, L, S, H, gridtype, ac, interp, layout, st, n_rows);
         default: return FOC_ERR_UNSUPPORTED;
     }
 }
@@ -395,6 +400,20 @@ FOC_API int foc_grid_encode_backward(const void* grad, const float* inputs, cons
         FOC_LAUNCH_CHECK();
     }
     return 0;
+}
+
+// foc_grid_encode_backward over the first *n_rows rows only (device-side count, see foc_grid_encode_forward_rows); point-major layout,
+// no input gradients.
+FOC_API int foc_grid_encode_backward_rows(const void* grad, const float* inputs, const int32_t* offsets, void* grad_embeddings, uint32_t B,
+                                          uint32_t D, uint32_t C, uint32_t L, float S, uint32_t H, uint32_t gridtype, int align_corners,
+                                          uint32_t interp, int dtype, const int32_t* n_rows, void* stream) {
+    if (B == 0 || L == 0) return 0;
+    if (n_rows == nullptr || D != 3) return FOC_ERR_UNSUPPORTED;
+    cudaStream_t st = reinterpret_cast<cudaStream_t>(stream);
+    const bool ac = align_corners != 0;
+    if (dtype == 1) return dispatch_bwd<__half, 3>(C, grad, inputs, offsets, grad_embeddings, B, L, S, H, gridtype, ac, interp, 1, st, n_rows);
+    if (dtype == 0) return dispatch_bwd<float, 3>(C, grad, inputs, offsets, grad_embeddings, B, L, S, H, gridtype, ac, interp, 1, st, n_rows);
+    return FOC_ERR_UNSUPPORTED;
 }
 
 FOC_API int foc_grad_total_variation(const float* inputs, const float* embeddings, float* grad, const int32_t* offsets,

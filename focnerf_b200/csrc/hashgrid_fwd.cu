@@ -200,8 +200,13 @@ constexpr int kTilePts = 64, kTileMaxLevels = 32;
 template <typename T, int D, int C>
 __global__ void __launch_bounds__(256)
 k_grid_fwd_tile(const float* __restrict__ inputs, const T* __restrict__ table, const int32_t* __restrict__ offsets,
-                T* __restrict__ outputs, uint32_t B, uint32_t L, float S, uint32_t H, uint32_t gridtype, bool align_corners, uint32_t interp) {
+                T* __restrict__ outputs, uint32_t B, uint32_t L, float S, uint32_t H, uint32_t gridtype, bool align_corners, uint32_t interp,
+                const int32_t* __restrict__ n_rows) {
     pdl_sync();
+    // n_rows (optional): the number of VALID leading rows, read from device memory -- a caller that replays this launch inside a CUDA
+    // graph sizes the buffers once (B) and lets the march publish how many rows this step really has; CTAs beyond it leave at once
+    if (n_rows != nullptr) { const uint32_t v = (uint32_t)max(__ldg(n_rows), 0); B = v < B ? v : B; }
+    if (blockIdx.x * kTilePts >= B) return;
     extern __shared__ __align__(16) uint8_t tile_raw[];
     // [64][L*C (+ one 4-byte pad word when a row element is exactly one word: the fp16 C = 2 table -> conflict-free banks)]
     constexpr bool kPad = sizeof(T) * C == 4;
@@ -333,13 +338,15 @@ k_grid_fwd(const float* __restrict__ inputs, const T* __restrict__ table, const 
 
 template <typename T, int D, int C>
 int launch_fwd(const float* inputs, const void* table, const int32_t* offsets, void* outputs, uint32_t B, uint32_t L,
-               float S, uint32_t H, void* dy_dx, uint32_t gridtype, bool ac, uint32_t interp, int layout, cudaStream_t st) {
+               float S, uint32_t H, void* dy_dx, uint32_t gridtype, bool ac, uint32_t interp, int layout, cudaStream_t st, const int32_t* n_rows = nullptr) {
+    const bool tile_ok = layout != 0 && !dy_dx && L <= (uint32_t)kTileMaxLevels && (size_t)kTilePts * (L * C * sizeof(T) + 4) <= 40 * 1024;
+    if (n_rows != nullptr && !tile_ok) return FOC_ERR_UNSUPPORTED;     // the device-side row count is implemented by the tile kernel only
     if (layout == 0) {
         dim3 grid(ceil_div(B, 256), L);
         foc::launch(k_grid_fwd<T, D, C, 0>, grid, 256, 0, st, inputs, (const T*)table, offsets, (T*)outputs, B, L, S, H, (T*)dy_dx, gridtype, ac, interp);
     } else if (!dy_dx && L <= (uint32_t)kTileMaxLevels && (size_t)kTilePts * (L * C * sizeof(T) + 4) <= 40 * 1024) {
         foc::launch(k_grid_fwd_tile<T, D, C>, ceil_div(B, (uint32_t)kTilePts), 256, (size_t)kTilePts * (L * C * sizeof(T) + 4), st, inputs, (const T*)table, offsets,
-                    (T*)outputs, B, L, S, H, gridtype, ac, interp);
+                    (T*)outputs, B, L, S, H, gridtype, ac, interp, n_rows);
     } else {
         const uint64_t total = (uint64_t)B * L;
         foc::launch(k_grid_fwd<T, D, C, 1>, (uint32_t)((total + 255) / 256), 256, 0, st, inputs, (const T*)table, offsets, (T*)outputs, B, L, S, H, (T*)dy_dx, gridtype, ac, interp);
@@ -349,12 +356,13 @@ int launch_fwd(const float* inputs, const void* table, const int32_t* offsets, v
 
 template <typename T, int D>
 int dispatch_c(uint32_t C, const float* inputs, const void* table, const int32_t* offsets, void* outputs, uint32_t B,
-               uint32_t L, float S, uint32_t H, void* dy_dx, uint32_t gridtype, bool ac, uint32_t interp, int layout, cudaStream_t st) {
+               uint32_t L, float S, uint32_t H, void* dy_dx, uint32_t gridtype, bool ac, uint32_t interp, int layout, cudaStream_t st,
+               const int32_t* n_rows = nullptr) {
     switch (C) {
-        case 1: return launch_fwd<T, D, 1>(inputs, table, offsets, outputs, B, L, S, H, dy_dx, gridtype, ac, interp, layout, st);
-        case 2: return launch_fwd<T, D, 2>(inputs, table, offsets, outputs, B, L, S, H, dy_dx, gridtype, ac, interp, layout, st);
-        case 4: return launch_fwd<T, D, 4>(inputs, table, offsets, outputs, B, L, S, H, dy_dx, gridtype, ac, interp, layout, st);
-        case 8: return launch_fwd<T, D, 8>(inputs, table, offsets, outputs, B, L, S, H, dy_dx, gridtype, ac, interp, layout, st);
+        case 1: return launch_fwd<T, D, 1>(inputs, table, offsets, outputs, B, L, S, H, dy_dx, gridtype, ac, interp, layout, st, n_rows);
+        case 2: return launch_fwd<T, D, 2>(inputs, table, offsets, outputs, B, L, S, H, dy_dx, gridtype, ac, interp, layout, st, n_rows);
+        case 4: return launch_fwd<T, D, 4>(inputs, table, offsets, outputs, B, L, S, H, dy_dx, gridtype, ac, interp, layout, st, n_rows);
+        case 8: return launch_fwd<T, D, 8>(inputs, table, offsets, outputs, B, L, S, H, dy_dx, gridtype, ac, interp, layout, st, n_rows);
         default: return FOC_ERR_UNSUPPORTED;     // the reference throws for other C (gridencoder.cu:381)
     }
 }
@@ -387,4 +395,18 @@ FOC_API int foc_grid_encode_forward(const float* inputs, const void* embeddings,
         if (D == 3) return dispatch_c<float, 3>(C, inputs, embeddings, offsets, outputs, B, L, S, H, dy_dx, gridtype, ac, interp, layout, st);
     }
     return FOC_ERR_UNSUPPORTED;                  // the reference supports D in {2,3,4,5}; FOC uses 3 (gridencoder.cu:388-398)
+}
+
+// foc_grid_encode_forward over the first *n_rows rows only (n_rows in device memory, clamped to B): for launches replayed inside a CUDA
+// graph whose buffers are sized once.  Point-major layout without dy_dx (the training / render path); rows >= *n_rows are not written.
+FOC_API int foc_grid_encode_forward_rows(const float* inputs, const void* embeddings, const int32_t* offsets, void* outputs,
+                                         uint32_t B, uint32_t D, uint32_t C, uint32_t L, float S, uint32_t H, uint32_t gridtype,
+                                         int align_corners, uint32_t interp, int dtype, const int32_t* n_rows, void* stream) {
+    if (B == 0 || L == 0) return 0;
+    if (n_rows == nullptr) return FOC_ERR_UNSUPPORTED;
+    cudaStream_t st = reinterpret_cast<cudaStream_t>(stream);
+    const bool ac = align_corners != 0;
+    if (dtype == 1 && D == 3) return dispatch_c<__half, 3>(C, inputs, embeddings, offsets, outputs, B, L, S, H, nullptr, gridtype, ac, interp, 1, st, n_rows);
+    if (dtype == 0 && D == 3) return dispatch_c<float, 3>(C, inputs, embeddings, offsets, outputs, B, L, S, H, nullptr, gridtype, ac, interp, 1, st, n_rows);
+    return FOC_ERR_UNSUPPORTED;
 }

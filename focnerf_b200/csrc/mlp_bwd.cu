@@ -53,6 +53,7 @@ struct BwdParams {
     const float* head_grad;      // grad_rgb / grad_sigma
     const float* head_fwd;       // rgb / sigma
     const __half* head_gcin;     // [B,32] (head 2)
+    const int32_t* n_rows;       // optional: valid leading rows (a multiple of 128), read from device memory; tiles beyond are skipped
     float fifteen;               // 15.0f at run time: expf(+-15) must be the DEVICE's expf, as in k_field_mid_bwd, not a folded constant
     const __half* grad;          // [B, 16]
     const __half* weights;       // flat
@@ -122,6 +123,7 @@ k_mlp_bwd(const __grid_constant__ CUtensorMap tm_fb, const __grid_constant__ CUt
     extern __shared__ uint8_t smem_raw[];
     uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~(uintptr_t)1023);
     const int L = (int)p.num_layers, n_hmm = L - 1;
+    if (p.n_rows != nullptr) { const uint32_t t = (uint32_t)max(__ldg(p.n_rows), 0) / kTile; p.num_tiles = t < p.num_tiles ? t : p.num_tiles; }
     uint64_t* bars = reinterpret_cast<uint64_t*>(smem + SM::off_bars(L));
     uint64_t* bar_act = bars;                     // [L] one per stored-activation tile + [L] = the input tile X: each buffer is
     uint64_t* bar_x = bars + L;                   // refilled for the CTA's NEXT tile as soon as its last reader of this tile is done
@@ -393,12 +395,12 @@ uint32_t bwd_grid(uint32_t B) {
 }
 uint32_t num_params_of(uint32_t input_dim, uint32_t num_layers) { return kHidden * (input_dim + kHidden * (num_layers - 1) + kOutPad); }
 
-struct BwdHead { int head; const float* grad; const float* fwd; const uint16_t* gcin; int accumulate; };
+struct BwdHead { int head; const float* grad; const float* fwd; const uint16_t* gcin; int accumulate; const int32_t* n_rows; };
 
 template <int IN, int ACT>
 int launch_bwd(const uint16_t* grad, const uint16_t* inputs, const uint16_t* weights, const uint16_t* forward_buffer, uint32_t B,
                uint32_t num_layers, uint32_t activation, int calc_grad_inputs, uint16_t* backward_buffer, uint16_t* grad_inputs,
-               uint16_t* grad_weights, void* scratch, cudaStream_t st, BwdHead hd = BwdHead{0, nullptr, nullptr, nullptr, 0}) {
+               uint16_t* grad_weights, void* scratch, cudaStream_t st, BwdHead hd = BwdHead{0, nullptr, nullptr, nullptr, 0, nullptr}) {
     using SM = BwdSmem<IN>;
     CUtensorMap tm_fb, tm_in, tm_win, tm_w;
     int rc = make_tmap_f16_2d(&tm_fb, forward_buffer, (uint64_t)num_layers * B, kHidden, kTile, kHidden);
@@ -414,7 +416,7 @@ int launch_bwd(const uint16_t* grad, const uint16_t* inputs, const uint16_t* wei
     static DynSmemOptIn optin;                                         // per (instantiation, device)
     if (int rc2 = optin.ensure(k_mlp_bwd<IN, ACT>, 227 * 1024)) return rc2;
     BwdParams p;
-    p.head = hd.head; p.head_grad = hd.grad; p.head_fwd = hd.fwd; p.head_gcin = reinterpret_cast<const __half*>(hd.gcin); p.fifteen = 15.0f;
+    p.head = hd.head; p.head_grad = hd.grad; p.head_fwd = hd.fwd; p.head_gcin = reinterpret_cast<const __half*>(hd.gcin); p.fifteen = 15.0f; p.n_rows = hd.n_rows;
     p.grad = reinterpret_cast<const __half*>(grad);
     p.weights = reinterpret_cast<const __half*>(weights);
     p.backward_buffer = reinterpret_cast<__half*>(backward_buffer);
@@ -490,13 +492,14 @@ FOC_API int foc_ffmlp_backward(const uint16_t* grad, const uint16_t* inputs, con
 //                                                                                               -> G = [grad_sigma * clamp(sigma, e^-15, e^15), grad_cin[16:31]]
 // Same values as foc_rgb_sigmoid_backward / foc_field_mid_backward followed by foc_ffmlp_backward.  accumulate != 0: the reduced weight
 // gradient is ADDED to grad_weights (a persistent buffer zeroed by the optimiser sweep), else it overwrites it.  ReLU nets, hidden 64.
+// n_rows (optional, device memory): only the first *n_rows rows (a multiple of 128) take part; grad_inputs rows beyond are not written.
 FOC_API int foc_ffmlp_backward_head(int head, const float* head_grad, const float* head_fwd, const uint16_t* grad_cin, const uint16_t* inputs,
                                     const uint16_t* weights, const uint16_t* forward_buffer, uint32_t B, uint32_t input_dim, uint32_t hidden_dim,
                                     uint32_t num_layers, int calc_grad_inputs, uint16_t* grad_inputs, uint16_t* grad_weights, int accumulate,
-                                    void* scratch, void* stream) {
+                                    const int32_t* n_rows, void* scratch, void* stream) {
     if (B == 0) return 0;
     if (hidden_dim != (uint32_t)kHidden || input_dim != 32 || num_layers < 1 || num_layers > (uint32_t)kMaxLayers || B % kTile != 0 || !scratch ||
         (head != 1 && head != 2) || head_fwd == nullptr || (head == 1 && head_grad == nullptr) || (head == 2 && grad_cin == nullptr)) return FOC_ERR_UNSUPPORTED;
     return launch_bwd<32, 0>(nullptr, inputs, weights, forward_buffer, B, num_layers, 0u, calc_grad_inputs, nullptr, grad_inputs, grad_weights, scratch,
-                             reinterpret_cast<cudaStream_t>(stream), BwdHead{head, head_grad, head_fwd, grad_cin, accumulate});
+                             reinterpret_cast<cudaStream_t>(stream), BwdHead{head, head_grad, head_fwd, grad_cin, accumulate, n_rows});
 }

@@ -542,7 +542,7 @@ __global__ void __launch_bounds__(128) k_march_expand(const float* __restrict__ 
                                                       int32_t* __restrict__ rays, const float* __restrict__ tbuf,
                                                       float* __restrict__ xyzs, float* __restrict__ dirs, float* __restrict__ deltas,
                                                       const uint32_t* __restrict__ counts, const uint32_t* __restrict__ base_slot,
-                                                      int32_t* __restrict__ counter) {
+                                                      int32_t* __restrict__ counter, int32_t* __restrict__ rows_out) {
     pdl_sync();
     const uint32_t n = (blockIdx.x * blockDim.x + threadIdx.x) >> 5, lane = threadIdx.x & 31u;
     uint32_t off, num;
@@ -584,7 +584,16 @@ __global__ void __launch_bounds__(128) k_march_expand(const float* __restrict__ 
                 reinterpret_cast<float2*>(deltas)[i] = make_float2(0.f, 0.f);
             }
         }
-        for (uint64_t i = total + (uint64_t)n * 32u + lane; i < M; i += (uint64_t)N * 32u) {
+        // rows_out (optional): publish the number of valid rows -- the total rounded up to the 128-row tile of the MLP kernels, at
+        // most M -- for consumers that read their row count from device memory (foc_*_rows); only those rows need clearing then
+        uint64_t hi = M;
+        if (rows_out != nullptr) {
+            const uint64_t r128 = (total + 127u) & ~(uint64_t)127u;
+            hi = r128 < (uint64_t)M ? r128 : (uint64_t)M;
+            if (hi == 0) hi = M < 128u ? M : 128u;                     // an empty march still hands one (zero-filled) tile on
+            if (n == N - 1 && lane == 0) rows_out[0] = (int32_t)hi;
+        }
+        for (uint64_t i = total + (uint64_t)n * 32u + lane; i < hi; i += (uint64_t)N * 32u) {
             xyzs[3 * i] = 0.f; xyzs[3 * i + 1] = 0.f; xyzs[3 * i + 2] = 0.f;
             dirs[3 * i] = 0.f; dirs[3 * i + 1] = 0.f; dirs[3 * i + 2] = 0.f;
             reinterpret_cast<float2*>(deltas)[i] = make_float2(0.f, 0.f);
@@ -739,7 +748,7 @@ FOC_API int foc_march_rays_expand(const float* rays_o, const float* rays_d, floa
     const MarchParams p = make_march_params(nullptr, bound, dt_gamma, max_steps, C, H);
     const float* tbuf = reinterpret_cast<const float*>(static_cast<const uint8_t*>(scratch) + march_counts_bytes(N));
     foc::launch(k_march_expand<false>, ceil_div(N, 4), 128, 0, S(stream), rays_o, rays_d, nears, noises, N, M, max_steps, 0u, p, const_cast<int32_t*>(rays), tbuf, xyzs, dirs, deltas,
-                (const uint32_t*)nullptr, (const uint32_t*)nullptr, (int32_t*)nullptr);
+                (const uint32_t*)nullptr, (const uint32_t*)nullptr, (int32_t*)nullptr, (int32_t*)nullptr);
     FOC_LAUNCH_CHECK(); return 0;
 }
 
@@ -784,14 +793,14 @@ FOC_API int foc_march_window_expand(const float* rays_o, const float* rays_d, fl
     const MarchParams p = make_march_params(nullptr, bound, dt_gamma, max_steps, C, H);
     const float* tbuf = reinterpret_cast<const float*>(static_cast<const uint8_t*>(scratch) + march_counts_bytes(N));
     foc::launch(k_march_expand<false>, ceil_div(N, 4), 128, 0, S(stream), rays_o, rays_d, nears, noises, N, M, max_steps, start, p, const_cast<int32_t*>(rays_w), tbuf, xyzs, dirs, deltas,
-                (const uint32_t*)nullptr, (const uint32_t*)nullptr, (int32_t*)nullptr);
+                (const uint32_t*)nullptr, (const uint32_t*)nullptr, (int32_t*)nullptr, (int32_t*)nullptr);
     FOC_LAUNCH_CHECK(); return 0;
 }
 
-FOC_API int foc_march_rays_train(const float* rays_o, const float* rays_d, const uint8_t* grid, float bound, float dt_gamma,
-                                 uint32_t max_steps, uint32_t N, uint32_t C, uint32_t H, uint32_t M, const float* nears,
-                                 const float* fars, float* xyzs, float* dirs, float* deltas, int32_t* rays, int32_t* counter,
-                                 const float* noises, void* scratch, void* stream) {
+static int march_train_impl(const float* rays_o, const float* rays_d, const uint8_t* grid, float bound, float dt_gamma,
+                            uint32_t max_steps, uint32_t N, uint32_t C, uint32_t H, uint32_t M, const float* nears,
+                            const float* fars, float* xyzs, float* dirs, float* deltas, int32_t* rays, int32_t* counter,
+                            const float* noises, void* scratch, void* stream, int32_t* rows_out) {
     if (N != 0 && march_self_scan_ok(dt_gamma, N)) {                   // two launches: record, then an expansion that scans for itself
         if (int rc = march_count_impl(rays_o, rays_d, grid, bound, dt_gamma, max_steps, N, C, H, nears, fars, rays, counter, noises, scratch, stream, true)) return rc;
         const MarchParams p = make_march_params(nullptr, bound, dt_gamma, max_steps, C, H);
@@ -799,11 +808,39 @@ FOC_API int foc_march_rays_train(const float* rays_o, const float* rays_d, const
         const uint32_t* base_slot = reinterpret_cast<const uint32_t*>(static_cast<const uint8_t*>(scratch) + march_block_sums_offset(N));
         const float* tbuf = reinterpret_cast<const float*>(static_cast<const uint8_t*>(scratch) + march_counts_bytes(N));
         foc::launch(k_march_expand<true>, ceil_div(N, 4), 128, 0, S(stream), rays_o, rays_d, nears, noises, N, M, max_steps, 0u, p, rays, tbuf, xyzs, dirs, deltas,
-                    counts, base_slot, counter);
+                    counts, base_slot, counter, rows_out);
         FOC_LAUNCH_CHECK(); return 0;
     }
+    if (N == 0) return 0;
     if (int rc = foc_march_rays_count(rays_o, rays_d, grid, bound, dt_gamma, max_steps, N, C, H, nears, fars, rays, counter, noises, scratch, stream)) return rc;
-    return foc_march_rays_expand(rays_o, rays_d, bound, dt_gamma, max_steps, N, C, H, M, nears, rays, noises, scratch, xyzs, dirs, deltas, stream);
+    if (C == 0 || C > 8 || H == 0 || H > 1024) return FOC_ERR_UNSUPPORTED;
+    const MarchParams p = make_march_params(nullptr, bound, dt_gamma, max_steps, C, H);
+    const float* tbuf = reinterpret_cast<const float*>(static_cast<const uint8_t*>(scratch) + march_counts_bytes(N));
+    foc::launch(k_march_expand<false>, ceil_div(N, 4), 128, 0, S(stream), rays_o, rays_d, nears, noises, N, M, max_steps, 0u, p, rays, tbuf, xyzs, dirs, deltas,
+                (const uint32_t*)nullptr, (const uint32_t*)nullptr, (int32_t*)nullptr, rows_out);
+    FOC_LAUNCH_CHECK(); return 0;
+}
+
+FOC_API int foc_march_rays_train(const float* rays_o, const float* rays_d, const uint8_t* grid, float bound, float dt_gamma,
+                                 uint32_t max_steps, uint32_t N, uint32_t C, uint32_t H, uint32_t M, const float* nears,
+                                 const float* fars, float* xyzs, float* dirs, float* deltas, int32_t* rays, int32_t* counter,
+                                 const float* noises, void* scratch, void* stream) {
+    return march_train_impl(rays_o, rays_d, grid, bound, dt_gamma, max_steps, N, C, H, M, nears, fars, xyzs, dirs, deltas, rays, counter, noises,
+                            scratch, stream, nullptr);
+}
+
+// foc_march_rays_train that also PUBLISHES the number of valid sample rows in device memory: rows_out[0] = min(M, total rounded up to 128).
+// Buffers sized once (M rows, M % 128 == 0) can then be reused by a CUDA-graph replay for steps of any sample count <= M: the consumers
+// (foc_grid_encode_forward_rows, foc_field_forward, foc_ffmlp_backward_head, foc_grid_encode_backward_rows, foc_composite_mse_backward_rows)
+// read the count instead of processing padding rows, and only rows [total, rows_out[0]) are zero-filled.  No reference counterpart: the
+// reference re-allocates per step and drops the rays that do not fit its running-mean-sized buffers (raymarching.py:198-203).
+FOC_API int foc_march_rays_train_rows(const float* rays_o, const float* rays_d, const uint8_t* grid, float bound, float dt_gamma,
+                                      uint32_t max_steps, uint32_t N, uint32_t C, uint32_t H, uint32_t M, const float* nears,
+                                      const float* fars, float* xyzs, float* dirs, float* deltas, int32_t* rays, int32_t* counter,
+                                      const float* noises, int32_t* rows_out, void* scratch, void* stream) {
+    if (rows_out == nullptr || M % 128u != 0) return FOC_ERR_UNSUPPORTED;
+    return march_train_impl(rays_o, rays_d, grid, bound, dt_gamma, max_steps, N, C, H, M, nears, fars, xyzs, dirs, deltas, rays, counter, noises,
+                            scratch, stream, rows_out);
 }
 
 FOC_API int foc_march_rays(uint32_t n_alive, uint32_t n_step, const int32_t* rays_alive, const float* rays_t,

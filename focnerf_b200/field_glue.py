@@ -3,7 +3,7 @@ nerf/network_ff.py:51-74 between encoder, sigma net, colour net and compositor."
 import torch
 from torch.autograd import Function
 
-from ._lib import check, lib, ptr, require_cuda, stream
+from ._lib import check, lib, ptr, require_cuda, stream, valid_rows
 
 
 class _field_mid(Function):
@@ -82,8 +82,10 @@ class _field_eval(Function):
             cin = torch.empty(B, 32, dtype=torch.float16, device=dev)
         else:
             fb_s = fb_c = cin = None
+        rows = valid_rows()
+        ctx.rows = rows
         check(lib().foc_field_forward(ptr(enc), ptr(dirs), ptr(ss), ptr(sc), B, sn.num_layers, cn.num_layers, ptr(fb_s), ptr(fb_c), ptr(cin),
-                                      ptr(sigma), ptr(rgb), stream()), "field_forward")
+                                      ptr(sigma), ptr(rgb), ptr(rows), stream()), "field_forward")
         if train:
             ctx.save_for_backward(enc, cin, fb_s, fb_c, sigma, rgb, ss, sc)
             ctx.nets = (sn, cn)
@@ -99,11 +101,11 @@ class _field_eval(Function):
         g_cin = torch.empty(B, 32, dtype=torch.float16, device=dev)
         scr = torch.empty(l.foc_ffmlp_backward_scratch_bytes(B, 32, 64, cn.num_layers), dtype=torch.uint8, device=dev)
         check(l.foc_ffmlp_backward_head(1, ptr(g_rgb), ptr(rgb), None, ptr(cin), ptr(sc), ptr(fb_c), B, 32, 64, cn.num_layers, 1, ptr(g_cin),
-                                        ptr(cn._grad16), 1, ptr(scr), st), "ffmlp_backward_head(colour)")
+                                        ptr(cn._grad16), 1, ptr(ctx.rows), ptr(scr), st), "ffmlp_backward_head(colour)")
         g_enc = torch.empty(B, 32, dtype=torch.float16, device=dev)
         scr2 = torch.empty(l.foc_ffmlp_backward_scratch_bytes(B, 32, 64, sn.num_layers), dtype=torch.uint8, device=dev)
         check(l.foc_ffmlp_backward_head(2, ptr(g_sigma), ptr(sigma), ptr(g_cin), ptr(enc), ptr(ss), ptr(fb_s), B, 32, 64, sn.num_layers, 1, ptr(g_enc),
-                                        ptr(sn._grad16), 1, ptr(scr2), st), "ffmlp_backward_head(sigma)")
+                                        ptr(sn._grad16), 1, ptr(ctx.rows), ptr(scr2), st), "ffmlp_backward_head(sigma)")
         return g_enc, None, None, None, None, None, None
 
 

@@ -18,7 +18,7 @@ import torch.nn as nn
 from torch.autograd import Function
 from torch.amp import custom_bwd, custom_fwd
 
-from .._lib import check, lib, ptr, require_cuda, stream
+from .._lib import check, lib, ptr, require_cuda, stream, valid_rows
 
 _gridtype_to_id = {'hash': 0, 'tiled': 1}
 _interp_to_id = {'linear': 0, 'smoothstep': 1}
@@ -104,8 +104,15 @@ class _grid_encode(Function):
             ctx.grad16 = grad16
         outputs = torch.empty(B, L * C, device=inputs.device, dtype=embeddings.dtype)
         dy_dx = torch.empty(B, L * D * C, device=inputs.device, dtype=embeddings.dtype) if calc_grad_inputs else None
-        _backend.grid_encode_forward(inputs, embeddings, offsets, outputs, B, D, C, L, S, H, dy_dx, gridtype, align_corners,
-                                     interpolation, FOC_BLC)
+        rows = valid_rows() if (dy_dx is None and D == 3) else None
+        ctx.rows = rows
+        if rows is not None:                                      # graph-replayed step: only the first rows[0] rows are valid
+            check(lib().foc_grid_encode_forward_rows(ptr(inputs), ptr(embeddings), ptr(offsets), ptr(outputs), B, D, C, L, float(S), H, gridtype,
+                                                     int(align_corners), interpolation, _dtype_code(embeddings), ptr(rows), stream()),
+                  "grid_encode_forward_rows")
+        else:
+            _backend.grid_encode_forward(inputs, embeddings, offsets, outputs, B, D, C, L, S, H, dy_dx, gridtype, align_corners,
+                                         interpolation, FOC_BLC)
         ctx.save_for_backward(inputs, embeddings, offsets, dy_dx)
         ctx.dims = [B, D, C, L, S, H, gridtype, interpolation]
         ctx.align_corners = align_corners
@@ -122,8 +129,13 @@ class _grid_encode(Function):
         side = ctx.grad16 is not None
         grad_embeddings = ctx.grad16 if side else torch.zeros_like(embeddings)      # the side buffer accumulates, like .grad
         grad_inputs = torch.zeros_like(inputs, dtype=embeddings.dtype) if dy_dx is not None else None
-        _backend.grid_encode_backward(grad, inputs, embeddings, offsets, grad_embeddings, B, D, C, L, S, H, dy_dx, grad_inputs,
-                                      gridtype, ctx.align_corners, interpolation, FOC_BLC)
+        if ctx.rows is not None:
+            check(lib().foc_grid_encode_backward_rows(ptr(grad), ptr(inputs), ptr(offsets), ptr(grad_embeddings), B, D, C, L, float(S), H, gridtype,
+                                                      int(ctx.align_corners), interpolation, _dtype_code(embeddings), ptr(ctx.rows), stream()),
+                  "grid_encode_backward_rows")
+        else:
+            _backend.grid_encode_backward(grad, inputs, embeddings, offsets, grad_embeddings, B, D, C, L, S, H, dy_dx, grad_inputs,
+                                          gridtype, ctx.align_corners, interpolation, FOC_BLC)
         if dy_dx is not None:
             grad_inputs = grad_inputs.to(inputs.dtype)
         return grad_inputs, (None if side else grad_embeddings), None, None, None, None, None, None, None, None, None

@@ -35,6 +35,14 @@ class MultiObjectRenderer:
             raise ValueError("MultiObjectRenderer: one offset (or None) per object")
         self.num_steps, self.min_near, self.colour_mask, self.fp16 = int(num_steps), float(min_near), bool(colour_mask), bool(fp16)
         self._buf = {}
+        if self.fp16:
+            # resident fp16 copies of the MLP weights: the objects then take forward_fused's one-kernel field evaluation (csrc/field_fwd.cu)
+            # instead of four launches and three round trips per object and chunk (the copies follow later writes of the parameters)
+            for m in self.models:
+                for net in (getattr(m, "sigma_net", None), getattr(m, "color_net", None)):
+                    if net is not None and hasattr(net, "enable_fp16_side_buffers") and getattr(net, "_shadow16", None) is None \
+                            and net.weights.is_cuda:
+                        net.enable_fp16_side_buffers()
 
     def _buffers(self, n, dev):
         key = (n, str(dev))

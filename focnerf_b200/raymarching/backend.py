@@ -49,6 +49,16 @@ class _Backend:
                                          ptr(noises), ptr(scratch), stream()), "march_rays_train")
 
     @staticmethod
+    def march_rays_train_rows(rays_o, rays_d, grid, bound, dt_gamma, max_steps, N, C, H, M, nears, fars, xyzs, dirs, deltas,
+                              rays, counter, noises, rows_out):
+        """march_rays_train that also publishes min(M, total rounded up to 128) in rows_out (int32 [1], device) and zero-fills only up to it"""
+        require_cuda(rays_o, rays_d, grid, nears, fars, xyzs, dirs, deltas, rays, counter, noises, rows_out)
+        scratch = torch.empty(max(1, lib().foc_march_rays_train_scratch_bytes(N, max_steps)), dtype=torch.uint8, device=rays_o.device)
+        check(lib().foc_march_rays_train_rows(ptr(rays_o), ptr(rays_d), ptr(grid), bound, dt_gamma, max_steps, N, C, H, M,
+                                              ptr(nears), ptr(fars), ptr(xyzs), ptr(dirs), ptr(deltas), ptr(rays), ptr(counter),
+                                              ptr(noises), ptr(rows_out), ptr(scratch), stream()), "march_rays_train_rows")
+
+    @staticmethod
     def composite_rays_train_forward(sigmas, rgbs, deltas, rays, M, N, T_thresh, weights_sum, depth, image):
         require_cuda(sigmas, rgbs, deltas, rays, weights_sum, depth, image)
         check(lib().foc_composite_rays_train_forward(ptr(sigmas), ptr(rgbs), ptr(deltas), ptr(rays), M, N, T_thresh,
@@ -126,6 +136,13 @@ class _Backend:
         check(lib().foc_composite_mse_backward(ptr(grad_loss), ptr(gt), bg, ptr(sigmas), ptr(rgbs), ptr(deltas), ptr(rays), ptr(weights_sum),
                                                ptr(image), M, N, T_thresh, int(ordered), ptr(grad_sigmas), ptr(grad_rgbs), stream()),
               "composite_mse_backward")
+
+    @staticmethod
+    def composite_mse_backward_rows(grad_loss, gt, bg, sigmas, rgbs, deltas, rays, weights_sum, image, M, N, T_thresh, grad_sigmas, grad_rgbs, n_rows):
+        require_cuda(grad_loss, gt, sigmas, rgbs, deltas, rays, weights_sum, image, grad_sigmas, grad_rgbs, n_rows)
+        check(lib().foc_composite_mse_backward_rows(ptr(grad_loss), ptr(gt), bg, ptr(sigmas), ptr(rgbs), ptr(deltas), ptr(rays), ptr(weights_sum),
+                                                    ptr(image), M, N, T_thresh, ptr(grad_sigmas), ptr(grad_rgbs), ptr(n_rows), stream()),
+              "composite_mse_backward_rows")
 
     @staticmethod
     def composite_mse_hc_forward(sigmas, hc, deltas, rays, gt, bg, M, N, T_thresh, weights_sum, depth, image, err, loss):

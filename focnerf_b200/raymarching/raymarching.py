@@ -12,6 +12,7 @@ from torch.autograd import Function
 from torch.amp import custom_bwd, custom_fwd
 
 from .backend import _backend
+from .._lib import valid_rows
 
 _fwd32 = custom_fwd(device_type="cuda", cast_inputs=torch.float32)
 _bwd = custom_bwd(device_type="cuda")
@@ -119,8 +120,14 @@ class _march_rays_train(Function):
         if step_counter is None:
             step_counter = torch.zeros(2, dtype=torch.int32, device=dev)
         noises = torch.rand(N, dtype=dt, device=dev) if perturb else torch.zeros(N, dtype=dt, device=dev)
-        _backend.march_rays_train(rays_o, rays_d, density_bitfield, bound, dt_gamma, max_steps, N, C, H, M, nears, fars,
-                                  xyzs, dirs, deltas, rays, step_counter, noises)
+        rows = valid_rows()
+        if rows is not None and not force_all_rays and mean_count > 0 and M % 128 == 0:
+            # graph-replayed step: M is a fixed allocation; the kernel publishes this step's valid row count for the consumers
+            _backend.march_rays_train_rows(rays_o, rays_d, density_bitfield, bound, dt_gamma, max_steps, N, C, H, M, nears, fars,
+                                           xyzs, dirs, deltas, rays, step_counter, noises, rows)
+        else:
+            _backend.march_rays_train(rays_o, rays_d, density_bitfield, bound, dt_gamma, max_steps, N, C, H, M, nears, fars,
+                                      xyzs, dirs, deltas, rays, step_counter, noises)
         if force_all_rays or mean_count <= 0:
             m = _pad_up(int(step_counter[0].item()), align)      # D2H sync, first epochs only (raymarching.py:222)
             xyzs, dirs, deltas = xyzs[:m], dirs[:m], deltas[:m]
@@ -189,8 +196,13 @@ class _composite_rays_train_mse(Function):
         sigmas, rgbs, deltas, rays, gt, weights_sum, image = ctx.saved_tensors
         M, N, T_thresh, bg = ctx.dims
         grad_sigmas, grad_rgbs = torch.empty_like(sigmas), torch.empty_like(rgbs)       # fully written by the kernel (ordered = 1)
-        _backend.composite_mse_backward(grad_loss.float().contiguous().view(1), gt, bg, sigmas, rgbs, deltas, rays, weights_sum, image,
-                                        M, N, T_thresh, 1, grad_sigmas, grad_rgbs)
+        rows = valid_rows()
+        if rows is not None:                                                             # ... up to the step's valid row count
+            _backend.composite_mse_backward_rows(grad_loss.float().contiguous().view(1), gt, bg, sigmas, rgbs, deltas, rays, weights_sum, image,
+                                                 M, N, T_thresh, grad_sigmas, grad_rgbs, rows)
+        else:
+            _backend.composite_mse_backward(grad_loss.float().contiguous().view(1), gt, bg, sigmas, rgbs, deltas, rays, weights_sum, image,
+                                            M, N, T_thresh, 1, grad_sigmas, grad_rgbs)
         return grad_sigmas, grad_rgbs, None, None, None, None, None
 
 

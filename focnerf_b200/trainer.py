@@ -48,6 +48,7 @@ class Trainer:
         self.fused, self.use_graph = fused, use_graph
         self._graph = None
         self._refresh_graph, self._refresh_buf = None, None
+        self.capture_count = 0                          # how many times the step was (re-)captured (bench.py reports it for the timed region)
         # pipeline=True (fused optimiser + graph only, opt-in): the optimiser sweep of step i-1 runs on a side stream next to
         # the march of step i (the march reads rays + bitfield, never the parameters).  `_pending` = a backward has left
         # gradients that no sweep has consumed yet; flush() applies them.  Measured on B200: 0.441 ms vs 0.443 ms per step --
@@ -108,6 +109,18 @@ class Trainer:
         self.density_grid.copy_(g.view_as(self.density_grid))
         thresh = min(float(g.clamp(min=0).mean()), density_thresh)
         raymarching.packbits(g, thresh, self.density_bitfield)
+
+    @torch.no_grad()
+    def mark_untrained_grid(self, poses, intrinsic):
+        """NeRFRenderer.mark_untrained_grid (legacy/nerf/renderer.py:380-443): poses [B,4,4] c2w (numpy or tensor), intrinsic = (fx, fy, cx,
+        cy); grid cells outside every camera frustum get density -1 (never refreshed, never marched).  Returns how many were marked."""
+        from ._lib import check, lib, ptr, stream
+        poses = torch.as_tensor(poses, dtype=torch.float32).to(self.device).contiguous().view(-1, 4, 4)
+        fx, fy, cx, cy = (float(v) for v in intrinsic)
+        n_marked = torch.zeros(1, dtype=torch.int32, device=self.device)
+        check(lib().foc_mark_untrained_grid(ptr(poses), poses.shape[0], fx, fy, cx, cy, self.grid_size, self.cascade, self.bound,
+                                            ptr(self.density_grid), ptr(n_marked), stream()), "mark_untrained_grid")
+        return int(n_marked.item())
 
     def _density_at(self, xyzs):
         """sigma [m] f32 at xyzs [m,3]: `self.density(x)['sigma'] * density_scale` (renderer.py:480-481), through the fused operators when
@@ -269,25 +282,41 @@ class Trainer:
             self.optimizer.step()
             self._pending = False
 
-    def _step_body(self, rays_o, rays_d, gt_rgb, bg_color=1.0, counter=None, mean_count=None):
-        if self.scaler is None:
-            self.flush()
-            self.optimizer.zero_grad(set_to_none=True)      # no-op with persistent gradients (pipeline=True)
-            loss = self._forward_backward(rays_o, rays_d, gt_rgb, bg_color, counter, mean_count)
-            self.optimizer.step()
+    def _step_body(self, rays_o, rays_d, gt_rgb, bg_color=1.0, counter=None, mean_count=None, rows=None):
+        """rows (int32 [1] device tensor, graph-replayed step only): the march publishes this step's valid row count into it and the
+        grid / field / compositor operators process that many rows of the fixed-size sample buffers (_lib.set_valid_rows)."""
+        from ._lib import set_valid_rows
+        prev = set_valid_rows(rows)
+        try:
+            if self.scaler is None:
+                self.flush()
+                self.optimizer.zero_grad(set_to_none=True)      # no-op with persistent gradients (pipeline=True)
+                loss = self._forward_backward(rays_o, rays_d, gt_rgb, bg_color, counter, mean_count)
+                self.optimizer.step()
+                return loss
+            self.optimizer.zero_grad(set_to_none=True)
+            with torch.autocast("cuda", dtype=torch.float16, enabled=self.fp16):
+                image, _, _ = self.render_train(rays_o, rays_d, bg_color, counter=counter, mean_count=mean_count)
+                loss = torch.nn.functional.mse_loss(image, gt_rgb)
+            self.scaler.scale(loss).backward()
+            if self.grad_sync is not None:
+                self.grad_sync()
+            self.scaler.step(self.optimizer)
+            self.scaler.update()
+            if self.lr_scheduler is not None:
+                self.lr_scheduler.step()
             return loss
-        self.optimizer.zero_grad(set_to_none=True)
-        with torch.autocast("cuda", dtype=torch.float16, enabled=self.fp16):
-            image, _, _ = self.render_train(rays_o, rays_d, bg_color, counter=counter, mean_count=mean_count)
-            loss = torch.nn.functional.mse_loss(image, gt_rgb)
-        self.scaler.scale(loss).backward()
-        if self.grad_sync is not None:
-            self.grad_sync()
-        self.scaler.step(self.optimizer)
-        self.scaler.update()
-        if self.lr_scheduler is not None:
-            self.lr_scheduler.step()
-        return loss
+        finally:
+            set_valid_rows(prev)
+
+    def _rows_mode(self):
+        """Device-side row counts need every consumer of the sample buffers to honour them: the one-kernel field path with fp16 side
+        buffers (the unfused FFMLP kernels would accumulate weight gradients over stale rows beyond the count)."""
+        m = self.model
+        return (self.scaler is None and self.fused and self.fp16 and not self.pipeline and not self._fuse_rgb and self._wgrad_side is None
+                and getattr(m, "_field_fused", False) and getattr(m.sigma_net, "_shadow16", None) is not None
+                and getattr(m.color_net, "_shadow16", None) is not None and getattr(m.encoder, "_shadow16", None) is not None
+                and __import__("os").environ.get("FOC_ROWS", "1") == "1")
 
     def _pipelined_body(self, rays_o, rays_d, gt_rgb, bg_color, counter, mean_count):
         """[ optimiser sweep of the PREVIOUS step || near/far + march of this step ] -> field -> composite -> backward."""
@@ -323,9 +352,19 @@ class Trainer:
         be static: the sample buffers are sized by the reference's own `mean_count` rule (raymarching.py:198-203), here
         rounded up to GRAPH_QUANTUM so that the 16-step refresh of mean_count only re-captures when it moves by > 16k."""
         q = self.GRAPH_QUANTUM
-        m_q = ((self.mean_count + q - 1) // q) * q
-        if self._graph is not None and m_q <= self._graph[0][0] <= m_q + q:       # hysteresis: keep a slightly larger buffer
-            m_q = self._graph[0][0]
+        rows_mode = self._rows_mode()
+        if rows_mode:
+            # fixed allocation with 50 % headroom over the running mean: the kernels read the step's real row count from device memory, so
+            # the size only matters when a step would not fit (its trailing rays are then dropped, as the reference drops them against its
+            # mean-sized buffers, raymarching.py:198-203).  Re-capture only when the mean has grown to within 10 % of the allocation or
+            # shrunk below a third of it -- a drifting sample count no longer re-captures the step every few refreshes.
+            m_q = ((int(self.mean_count * 1.5) + q - 1) // q) * q
+            if self._graph is not None and self.mean_count * 1.1 <= self._graph[0][0] <= max(self.mean_count, 1) * 3 + q:
+                m_q = self._graph[0][0]
+        else:
+            m_q = ((self.mean_count + q - 1) // q) * q
+            if self._graph is not None and m_q <= self._graph[0][0] <= m_q + q:       # hysteresis: keep a slightly larger buffer
+                m_q = self._graph[0][0]
         pipelined = self.pipeline
         key = (m_q, tuple(rays_o.shape), float(bg_color), pipelined)
         if pipelined and not self._pending:
@@ -339,19 +378,21 @@ class Trainer:
             for dst, src in zip(g_in, (rays_o, rays_d, gt_rgb)):
                 dst.copy_(src)
             g_counter = torch.zeros(2, dtype=torch.int32, device=rays_o.device)
+            g_rows = torch.full((1,), m_q, dtype=torch.int32, device=rays_o.device) if rows_mode else None
             torch.cuda.synchronize()
             graph = torch.cuda.CUDAGraph()
             if not pipelined:
                 self.optimizer.zero_grad(set_to_none=True)
             if self._capture_stream is None:           # the step's own kernels outrank the deferred optimiser sweep
                 self._capture_stream = torch.cuda.Stream(priority=-1)
+            self.capture_count += 1
             with torch.cuda.graph(graph, stream=self._capture_stream):
                 if pipelined:
                     g_loss = self._pipelined_body(g_in[0], g_in[1], g_in[2], bg_color, g_counter, m_q)
                 else:
-                    g_loss = self._step_body(g_in[0], g_in[1], g_in[2], bg_color, counter=g_counter, mean_count=m_q)
-            self._graph = (key, graph, g_in, g_counter, g_loss)
-        _, graph, g_in, g_counter, g_loss = self._graph
+                    g_loss = self._step_body(g_in[0], g_in[1], g_in[2], bg_color, counter=g_counter, mean_count=m_q, rows=g_rows)
+            self._graph = (key, graph, g_in, g_counter, g_loss, g_rows)
+        _, graph, g_in, g_counter, g_loss = self._graph[:5]
         for dst, src in zip(g_in, (rays_o, rays_d, gt_rgb)):
             if dst.data_ptr() != src.data_ptr():
                 dst.copy_(src, non_blocking=True)

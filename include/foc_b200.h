@@ -181,6 +181,24 @@ int foc_ffmlp_wgrad_finish(const void *scratch, uint32_t B, uint32_t input_dim, 
 /* same reduction, ADDED to what grad_weights holds (`.grad` semantics for a persistent gradient buffer zeroed by the optimiser sweep) */
 int foc_ffmlp_wgrad_accumulate(const void *scratch, uint32_t B, uint32_t input_dim, uint32_t hidden_dim, uint32_t num_layers,
                                uint16_t *grad_weights, void *stream);
+/* ---- device-side row counts (no reference counterpart).  A train step replayed as a CUDA graph has fixed buffer sizes, while the number
+ * of samples the march produces changes every step.  foc_march_rays_train_rows publishes rows_out[0] = min(M, total rounded up to 128) in
+ * device memory and zero-fills only [total, rows_out[0]); the *_rows consumers (and the optional n_rows argument of foc_field_forward /
+ * foc_ffmlp_backward_head) process the first *n_rows rows only.  NULL n_rows = all B rows.  M and *n_rows are multiples of 128. */
+int foc_march_rays_train_rows(const float *rays_o, const float *rays_d, const uint8_t *grid, float bound, float dt_gamma,
+                              uint32_t max_steps, uint32_t N, uint32_t C, uint32_t H, uint32_t M, const float *nears,
+                              const float *fars, float *xyzs, float *dirs, float *deltas, int32_t *rays, int32_t *counter,
+                              const float *noises, int32_t *rows_out, void *scratch, void *stream);
+int foc_grid_encode_forward_rows(const float *inputs, const void *embeddings, const int32_t *offsets, void *outputs, uint32_t B,
+                                 uint32_t D, uint32_t C, uint32_t L, float S, uint32_t H, uint32_t gridtype, int align_corners,
+                                 uint32_t interp, int dtype, const int32_t *n_rows, void *stream);
+int foc_grid_encode_backward_rows(const void *grad, const float *inputs, const int32_t *offsets, void *grad_embeddings, uint32_t B,
+                                  uint32_t D, uint32_t C, uint32_t L, float S, uint32_t H, uint32_t gridtype, int align_corners,
+                                  uint32_t interp, int dtype, const int32_t *n_rows, void *stream);
+int foc_composite_mse_backward_rows(const float *grad_loss, const float *gt, float bg, const float *sigmas, const float *rgbs,
+                                    const float *deltas, const int32_t *rays, const float *weights_sum, const float *image, uint32_t M,
+                                    uint32_t N, float T_thresh, float *grad_sigmas, float *grad_rgbs, const int32_t *n_rows, void *stream);
+
 /* The FOC field behind the hash grid in one kernel (nerf/network_ff.py:51-74: sigma_net -> trunc_exp / SH-4 / cat -> color_net ->
  * sigmoid; two ffmlp_forward calls (ffmlp.h:7) + ~10 elementwise torch kernels in the reference).  enc [B,32] f16, dirs [B,3] f32,
  * fp16 weight blobs in the ffmlp.cu:632 layout, hidden width 64, B % 128 == 0 -> sigma [B] f32, rgb [B,3] f32.  Training: pass
@@ -188,14 +206,14 @@ int foc_ffmlp_wgrad_accumulate(const void *scratch, uint32_t B, uint32_t input_d
  * NULL for all three = inference.  Bit-identical to foc_ffmlp_forward x 2 + foc_field_mid_forward + foc_rgb_sigmoid_forward. */
 int foc_field_forward(const uint16_t *enc, const float *dirs, const uint16_t *weights_sigma, const uint16_t *weights_color, uint32_t B,
                       uint32_t num_layers_sigma, uint32_t num_layers_color, uint16_t *forward_buffer_sigma,
-                      uint16_t *forward_buffer_color, uint16_t *cin, float *sigma, float *rgb, void *stream);
+                      uint16_t *forward_buffer_color, uint16_t *cin, float *sigma, float *rgb, const int32_t *n_rows, void *stream);
 /* foc_ffmlp_backward for the two nets of the FOC field with the output gradient formed in the kernel's prologue (see csrc/mlp_bwd.cu):
  * head 1 = colour net from grad_rgb / rgb [B,3] f32; head 2 = sigma net from grad_sigma (or NULL) / sigma [B] f32 and the colour net's
  * grad_inputs grad_cin [B,32] f16.  scratch: foc_ffmlp_backward_scratch_bytes.  accumulate != 0 adds to grad_weights. */
 int foc_ffmlp_backward_head(int head, const float *head_grad, const float *head_fwd, const uint16_t *grad_cin, const uint16_t *inputs,
                             const uint16_t *weights, const uint16_t *forward_buffer, uint32_t B, uint32_t input_dim, uint32_t hidden_dim,
                             uint32_t num_layers, int calc_grad_inputs, uint16_t *grad_inputs, uint16_t *grad_weights, int accumulate,
-                            void *scratch, void *stream);
+                            const int32_t *n_rows, void *scratch, void *stream);
 /* kept for API compatibility with ffmlp.h:12-13; no-ops (no side streams, no workspaces) */
 int foc_allocate_splitk(size_t size);
 int foc_free_splitk(void);
@@ -233,6 +251,10 @@ int foc_density_cell_positions(const int32_t *indices, uint32_t n, uint32_t H, f
 size_t foc_density_grid_update_scratch_bytes(uint32_t n);
 int foc_density_grid_update(float *grid, const float *tmp, uint32_t n, float decay, float density_thresh, float *mean,
                             uint8_t *bitfield, void *scratch, void *stream);
+/* NeRFRenderer.mark_untrained_grid (legacy/nerf/renderer.py:380-443; FOC copy nerf/renderer.py:357-417): density_grid [cascade, H^3] cells
+ * that no pose (c2w [n_poses,4,4] row-major, pinhole fx fy cx cy) sees := -1.  n_marked: optional device counter (zeroed by the caller). */
+int foc_mark_untrained_grid(const float *poses, uint32_t n_poses, float fx, float fy, float cx, float cy, uint32_t H, uint32_t cascade,
+                            float bound, float *density_grid, uint32_t *n_marked, void *stream);
 /* foc_density_grid_update WITHOUT a caller-supplied scratch buffer and without any allocation.  No counterpart in the reference:
  * added for callers that cannot call cudaMalloc (code under CUDA graph capture, tight
  * serving loops, harnesses that forbid it).  The per-CTA partial sums of the mean live in a file-scope

@@ -230,3 +230,40 @@ def test_partial_refresh_static_shapes_and_graph_replay():
         torch.manual_seed(13)
         tr.update_extra_state(); tr.update_extra_state()
     assert torch.equal(c.density_bitfield, d.density_bitfield) and torch.equal(c.density_grid, d.density_grid)
+
+
+def test_mark_untrained_grid_vs_reference_logic():
+    """csrc/density_grid.cu: k_mark_untrained against the reference's steps (legacy/nerf/renderer.py:380-443) restated with torch ops:
+    same cells marked -1, up to cells whose frustum test falls within float rounding of a mask edge."""
+    import synthetic
+    from focnerf_b200 import raymarching as rm
+    for bound, n_poses, radius in ((1.0, 5, 2.2), (2.0, 70, 3.0)):
+        scene, tr = _trainer(bound)
+        H, C = tr.grid_size, tr.cascade
+        poses = synthetic.ring_poses(n_poses, radius=radius, seed=9)
+        fx, fy, cx, cy = synthetic.intrinsics(800, 800, fovy_deg=30.0)
+        grid0 = tr.density_grid.clone()
+        got = tr.mark_untrained_grid(poses, (fx, fy, cx, cy))
+        P = torch.from_numpy(poses).cuda()
+        idx = torch.arange(H ** 3, dtype=torch.int32, device="cuda")
+        coords = rm.morton3D_invert(idx).float()
+        world = 2 * coords / (H - 1) - 1
+        count = torch.zeros(C, H ** 3, device="cuda")
+        margin = torch.full((C, H ** 3), 1e9, device="cuda")            # distance of each test from its mask edge, for the rounding band
+        for cas in range(C):
+            b = min(2 ** cas, bound)
+            hgs = b / H
+            xw = (world * (b - hgs)).unsqueeze(0)
+            cam = (xw - P[:, :3, 3].unsqueeze(1)) @ P[:, :3, :3]
+            z = cam[..., 2]
+            ex = cx / fx * z + hgs * 2 - cam[..., 0].abs()
+            ey = cy / fy * z + hgs * 2 - cam[..., 1].abs()
+            count[cas] = ((z > 0) & (ex > 0) & (ey > 0)).sum(0)
+            margin[cas] = torch.minimum(torch.minimum(z.abs(), ex.abs()), ey.abs()).amin(0)
+        want = count == 0
+        have = tr.density_grid == -1
+        differ = want != have
+        assert int((differ & (margin > 1e-5)).sum()) == 0                # any disagreement sits on a mask edge
+        assert int(differ.sum()) <= 64
+        assert got == int(have.sum()) and 0 < got < C * H ** 3
+        assert torch.equal(tr.density_grid[~have], grid0[~have])         # seen cells untouched

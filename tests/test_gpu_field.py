@@ -111,3 +111,41 @@ def test_trainer_step_with_and_without_the_fused_field_gives_the_same_losses(mon
     # step 1 is bit-identical; later steps differ only through the fp16 atomics of the grid backward (arrival order)
     assert losses["0"][0] == losses["1"][0]
     assert np.allclose(losses["0"], losses["1"], rtol=2e-3)
+
+
+def test_graph_step_with_device_side_row_count(monkeypatch):
+    """The graph-replayed step with a fixed 1.5x allocation whose kernels read the valid row count from device memory (FOC_ROWS=1,
+    include/foc_b200.h "device-side row counts") against the same step on mean-sized, fully processed buffers (FOC_ROWS=0): same
+    samples, same losses (up to the fp16 atomics of the grid backward), the published count is the step's total rounded up to 128,
+    and a drifting sample count does not re-capture the graph."""
+    import cases
+    from focnerf_b200.trainer import Trainer
+    scene, cascade, grid, bits, thresh = cases.scene_bitfield(1.0)
+    batches = []
+    for i in range(6):
+        o, dd = cases.camera_rays(4096, 700 + i)
+        o, dd = torch.from_numpy(o).cuda(), torch.from_numpy(dd).cuda()
+        batches.append((o, dd, scene.render_gt(o, dd)))
+    runs = {}
+    for rows in ("0", "1"):
+        monkeypatch.setenv("FOC_ROWS", rows)
+        tr = Trainer(bound=1.0, density_grid=torch.from_numpy(grid), seed=2, use_graph=True, lr=1e-2)
+        torch.manual_seed(55)
+        losses, counts = [], []
+        for it in range(48):
+            losses.append(float(tr.train_step(*batches[it % len(batches)])))
+            if tr.local_step % 16 == 0:
+                tr.update_mean_count()
+            counts.append(int(tr.step_counter[(tr.local_step - 1) % 16, 0]))
+        assert tr._rows_mode() == (rows == "1")
+        runs[rows] = (losses, counts, tr)
+    l0, c0, _ = runs["0"]
+    l1, c1, tr1 = runs["1"]
+    assert c0[:16] == c1[:16]                                        # eager steps before the first capture: identical marches
+    assert np.allclose(l0, l1, rtol=5e-2, atol=1e-4), (l0[-4:], l1[-4:])
+    assert np.mean(l1[-8:]) < 0.5 * np.mean(l1[:4])                   # it trains
+    g_rows = int(tr1._graph[5])
+    m_alloc = tr1._graph[0][0]
+    assert g_rows == min(m_alloc + 128, (c1[-1] + 127) // 128 * 128) and g_rows % 128 == 0
+    assert m_alloc >= int(1.4 * tr1.mean_count)
+    assert tr1.capture_count == 1                                     # sample counts moved every step; one capture served them all

@@ -112,7 +112,7 @@ def _train_rank(rank, world, port, mode, result):
     import cases
     from focnerf_b200.trainer import Trainer
     scene, cascade, grid, bits, thresh = cases.scene_bitfield(1.0)
-    tr = Trainer(bound=1.0, density_grid=torch.from_numpy(grid), device=dev, seed=0, use_graph=True, data_parallel=mode)
+    tr = Trainer(bound=1.0, density_grid=torch.from_numpy(grid), device=dev, seed=0, use_graph=True, data_parallel=mode, lr=1e-2)
     losses = []
     for it in range(40):
         o, d = cases.camera_rays(1024, seed=100 + 2 * it + rank)          # every rank its own rays
