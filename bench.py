@@ -253,7 +253,7 @@ def run_ours(args):
     loop(tr, C.PRETRAIN, False, 0)
     torch.cuda.synchronize()
     pretrain_s = time.time() - t0
-    psnrs = [C.psnr_of(tr.render(eo, ed)[0], egt)] if world == 1 else []
+    psnrs = [C.psnr_of(tr.render(eo, ed)[0], egt)]            # N > 1: the data-parallel model (N x 4096 rays per step), reported as quality_dp
 
     # ---- timed region ---------------------------------------------------------------------------------------------------------------
     warm = max(3, args.warmup)
@@ -393,6 +393,8 @@ def run_ours(args):
 
     # ---- quality: the other seeds of the fixed-iteration run ---------------------------------------------------------------------------
     quality = None
+    quality_dp = None if world == 1 else {"psnr_db": psnrs[0], "steps": C.PRETRAIN, "rays_per_step": world * C.RAYS_PER_GPU, "eval_rays": C.EVAL_RAYS,
+                                          "note": "rank 0's replica after the protocol's PRETRAIN data-parallel steps, held-out rays"}
     if world == 1:
         if args.psnr_steps > 0:
             for s in C.QUALITY_SEEDS[1:args.psnr_seeds]:
@@ -491,7 +493,7 @@ def run_ours(args):
                 "h2d_bytes_per_step": world * C.RAYS_PER_GPU * 9 * 4, "d2h_bytes_per_step": world * 4},
         "gpu_launches": int(round(launches_per_step * args.steps)),
         "render_own_model": render_own if render is not render_own else None,
-        "multi_object": multi, "multi_object_edit8": multi8, "density_refresh": refresh, "quality": quality, "frozen_bitfield": frozen,
+        "multi_object": multi, "multi_object_edit8": multi8, "density_refresh": refresh, "quality": quality, "quality_dp": quality_dp, "frozen_bitfield": frozen,
         "roofline": roof,
     }
     if world == 1:

@@ -268,6 +268,8 @@ class PeerAdam(ScaledAdam):
             g = g16 if g16 is not None else p.grad
             if g is not None:
                 self.tail_grad[off:off + p.numel()].copy_(g.reshape(-1))
+                if g16 is not None:
+                    g16.zero_()                                # consumed: the side buffers ACCUMULATE between steps (like .grad)
         fi = None if self.scale is None else self.found_inf
         self.arena.barrier()                                   # every rank's gradients are complete
         check(l.foc_dp_reduce(ctypes.byref(self._reduce_args), st), "dp_reduce")
