@@ -40,7 +40,7 @@ ALG_BYTES = {
 }
 ALG_BYTES_PER_PARAM = {"foc_adam_step": 30, "foc_adam_nonfinite": 2}
 # data-parallel exchange (csrc/peer.cu): timed, no single-GPU roofline (NVLink pulls / pushes of 1/N of the table + barrier latency)
-PEER_TIMED = ["foc_dp_reduce", "foc_adam_step_peers", "foc_peer_barrier"]
+PEER_TIMED = ["foc_dp_reduce", "foc_adam_step_peers", "foc_adam_step_dp", "foc_peer_barrier"]
 N_PARAMS = 6119864 * 2 + 7168 + 11264
 # MLP entry points: FLOPs per sample and call (sigma net 32-64-64-16, colour net 32-64-64-64-16), forward; backward = 2x
 MLP_FLOPS_FWD = 36864
@@ -126,8 +126,11 @@ def render_bench(tr, dev, rank, world, frames=3, H=800, W=800, tag="own"):
     torch.cuda.synchronize()
     e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
     e0.record()
-    for _ in range(frames):
-        out = frame()
+    if via_peer or world == 1:                       # a camera path: no host read between frames, one at the end (Trainer.render_frames)
+        out = tr.render_frames([(o, d)] * frames, exchange=ex)[-1]
+    else:
+        for _ in range(frames):
+            out = frame()
     e1.record()
     if world > 1:
         dist.barrier()
@@ -137,7 +140,8 @@ def render_bench(tr, dev, rank, world, frames=3, H=800, W=800, tag="own"):
         dist.all_reduce(ms, op=dist.ReduceOp.MAX)
     ms = float(ms.item()) / frames
     return {"metric": "800x800 render Mrays/s", "value": n / (ms * 1e-3) / 1e6, "unit": "Mrays/s", "ms_per_frame": ms, "frames": frames,
-            "rays": n, "scaling": "strong", "coverage": C.coverage_of(out[0]), "mean_image": float(out[0].float().mean().item()), "checkpoint": tag,
+            "rays": n, "scaling": "strong", "host_reads": "one 4-byte read per %d-frame path (Trainer.render_frames)" % frames if (via_peer or world == 1) else "one per frame",
+            "frames_rendered_twice": tr.render_overflows, "coverage": C.coverage_of(out[0]), "mean_image": float(out[0].float().mean().item()), "checkpoint": tag,
             "exchange": "peer-memory stores in the render epilogue" if via_peer else ("all_gather" if world > 1 else None),
             "workload": "configs[2]: one 800x800 test pose of the synthetic scene, T_thresh 1e-4, max_steps 1024"}
 
@@ -468,6 +472,11 @@ def run_ours(args):
         if k in MLP_BYTES:
             flops = MLP_FLOPS[k] * samples_prof / calls
             row.update({"tensor_TFLOPs": flops / t_call / 1e12, "tensor_frac_of_burst": flops / t_call / 1e12 / tc_burst})
+        tk = traffic.get("entry_points", {}).get(k[:-5] if k.endswith("_rows") else k)
+        if tk:                                            # measured by ncu on one step of this workload, scaled to this run's samples per step
+            sc_ = 1.0 if k in ALG_BYTES_PER_PARAM else samples_prof / traffic["samples_per_step"]
+            row.update({"algorithmic_MB": nbytes / 1e6, "ncu_dram_MB": tk["dram_bytes"] * sc_ / 1e6, "ncu_l2_MB": tk["l2_bytes"] * sc_ / 1e6,
+                        "l2_GBs": tk["l2_bytes"] * sc_ / t_call / 1e9, "ncu_tensor_pipe_pct": tk["tensor_pipe_pct"]})
         rows[k] = {kk: round(vv, 4) for kk, vv in row.items()}
     top = max((k for k in per if k not in PEER_TIMED), key=per.get)
     r_ = rows[top]
@@ -476,7 +485,10 @@ def run_ours(args):
                 "hbm_frac": r_["hbm_frac"], "note": "timed alone between events -> burst peak; in fact HBM-bound at training sizes, see hbm_frac"}
     else:
         roof = {"kernel": top, "bound": "hbm", "achieved": r_["hbm_GBs"], "peak": hbm, "unit": "GB/s", "frac": r_["hbm_frac"]}
-    roof.update({"traffic": traffic.get(top), "traffic_source": "profiles/r2_traffic.json (ncu --set full, DRAM bytes per call)" if traffic.get(top) else None,
+    t_top = traffic.get("entry_points", {}).get(top[:-5] if top.endswith("_rows") else top)
+    roof.update({"traffic": None if not t_top else round(t_top["dram_bytes"] * (1.0 if top in ALG_BYTES_PER_PARAM else samples_prof / traffic["samples_per_step"])),
+                 "traffic_source": "profiles/r2_traffic.json: dram__bytes_read.sum + dram__bytes_write.sum per call from the committed ncu --set full capture of this "
+                                   "workload (profiles/r2_kernels.md), scaled by samples per step" if t_top else None,
                  "peak_source": how, "ms_per_launch": r_["ms_per_call"], "samples_per_step": samples_prof, "timing": timing_mode,
                  "ms_per_step_by_entry_point": {k: round(v, 4) for k, v in sorted(per.items(), key=lambda kv: -kv[1])}, "by_entry_point": rows})
     out = {

@@ -35,6 +35,49 @@ struct PeerShadow {
     int world, tensor;
 };
 
+// foc_adam_step_dp: where the gradients of a data-parallel step come from -- every rank's buffers, read over peer memory
+struct PeerGrad {
+    const uint16_t* g16[FOC_MAX_PEERS];        // fp16 table gradients, already offset to THIS rank's shard
+    const float* tail[FOC_MAX_PEERS];          // flat fp32 gradients of the replicated tensors; tensors[i].grad points into tail[rank]
+    int rank;
+};
+// peer data: never served from a stale L1 line
+__device__ __forceinline__ uint2 ld_peer8(const void* p) {
+    uint2 v; asm volatile("ld.relaxed.sys.global.v2.u32 {%0,%1}, [%2];" : "=r"(v.x), "=r"(v.y) : "l"(p) : "memory"); return v;
+}
+__device__ __forceinline__ uint4 ld_peer16(const void* p) {
+    uint4 v; asm volatile("ld.relaxed.sys.global.v4.u32 {%0,%1,%2,%3}, [%4];" : "=r"(v.x), "=r"(v.y), "=r"(v.z), "=r"(v.w) : "l"(p) : "memory"); return v;
+}
+// mean over the W ranks, summed in fp32 in rank order: the same bits on whichever rank owns the element (k_dp_reduce's arithmetic)
+template <int W>
+__device__ __forceinline__ void pull_table4(const PeerGrad& G, uint64_t i, float (&g)[4]) {
+    uint2 v[W];
+    #pragma unroll
+    for (int r = 0; r < W; ++r) v[r] = ld_peer8(G.g16[r] + i);
+    g[0] = g[1] = g[2] = g[3] = 0.f;
+    #pragma unroll
+    for (int r = 0; r < W; ++r) {
+        const __half2 a = *reinterpret_cast<const __half2*>(&v[r].x), b = *reinterpret_cast<const __half2*>(&v[r].y);
+        g[0] += __low2float(a); g[1] += __high2float(a); g[2] += __low2float(b); g[3] += __high2float(b);
+    }
+    const float inv = 1.0f / (float)W;
+    #pragma unroll
+    for (int k = 0; k < 4; ++k) g[k] *= inv;
+}
+template <int W>
+__device__ __forceinline__ void pull_tail4(const PeerGrad& G, const FocAdamTensor& T, uint64_t i, float (&g)[4]) {
+    const uint64_t off = (uint64_t)(static_cast<const float*>(T.grad) - G.tail[G.rank]) + i;     // rows start on 4-float boundaries, padded with zeros
+    uint4 v[W];
+    #pragma unroll
+    for (int r = 0; r < W; ++r) v[r] = ld_peer16(G.tail[r] + off);
+    g[0] = g[1] = g[2] = g[3] = 0.f;
+    #pragma unroll
+    for (int r = 0; r < W; ++r) { g[0] += __uint_as_float(v[r].x); g[1] += __uint_as_float(v[r].y); g[2] += __uint_as_float(v[r].z); g[3] += __uint_as_float(v[r].w); }
+    const float inv = 1.0f / (float)W;
+    #pragma unroll
+    for (int k = 0; k < 4; ++k) g[k] *= inv;
+}
+
 __device__ __forceinline__ int find_tensor(const AdamList& L, uint32_t block) {
     int i = 0;
     #pragma unroll
@@ -104,10 +147,14 @@ __global__ void __launch_bounds__(kThreads) k_adam_nonfinite(const __grid_consta
     if (!ok) *found_inf = 1.0f;
 }
 
-template <bool PEERS>
+// PULL = W > 0 (foc_adam_step_dp): the gradient exchange of a W-rank data-parallel step happens HERE -- each element's gradient is the
+// mean of the W ranks' values, loaded over peer memory at the point of use, so the shard is swept once (pull -> fp32 mean -> Adam ->
+// push) instead of k_dp_reduce writing an fp32 copy that this kernel reads back.
+template <bool PEERS, int PULL>
 __global__ void __launch_bounds__(kThreads) k_adam_step(const __grid_constant__ AdamList L, const float* __restrict__ lr_p, float beta1, float beta2,
                                                         float eps, const float* __restrict__ scale, const float* __restrict__ found_inf,
-                                                        const int32_t* __restrict__ step, const __grid_constant__ PeerShadow PS) {
+                                                        const int32_t* __restrict__ step, const __grid_constant__ PeerShadow PS,
+                                                        const __grid_constant__ PeerGrad PG) {
     pdl_sync();
     const bool bad = found_inf != nullptr && *found_inf != 0.0f;
     __shared__ float s_step_size, s_rsqrt_bc2, s_inv_scale;
@@ -137,7 +184,10 @@ __global__ void __launch_bounds__(kThreads) k_adam_step(const __grid_constant__ 
         const bool full = i + 4 <= T.n;
         if (!skip) {
             float g[4], p[4], m[4], v[4];
-            load_grad4(T, i, T.n, g);
+            if constexpr (PULL > 0) {
+                if (ti == PS.tensor) pull_table4<PULL>(PG, i, g);     // the shard is a multiple of 8 elements: never a partial vector
+                else pull_tail4<PULL>(PG, T, i, g);
+            } else load_grad4(T, i, T.n, g);
             if (full) {
                 // the fp32 master values and moments stream through once per step (294 MB against a 126 MB L2): evict-first loads and
                 // stores, so that what the NEXT step gathers from / scatters into -- the fp16 shadow and the zeroed fp16 gradient written
@@ -255,7 +305,7 @@ FOC_API int foc_adam_step(const FocAdamTensor* tensors, int count, const float* 
     if (int rc = make_list(tensors, count, L)) return rc;
     const uint32_t adam_grid = L.block_start[kMaxTensors];
     PeerShadow ps{};
-    foc::launch(k_adam_step<false>, adam_grid, kThreads, 0, reinterpret_cast<cudaStream_t>(stream), L, lr, beta1, beta2, eps, scale, found_inf, step, ps);
+    foc::launch(k_adam_step<false, 0>, adam_grid, kThreads, 0, reinterpret_cast<cudaStream_t>(stream), L, lr, beta1, beta2, eps, scale, found_inf, step, ps, PeerGrad{});
     FOC_LAUNCH_CHECK(); return 0;
 }
 
@@ -271,8 +321,49 @@ FOC_API int foc_adam_step_peers(const FocAdamTensor* tensors, int count, const f
         if (peer_shadow16[r] == nullptr || (reinterpret_cast<uintptr_t>(peer_shadow16[r]) & 15u)) return FOC_ERR_UNSUPPORTED;
         ps.base[r] = peer_shadow16[r];
     }
-    foc::launch(k_adam_step<true>, L.block_start[kMaxTensors], kThreads, 0, reinterpret_cast<cudaStream_t>(stream), L, lr, beta1, beta2, eps, scale,
-                found_inf, step, ps);
+    foc::launch(k_adam_step<true, 0>, L.block_start[kMaxTensors], kThreads, 0, reinterpret_cast<cudaStream_t>(stream), L, lr, beta1, beta2, eps, scale,
+                found_inf, step, ps, PeerGrad{});
+    FOC_LAUNCH_CHECK(); return 0;
+}
+
+template <int W>
+static void launch_dp(const AdamList& L, const float* lr, float beta1, float beta2, float eps, const float* scale, const float* found_inf,
+                      const int32_t* step, const PeerShadow& ps, const PeerGrad& pg, void* stream) {
+    foc::launch(k_adam_step<true, W>, L.block_start[kMaxTensors], kThreads, 0, reinterpret_cast<cudaStream_t>(stream), L, lr, beta1, beta2, eps, scale,
+                found_inf, step, ps, pg);
+}
+
+FOC_API int foc_adam_step_dp(const FocAdamTensor* tensors, int count, const float* lr, float beta1, float beta2, float eps,
+                             const float* scale, const float* found_inf, const int32_t* step, int peer_tensor, const FocDpGrads* grads,
+                             uint16_t* const* peer_shadow16, void* stream) {
+    AdamList L;
+    if (int rc = make_list(tensors, count, L)) return rc;
+    if (grads == nullptr || grads->world < 1 || grads->world > FOC_MAX_PEERS || grads->rank < 0 || grads->rank >= grads->world ||
+        peer_tensor < 0 || peer_tensor >= count || peer_shadow16 == nullptr) return FOC_ERR_UNSUPPORTED;
+    if (tensors[peer_tensor].n % 8u) return FOC_ERR_UNSUPPORTED;
+    PeerShadow ps{};
+    PeerGrad pg{};
+    ps.world = grads->world; ps.tensor = peer_tensor; pg.rank = grads->rank;
+    for (int r = 0; r < grads->world; ++r) {
+        if (peer_shadow16[r] == nullptr || grads->grad16[r] == nullptr || grads->tail[r] == nullptr) return FOC_ERR_UNSUPPORTED;
+        if ((reinterpret_cast<uintptr_t>(peer_shadow16[r]) | reinterpret_cast<uintptr_t>(grads->grad16[r]) | reinterpret_cast<uintptr_t>(grads->tail[r])) & 15u) return FOC_ERR_UNSUPPORTED;
+        ps.base[r] = peer_shadow16[r]; pg.g16[r] = grads->grad16[r]; pg.tail[r] = grads->tail[r];
+    }
+    for (int i = 0; i < count; ++i) {                                   // every tensor but the table takes its gradient from the fp32 tails
+        if (i == peer_tensor) continue;
+        const float* g = static_cast<const float*>(tensors[i].grad);
+        if (g == nullptr || tensors[i].grad_dtype != 0 || g < pg.tail[pg.rank] || ((g - pg.tail[pg.rank]) & 3)) return FOC_ERR_UNSUPPORTED;
+    }
+    switch (grads->world) {
+        case 1: launch_dp<1>(L, lr, beta1, beta2, eps, scale, found_inf, step, ps, pg, stream); break;
+        case 2: launch_dp<2>(L, lr, beta1, beta2, eps, scale, found_inf, step, ps, pg, stream); break;
+        case 3: launch_dp<3>(L, lr, beta1, beta2, eps, scale, found_inf, step, ps, pg, stream); break;
+        case 4: launch_dp<4>(L, lr, beta1, beta2, eps, scale, found_inf, step, ps, pg, stream); break;
+        case 5: launch_dp<5>(L, lr, beta1, beta2, eps, scale, found_inf, step, ps, pg, stream); break;
+        case 6: launch_dp<6>(L, lr, beta1, beta2, eps, scale, found_inf, step, ps, pg, stream); break;
+        case 7: launch_dp<7>(L, lr, beta1, beta2, eps, scale, found_inf, step, ps, pg, stream); break;
+        default: launch_dp<8>(L, lr, beta1, beta2, eps, scale, found_inf, step, ps, pg, stream); break;
+    }
     FOC_LAUNCH_CHECK(); return 0;
 }
 

@@ -49,8 +49,8 @@ __device__ __forceinline__ uint4 ld_peer16(const void* p) {
 __global__ void __launch_bounds__(32) k_peer_barrier(const __grid_constant__ FocPeerGroup g, float* __restrict__ found_inf) {
     const int lane = threadIdx.x;
     const uint32_t epoch = g.state[0] + 1;
-    const uint32_t bit = g.state[1];
     const bool exch = found_inf != nullptr;
+    const uint32_t bit = g.state[1] | ((exch && *found_inf != 0.0f) ? 1u : 0u);     // k_dp_reduce's flag, or a local foc_adam_nonfinite result
     __syncwarp();
     __threadfence_system();
     uint32_t peer_bit = 0;

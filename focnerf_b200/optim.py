@@ -184,6 +184,11 @@ class FocDpReduce(ctypes.Structure):
                 ("reduced_tail", ctypes.c_void_p), ("inf_flag", ctypes.c_void_p), ("shard_blocks", ctypes.c_uint32)]
 
 
+class FocDpGrads(ctypes.Structure):
+    """include/foc_b200.h: struct FocDpGrads"""
+    _fields_ = [("world", ctypes.c_int32), ("rank", ctypes.c_int32), ("grad16", ctypes.c_void_p * 8), ("tail", ctypes.c_void_p * 8)]
+
+
 class PeerAdam(ScaledAdam):
     """ScaledAdam for data-parallel training on one NVSwitch node, with the gradient exchange fused into the optimiser over
     peer memory instead of an NCCL all-reduce in front of it (csrc/peer.cu has the protocol):
@@ -240,24 +245,35 @@ class PeerAdam(ScaledAdam):
             self.reduced.data_ptr(), (ctypes.c_void_p * 8)(*[a.address(r, self._off_tail) for r in range(self.world)]), self.tail_n,
             self.reduced_tail.data_ptr(), a.state.data_ptr() + 4, 0)
         self._peer_shadow = (ctypes.c_void_p * 8)(*[a.address(r, self._off_shadow + 2 * self.shard_start) for r in range(self.world)])
+        # exchange inside the sweep (foc_adam_step_dp): pull -> fp32 mean -> Adam -> push in one pass over the shard, two barriers.
+        # FOC_DP_FUSED=0 keeps the three-barrier protocol (foc_dp_reduce + foc_adam_step_peers), bit-identical results.
+        import os
+        self.fused_exchange = os.environ.get("FOC_DP_FUSED", "1") == "1" and (self.world - 1) * per < n      # same answer on every rank
+        self._dp_grads = FocDpGrads(self.world, self.rank,
+                                    (ctypes.c_void_p * 8)(*[a.address(r, self._off_grad + 2 * self.shard_start) for r in range(self.world)]),
+                                    (ctypes.c_void_p * 8)(*[a.address(r, self._off_tail) for r in range(self.world)]))
         dist.barrier(group=group)
 
     def grad_tensors(self):
         return []                      # nothing for an NCCL all-reduce: step() exchanges the gradients itself
 
-    def _descriptors(self):
+    def _descriptors(self, pull=False):
+        """pull=True (foc_adam_step_dp): the gradients are the ranks' own buffers -- the table row names the local fp16 shard, the
+        tail rows their slice of the local staged tail; the kernel reads the same offsets on every rank."""
         rows = []
         s, n = self.shard_start, self.shard_n
         ti = [i for i, p in enumerate(self.params) if p is self.table][0]
         if n > 0:
             flat = lambda t: t.view(-1)[s:s + n]
+            g = (self.grad16.view(-1)[s:s + n].data_ptr(), 1) if pull else (self.reduced.data_ptr(), 0)
             rows.append(FocAdamTensor(flat(self.table.data).data_ptr(), flat(self.exp_avg[ti]).data_ptr(), flat(self.exp_avg_sq[ti]).data_ptr(),
-                                      self.reduced.data_ptr(), 0, n, 0, 0))
+                                      g[0], 0, n, g[1], 0))
         for p, off in zip(self.tail, self.tail_off):
             i = [k for k, q in enumerate(self.params) if q is p][0]
             s16 = self._side.get(id(p), (None, None))[1]
             rows.append(FocAdamTensor(p.data_ptr(), self.exp_avg[i].data_ptr(), self.exp_avg_sq[i].data_ptr(),
-                                      self.reduced_tail.data_ptr() + 4 * off, 0 if s16 is None else s16.data_ptr(), p.numel(), 0, 0))
+                                      (self.tail_grad if pull else self.reduced_tail).data_ptr() + 4 * off, 0 if s16 is None else s16.data_ptr(),
+                                      p.numel(), 0, 0))
         return rows
 
     @torch.no_grad()
@@ -271,15 +287,30 @@ class PeerAdam(ScaledAdam):
                 if g16 is not None:
                     g16.zero_()                                # consumed: the side buffers ACCUMULATE between steps (like .grad)
         fi = None if self.scale is None else self.found_inf
+        b1, b2 = self.betas
+        sc = None if self.scale is None else self.scale.data_ptr()
+        fip = None if fi is None else fi.data_ptr()
+        if self.fused_exchange:
+            if fi is not None:                                 # this rank's own gradients (whole fp16 table + staged tail): one local pass
+                own = (FocAdamTensor * 2)(FocAdamTensor(0, 0, 0, self.grad16.data_ptr(), 0, self.grad16.numel(), 1, 0),
+                                          FocAdamTensor(0, 0, 0, self.tail_grad.data_ptr(), 0, max(self.tail_n, 4), 0, 0))
+                check(l.foc_adam_nonfinite(ctypes.cast(own, ctypes.c_void_p), 2, fip, st), "adam_nonfinite")
+            self.arena.barrier(fi)                             # every rank's gradients are complete; non-finite flags exchanged
+            rows = self._descriptors(pull=True)
+            arr = (FocAdamTensor * len(rows))(*rows)
+            check(l.foc_adam_step_dp(ctypes.cast(arr, ctypes.c_void_p), len(rows), self.lr.data_ptr(), b1, b2, self.eps, sc, fip,
+                                     self.step_count.data_ptr(), 0, ctypes.byref(self._dp_grads), ctypes.cast(self._peer_shadow, ctypes.c_void_p), st),
+                  "adam_step_dp")
+            self.arena.barrier()                               # every shard of the fp16 table has arrived, every rank has pulled
+            self._grad_span.zero_()
+            self._scaler_update(l, sc, fip, st)
+            return
         self.arena.barrier()                                   # every rank's gradients are complete
         check(l.foc_dp_reduce(ctypes.byref(self._reduce_args), st), "dp_reduce")
         self.arena.barrier(fi)                                 # every rank has pulled what it needs; non-finite flags exchanged
         self._grad_span.zero_()
         rows = self._descriptors()
         arr = (FocAdamTensor * len(rows))(*rows)
-        b1, b2 = self.betas
-        sc = None if self.scale is None else self.scale.data_ptr()
-        fip = None if fi is None else fi.data_ptr()
         if self.shard_n > 0:
             check(l.foc_adam_step_peers(ctypes.cast(arr, ctypes.c_void_p), len(rows), self.lr.data_ptr(), b1, b2, self.eps, sc, fip,
                                         self.step_count.data_ptr(), 0, self.world, ctypes.cast(self._peer_shadow, ctypes.c_void_p), st), "adam_step_peers")

@@ -11,6 +11,10 @@ from . import raymarching
 from .network import NeRFNetwork
 
 
+def _pad128(n):
+    return max(128, -(-int(n) // 128) * 128)
+
+
 class Trainer:
     """Defaults follow the reference's recipe: lr 1e-3 (main_nerf.py:26), Adam(betas=(0.9, 0.99), eps=1e-15) (main_nerf.py:472),
     density_thresh 10, min_near 0.2, max_steps 1024, density-grid refresh every update_extra_interval = 16 steps (main_nerf.py:33),
@@ -48,6 +52,8 @@ class Trainer:
         self.fused, self.use_graph = fused, use_graph
         self._graph = None
         self._refresh_graph, self._refresh_buf = None, None
+        self._render_cap = {}                           # rays per frame -> sample-buffer capacity learnt from the previous frame
+        self.render_overflows = 0                       # frames the speculative single pass had to render again with exact sizes
         self.capture_count = 0                          # how many times the step was (re-)captured (bench.py reports it for the timed region)
         # pipeline=True (fused optimiser + graph only, opt-in): the optimiser sweep of step i-1 runs on a side stream next to
         # the march of step i (the march reads rays + bitfield, never the parameters).  `_pending` = a backward has left
@@ -490,8 +496,50 @@ class Trainer:
 
     # ------------------------------------------------------------------------------------------------ inference
     @torch.no_grad()
+    def _render_rows_ok(self):
+        """The speculative single pass needs every consumer of the sample buffers to honour the device-side row count."""
+        import os
+        m = self.model
+        return (self.fused and self.fp16 and getattr(m, "_field_fused", False) and getattr(m.sigma_net, "_shadow16", None) is not None
+                and getattr(m.color_net, "_shadow16", None) is not None and getattr(m.encoder, "_shadow16", None) is not None
+                and os.environ.get("FOC_RENDER_SPECULATIVE", "1") == "1")
+
+    def _render_size(self, N, total):
+        """Capacity for the next N-ray frame: this frame's total + 12.5 %, in 16 384-row quanta; kept while the total stays inside
+        [cap / 1.5, cap / 1.03] so that a slowly moving camera does not change the allocation every frame."""
+        cap = self._render_cap.get(N)
+        if cap is None or total * 1.03 > cap or total * 1.5 < cap:
+            self._render_cap[N] = max(16384, -(-int(total * 1.125 + 128) // 16384) * 16384)
+
+    def render_frames(self, frames, bg_color=1.0, T_thresh=1e-4, exchange=None):
+        """A camera path: `frames` = [(rays_o, rays_d), ...] -> [(image, depth, weights_sum), ...] with NO host read between frames (the
+        reference's test loop, legacy/nerf/utils.py test(), pays ~45 reads per frame).  Every frame is enqueued into buffers sized from
+        the previous one; the exact totals of all frames come back in one read at the end and any frame whose samples did not fit is
+        rendered again with exact sizes.  With an `exchange` the frames are copies (its two buffers alternate)."""
+        outs, checks = [], []
+        for o, d in frames:
+            pend = []
+            out = self.render(o, d, bg_color, T_thresh, mode="single_pass", exchange=exchange, _defer=pend)
+            if exchange is not None:
+                out = tuple(t.clone() for t in out)
+            outs.append(out)
+            checks.append(pend[0] if pend else None)
+        live = [i for i, c in enumerate(checks) if c is not None]
+        if live:
+            totals = torch.cat([checks[i][0] for i in live]).tolist()              # the one host read
+            for i, t in zip(live, totals):
+                N = frames[i][0].reshape(-1, 3).shape[0]
+                if _pad128(t) > checks[i][1]:
+                    self.render_overflows += 1
+                    self._render_cap.pop(N, None)
+                    out = self.render(frames[i][0], frames[i][1], bg_color, T_thresh, mode="single_pass", exchange=exchange)
+                    outs[i] = tuple(x.clone() for x in out) if exchange is not None else out
+                elif i == live[-1]:
+                    self._render_size(N, t)
+        return outs
+
     def render(self, rays_o, rays_d, bg_color=1.0, T_thresh=1e-4, device_compaction=True, mode="single_pass", exchange=None,
-               windows=(48, 976)):
+               windows=(48, 976), _defer=None):
         """run_cuda, inference branch (legacy/nerf/renderer.py:331-372).
 
         mode="loop": the reference's caller-owned loop (march_rays -> field -> composite_rays, n_step = min(N // n_alive, 8)).
@@ -542,10 +590,53 @@ class Trainer:
                 start += width
             return finish(wm.image, wm.depth, wm.weights_sum, False)
         if mode == "single_pass":
+            field = self.model.forward_fused if self.fused and self.fp16 else self.model
+            cap = self._render_cap.get(N) if self._render_rows_ok() else None
+            if cap is not None:
+                # Speculative sizing: the whole frame is enqueued into buffers of the PREVIOUS frame's size (+12.5 %) with the row count
+                # published on the device (march_rays_train_rows -> _lib.valid_rows consumers), and the one 4-byte read of the exact total
+                # happens AFTER the last launch -- the GPU never waits for the host inside a frame.  A total beyond the capacity (rays
+                # dropped exactly as raymarching.cu:415-416 drops them) re-renders the frame below with exact sizes, so the result never
+                # depends on the guess.  defer=True hands the check to the caller (render_frames: one read for a whole camera path).
+                from ._lib import set_valid_rows
+                counter = torch.zeros(2, dtype=torch.int32, device=dev)
+                rows = torch.zeros(1, dtype=torch.int32, device=dev)
+                prev = set_valid_rows(rows)
+                try:
+                    xyzs, dirs, deltas, rays = raymarching.march_rays_train(
+                        rays_o, rays_d, self.bound, self.density_bitfield, self.cascade, self.grid_size, nears, fars, counter, cap,
+                        False, 128, False, self.dt_gamma, self.max_steps)
+                    with torch.autocast("cuda", dtype=torch.float16, enabled=self.fp16):
+                        sigmas, rgbs = field(xyzs, dirs)
+                finally:
+                    set_valid_rows(prev)
+                with torch.autocast("cuda", dtype=torch.float16, enabled=self.fp16):
+                    weights_sum, depth, image = raymarching.composite_rays_train(sigmas, rgbs, deltas, rays, T_thresh)
+                out = finish(image.float().contiguous(), depth.float().contiguous(), weights_sum.float().contiguous(), True)
+                total = counter[:1]
+                if exchange is not None and exchange.world > 1:           # every rank must take the same decision: the frame barrier is collective
+                    import torch.distributed as dist
+                    total = total.clone()
+                    dist.all_reduce(total, op=dist.ReduceOp.MAX, group=exchange.arena.group)
+                if _defer is not None:
+                    _defer.append((total, cap))
+                    return out
+                t = int(total.item())
+                self._render_size(N, t)
+                if _pad128(t) <= cap:
+                    return out
+                self.render_overflows += 1                              # fall through: exact sizes, one read in the middle
             xyzs, dirs, deltas, rays = raymarching.march_rays_all(rays_o, rays_d, self.bound, self.density_bitfield, self.cascade,
                                                                   self.grid_size, nears, fars, 128, self.dt_gamma, self.max_steps)
+            if exchange is not None and exchange.world > 1 and self._render_rows_ok():
+                import torch.distributed as dist
+                m = torch.tensor([xyzs.shape[0]], dtype=torch.int32, device=dev)
+                dist.all_reduce(m, op=dist.ReduceOp.MAX, group=exchange.arena.group)
+                self._render_size(N, int(m.item()))
+            else:
+                self._render_size(N, xyzs.shape[0])
             with torch.autocast("cuda", dtype=torch.float16, enabled=self.fp16):
-                sigmas, rgbs = (self.model.forward_fused if self.fused and self.fp16 else self.model)(xyzs, dirs)
+                sigmas, rgbs = field(xyzs, dirs)
                 weights_sum, depth, image = raymarching.composite_rays_train(sigmas, rgbs, deltas, rays, T_thresh)
             # the training compositor measures depth from the first sample's start (raymarching.cu:545 starts t at 0), the
             # inference one from the ray origin (raymarching.cu:858 starts at rays_t): the epilogue adds sum_i w_i * near

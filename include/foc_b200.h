@@ -349,8 +349,8 @@ typedef struct FocPeerGroup {
     uint32_t *flags[FOC_MAX_PEERS]; /* every rank's signal pad (>= 24 uint32, zero-initialised), [rank] = the local one */
     uint32_t *state;                /* local: [0] epoch, [1] non-finite flag of foc_dp_reduce, [2] sticky status (1 = barrier timeout) */
 } FocPeerGroup;
-/* All ranks of the group meet; found_inf != NULL additionally ORs the ranks' state[1] flags into *found_inf (sets 1.0f,
- * never clears) and resets state[1].  Gives up after ~2 s without progress and sets state[2] instead of hanging. */
+/* All ranks of the group meet; found_inf != NULL additionally ORs the ranks' flags (state[1], or a *found_inf that is already non-zero
+ * on entry: the result of a local foc_adam_nonfinite) into *found_inf (sets 1.0f, never clears) and resets state[1].  Gives up after ~2 s without progress and sets state[2] instead of hanging. */
 int foc_peer_barrier(const FocPeerGroup *group, float *found_inf, void *stream);
 typedef struct FocDpReduce {
     int32_t world, rank;
@@ -369,6 +369,22 @@ int foc_dp_reduce(const FocDpReduce *args, void *stream);
 int foc_adam_step_peers(const FocAdamTensor *tensors, int count, const float *lr, float beta1, float beta2, float eps,
                         const float *scale, const float *found_inf, const int32_t *step, int peer_tensor, int world,
                         uint16_t *const *peer_shadow16, void *stream);
+/* The exchange INSIDE the sweep (no reference counterpart; replaces foc_dp_reduce + foc_adam_step_peers and one of the three barriers):
+ * tensor `peer_tensor` (this rank's shard of the table: param / exp_avg / exp_avg_sq point at the shard, n = its length, a multiple of
+ * 8) takes as gradient the mean over the ranks of grads->grad16[r][i] (fp16, every pointer offset to the shard), summed in fp32 in rank
+ * order; every other tensor's `grad` must point into grads->tail[rank] (fp32, 4-float aligned, rows zero-padded to 4) and takes the mean
+ * of the same offset in every rank's tail.  Updated fp16 copies of the shard go to peer_shadow16[r] as in foc_adam_step_peers.
+ * Protocol per step: local foc_adam_nonfinite over the rank's own gradients -> foc_peer_barrier(found_inf) [gradients complete, flags
+ * exchanged: a sum of <= 8 finite fp16 values is finite, so "any rank non-finite" == "mean non-finite"] -> foc_adam_step_dp ->
+ * foc_peer_barrier [shards delivered, everybody has pulled] -> zero the gradients. */
+typedef struct FocDpGrads {
+    int32_t world, rank;
+    const uint16_t *grad16[FOC_MAX_PEERS];
+    const float *tail[FOC_MAX_PEERS];
+} FocDpGrads;
+int foc_adam_step_dp(const FocAdamTensor *tensors, int count, const float *lr, float beta1, float beta2, float eps,
+                     const float *scale, const float *found_inf, const int32_t *step, int peer_tensor, const FocDpGrads *grads,
+                     uint16_t *const *peer_shadow16, void *stream);
 
 /* Epilogue of an inference render (legacy/nerf/renderer.py:369-372), one launch: image + (1 - weights_sum) * bg, depth
  * normalised to [near, far] (depth_from_first_sample != 0: `depth` came from the training compositor, which measures from

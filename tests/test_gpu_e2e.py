@@ -61,6 +61,43 @@ def test_render_single_pass_matches_loop():
         assert torch.allclose(x, y, atol=tol, rtol=0), float((x - y).abs().max())
 
 
+def test_render_speculative_sizing_is_exact():
+    """Trainer.render(single_pass) sizes the sample buffers from the previous frame and reads the exact total only after the frame
+    is enqueued; render_frames does one read for a whole path.  Both must give the bits of the exactly-sized frame, also when the
+    guess was too small (the frame is then rendered again)."""
+    scene, tr = _trainer()
+    for it in range(32):
+        o, d = cases.camera_rays(4096, 500 + it)
+        o, d = torch.from_numpy(o).cuda(), torch.from_numpy(d).cuda()
+        tr.train_step(o, d, scene.render_gt(o, d))
+    assert tr._render_rows_ok()
+    o, d = cases.camera_rays(30000, 9)
+    o, d = torch.from_numpy(o).cuda(), torch.from_numpy(d).cuda()
+    o2, d2 = cases.camera_rays(30000, 10)
+    o2, d2 = torch.from_numpy(o2).cuda(), torch.from_numpy(d2).cuda()
+    N = o.shape[0]
+    exact = [t.clone() for t in tr.render(o, d)]                   # first frame of this size: no capacity yet -> exact path
+    exact2 = None
+    assert N in tr._render_cap and tr.render_overflows == 0
+    same = lambda a, b: all(torch.equal(torch.nan_to_num(x), torch.nan_to_num(y)) for x, y in zip(a, b))
+    assert same(tr.render(o, d), exact)                            # speculative path, the guess fits
+    assert tr.render_overflows == 0
+    tr._render_cap[N] = 16384                                      # far too small: most rays dropped by the march -> second, exact pass
+    assert same(tr.render(o, d), exact)
+    assert tr.render_overflows == 1 and tr._render_cap[N] > 16384
+    import os
+    os.environ["FOC_RENDER_SPECULATIVE"] = "0"
+    try:
+        exact2 = [t.clone() for t in tr.render(o2, d2)]
+    finally:
+        del os.environ["FOC_RENDER_SPECULATIVE"]
+    outs = tr.render_frames([(o, d), (o2, d2), (o, d)])
+    assert same(outs[0], exact) and same(outs[1], exact2) and same(outs[2], exact)
+    tr._render_cap[N] = 16384
+    outs = tr.render_frames([(o, d), (o2, d2)])                    # both overflow, both re-rendered after the single read
+    assert same(outs[0], exact) and same(outs[1], exact2) and tr.render_overflows >= 3
+
+
 @pytest.mark.parametrize("windows", [(48, 976), (8, 24, 64, 928), (1024,)])
 def test_render_windowed_matches_loop(windows):
     """Depth-windowed render (recorded march, K10 recurrence per window, alive flags) reproduces the reference-style loop."""
