@@ -15,3 +15,5 @@ def install_aliases():
     callers (nerf/renderer.py, nerf/network_ff.py, COMBINED.py, editable.py) run unchanged on top of it."""
     for name in _ALIASES:
         sys.modules[name] = importlib.import_module(f"{__name__}.{name}")
+    if "tinycudann" not in sys.modules:             # a real tiny-cuda-nn, when installed, is left alone
+        sys.modules["tinycudann"] = importlib.import_module(f"{__name__}.tinycudann")

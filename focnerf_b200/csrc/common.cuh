@@ -115,4 +115,17 @@ __device__ __forceinline__ uint32_t warp_incl_sum_u32(uint32_t v, int lane) {
     return v;
 }
 
+// mlp_generic.cu: the FFMLP shapes outside the tensor-core kernels' (hidden 64, input 32 / 64)
+bool mlp_generic_shape_ok(uint32_t B, uint32_t input_dim, uint32_t output_dim, uint32_t hidden_dim, uint32_t num_layers);
+size_t mlp_generic_num_params(uint32_t input_dim, uint32_t hidden_dim, uint32_t num_layers);
+size_t mlp_generic_scratch_bytes(uint32_t B, uint32_t input_dim, uint32_t hidden_dim, uint32_t num_layers);
+int mlp_generic_forward(const uint16_t* inputs, const uint16_t* weights, uint32_t B, uint32_t input_dim, uint32_t output_dim, uint32_t hidden_dim,
+                        uint32_t num_layers, uint32_t activation, uint32_t output_activation, uint16_t* forward_buffer, uint16_t* outputs, cudaStream_t st);
+int mlp_generic_backward(const uint16_t* grad, const uint16_t* inputs, const uint16_t* weights, const uint16_t* forward_buffer, uint32_t B,
+                         uint32_t input_dim, uint32_t output_dim, uint32_t hidden_dim, uint32_t num_layers, uint32_t activation, int calc_grad_inputs,
+                         uint16_t* backward_buffer, uint16_t* grad_inputs, uint16_t* grad_weights, int accumulate, void* scratch, cudaStream_t st);
+int mlp_generic_finish(const void* scratch, uint32_t input_dim, uint32_t hidden_dim, uint32_t num_layers, uint16_t* grad_weights, int accumulate, cudaStream_t st);
+// num_layers == 1 (one hidden layer: tcnn's n_hidden_layers = 1; the reference's FFMLP module asserts >= 2) also goes to the generic kernels
+inline bool mlp_tensor_shape(uint32_t input_dim, uint32_t hidden_dim, uint32_t num_layers) { return hidden_dim == 64 && (input_dim == 32 || input_dim == 64) && num_layers >= 2; }
+
 }  // namespace foc

@@ -439,6 +439,8 @@ int launch_bwd(const uint16_t* grad, const uint16_t* inputs, const uint16_t* wei
 }  // namespace
 
 FOC_API size_t foc_ffmlp_backward_scratch_bytes(uint32_t B, uint32_t input_dim, uint32_t hidden_dim, uint32_t num_layers) {
+    if (!foc::mlp_tensor_shape(input_dim, hidden_dim, num_layers))
+        return foc::mlp_generic_shape_ok(B, input_dim, 16, hidden_dim, num_layers) ? foc::mlp_generic_scratch_bytes(B, input_dim, hidden_dim, num_layers) : 0;
     if (hidden_dim != (uint32_t)kHidden || B % kTile != 0 || num_layers < 1) return 0;
     return (size_t)bwd_grid(B) * num_params_of(input_dim, num_layers) * sizeof(float);
 }
@@ -449,6 +451,8 @@ FOC_API size_t foc_ffmlp_backward_scratch_bytes(uint32_t B, uint32_t input_dim, 
 FOC_API int foc_ffmlp_wgrad_finish(const void* scratch, uint32_t B, uint32_t input_dim, uint32_t hidden_dim, uint32_t num_layers,
                                    uint16_t* grad_weights, void* stream) {
     if (B == 0) return 0;
+    if (!foc::mlp_tensor_shape(input_dim, hidden_dim, num_layers) && foc::mlp_generic_shape_ok(B, input_dim, 16, hidden_dim, num_layers) && scratch && grad_weights)
+        return foc::mlp_generic_finish(scratch, input_dim, hidden_dim, num_layers, grad_weights, 0, reinterpret_cast<cudaStream_t>(stream));
     if (hidden_dim != (uint32_t)kHidden || B % kTile != 0 || num_layers < 1 || !scratch || !grad_weights) return FOC_ERR_UNSUPPORTED;
     const uint32_t n = num_params_of(input_dim, num_layers);
     foc::launch(k_mlp_wgrad_finish, ceil_div(n, 32), 256, 0, reinterpret_cast<cudaStream_t>(stream), static_cast<const float*>(scratch), bwd_grid(B), n,
@@ -461,6 +465,8 @@ FOC_API int foc_ffmlp_wgrad_finish(const void* scratch, uint32_t B, uint32_t inp
 FOC_API int foc_ffmlp_wgrad_accumulate(const void* scratch, uint32_t B, uint32_t input_dim, uint32_t hidden_dim, uint32_t num_layers,
                                        uint16_t* grad_weights, void* stream) {
     if (B == 0) return 0;
+    if (!foc::mlp_tensor_shape(input_dim, hidden_dim, num_layers) && foc::mlp_generic_shape_ok(B, input_dim, 16, hidden_dim, num_layers) && scratch && grad_weights)
+        return foc::mlp_generic_finish(scratch, input_dim, hidden_dim, num_layers, grad_weights, 1, reinterpret_cast<cudaStream_t>(stream));
     if (hidden_dim != (uint32_t)kHidden || B % kTile != 0 || num_layers < 1 || !scratch || !grad_weights) return FOC_ERR_UNSUPPORTED;
     const uint32_t n = num_params_of(input_dim, num_layers);
     foc::launch(k_mlp_wgrad_finish, ceil_div(n, 32), 256, 0, reinterpret_cast<cudaStream_t>(stream), static_cast<const float*>(scratch), bwd_grid(B), n,
@@ -474,6 +480,11 @@ FOC_API int foc_ffmlp_backward(const uint16_t* grad, const uint16_t* inputs, con
                                uint16_t* grad_inputs, uint16_t* grad_weights, void* scratch, void* stream) {
     if (B == 0) return 0;
     // output activation is always `none` in the reference module (ffmlp.py:108); activation 2 (sine) has no stored-value derivative
+    if (!foc::mlp_tensor_shape(input_dim, hidden_dim, num_layers)) {
+        if (output_dim != (uint32_t)kOutPad || output_activation != 6) return FOC_ERR_UNSUPPORTED;
+        return foc::mlp_generic_backward(grad, inputs, weights, forward_buffer, B, input_dim, output_dim, hidden_dim, num_layers, activation, calc_grad_inputs,
+                                         backward_buffer, grad_inputs, grad_weights, 0, scratch, reinterpret_cast<cudaStream_t>(stream));
+    }
     if (hidden_dim != (uint32_t)kHidden || output_dim != (uint32_t)kOutPad || num_layers < 1 || num_layers > (uint32_t)kMaxLayers ||
         B % kTile != 0 || output_activation != 6 || activation == 2 || !scratch) return FOC_ERR_UNSUPPORTED;
     cudaStream_t st = reinterpret_cast<cudaStream_t>(stream);

@@ -248,7 +248,11 @@ FOC_API int foc_ffmlp_forward(const uint16_t* inputs, const uint16_t* weights, u
                               uint32_t output_dim, uint32_t hidden_dim, uint32_t num_layers, uint32_t activation,
                               uint32_t output_activation, uint16_t* forward_buffer, uint16_t* outputs, void* stream) {
     if (B == 0) return 0;
-    // shapes of the FOC field networks (network_ff.py:31-49); the reference additionally allows hidden 16/32/128/256
+    // the shapes of the FOC field networks (network_ff.py:31-49) take the tcgen05 kernel; whatever else ffmlp.py:99-123 allows (hidden
+    // 16 / 32 / 128 / 256, input_dim = 16 m) goes to the CUDA-core kernels of mlp_generic.cu
+    if (!foc::mlp_tensor_shape(input_dim, hidden_dim, num_layers))
+        return foc::mlp_generic_forward(inputs, weights, B, input_dim, output_dim, hidden_dim, num_layers, activation, output_activation, forward_buffer,
+                                        outputs, reinterpret_cast<cudaStream_t>(stream));
     if (hidden_dim != (uint32_t)kHidden || output_dim > (uint32_t)kOutPad || num_layers < 1 || num_layers > (uint32_t)kMaxLayers ||
         B % kTile != 0) return FOC_ERR_UNSUPPORTED;
     cudaStream_t st = reinterpret_cast<cudaStream_t>(stream);

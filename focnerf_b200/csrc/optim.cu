@@ -239,7 +239,10 @@ __global__ void __launch_bounds__(kThreads) k_adam_step(const __grid_constant__ 
         }
     }
     }
-    if (PEERS) __threadfence_system();             // the pushed fp16 copies must be visible to the peers before the barrier that follows
+    // the pushed fp16 copies must be visible to the peers before the barrier that follows: ONE system-scope fence per CTA (thread 0, after
+    // a CTA barrier -- fence cumulativity covers the other threads' stores, the pattern of a cooperative-groups grid sync) instead of one
+    // per thread: thousands of concurrent MEMBAR.SYS, each waiting for NVLink acknowledgements, kept the CTA slots occupied
+    if (PEERS) { __syncthreads(); if (threadIdx.x == 0) __threadfence_system(); }
 }
 
 // torch.amp.GradScaler.update() (torch/amp/grad_scaler.py, amp_update_scale_cuda_kernel) + the step counter

@@ -161,7 +161,7 @@ __global__ void __launch_bounds__(kDeal) k_render_finish(const float* __restrict
             else for (uint32_t k = q * 4; k < valid * 5; ++k) dst[k] = rows[k];
         }
     }
-    if (o.world > 1) __threadfence_system();
+    if (o.world > 1) { __syncthreads(); if (threadIdx.x == 0) __threadfence_system(); }      // one fence per CTA (see k_adam_step)
 }
 
 inline bool valid_group(const FocPeerGroup* g) {

@@ -6,8 +6,9 @@ that always appends 1..128 zero rows (ffmlp.py:157-159), `custom_fwd(cast_inputs
 `_backend` method names (ffmlp/src/bindings.cpp:5-11).  Not imported: `turtle` (ffmlp.py:2, needs tkinter).
 
 Differences, on purpose: `backward_buffer` is not materialised (the kernel keeps dL/dact in shared memory and reduces
-the weight gradients itself); `allocate_splitk/free_splitk` are no-ops; only hidden_dim == 64 and input_dim in
-{32, 64} are implemented by the sm_100a kernels (the FOC field networks) -- other shapes raise RuntimeError.
+the weight gradients itself); `allocate_splitk/free_splitk` are no-ops.  hidden_dim == 64 with input_dim in {32, 64} (the FOC
+field networks) runs on the tcgen05 kernels; every other shape the constructor accepts (hidden 16 / 32 / 128 / 256, input_dim = 16 m)
+runs on the CUDA-core kernels of csrc/mlp_generic.cu, which do write `backward_buffer`.
 """
 import math
 

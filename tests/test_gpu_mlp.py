@@ -85,11 +85,77 @@ def test_ffmlp_module_matches_reference_wrapper_semantics():
     assert torch.equal(y2, y.detach())
 
 
-def test_unsupported_shapes_raise():
+def _mlp_run(be, c, hidden, act=0):
+    """runners.mlp_fwd_bwd for any hidden width / activation."""
+    T = runners.T
+    x, w, g = T(c["inputs"]), T(c["weights"]), T(c["grad"])
+    B, IN, L = x.shape[0], c["input_dim"], c["num_layers"]
+    fb = torch.empty(L, B, hidden, dtype=torch.float16, device="cuda")
+    out = torch.empty(B, 16, dtype=torch.float16, device="cuda")
+    be.ffmlp_forward(x, w, B, IN, 16, hidden, L, act, 6, fb, out)
+    out_inf = torch.empty(B, 16, dtype=torch.float16, device="cuda")
+    be.ffmlp_inference(x, w, B, IN, 16, hidden, L, act, 6, torch.empty(B, hidden, dtype=torch.float16, device="cuda"), out_inf)
+    bb = torch.zeros(L, B, hidden, dtype=torch.float16, device="cuda")
+    gi = torch.zeros(B, IN, dtype=torch.float16, device="cuda")
+    gw = torch.zeros_like(w)
+    be.ffmlp_backward(g, x, w, fb, B, IN, 16, hidden, L, act, 6, True, bb, gi, gw)
+    torch.cuda.synchronize()
+    return dict(out=out.float().cpu().numpy(), out_inf=out_inf.float().cpu().numpy(), fb=fb.float().cpu().numpy(), bb=bb.float().cpu().numpy(),
+                grad_inputs=gi.float().cpu().numpy(), grad_weights=gw.float().cpu().numpy())
+
+
+@pytest.mark.parametrize("input_dim,hidden,num_layers,act", [(16, 16, 2, 0), (144, 16, 2, 0), (48, 64, 3, 0), (32, 32, 2, 0), (32, 128, 3, 0),
+                                                             (64, 256, 2, 0), (32, 128, 5, 0), (32, 64, 2, 3), (48, 32, 2, 6), (16, 64, 2, 1)])
+def test_mlp_generic_shapes_vs_oracle(input_dim, hidden, num_layers, act):
+    """Everything ffmlp.py:99-123 accepts besides the field's own shapes (hidden 16 / 32 / 128 / 256, input_dim = 16 m, e.g. the 144 -> 16 -> 16
+    feature encoder and the 48-wide colour input of nerf/network_tcnn.py:504-546; activations relu / exponential / sigmoid / none) runs on the
+    CUDA-core kernels of csrc/mlp_generic.cu -- same storage roundings, checked against the same oracle.  (32 / 64 -> 64 with a non-ReLU
+    activation stays on the tcgen05 kernel: the (32, 64, 2, sigmoid) case.)"""
+    import math
+    import oracle
+    g = np.random.RandomState(77)
+    B = 128 * 5
+    n = hidden * (input_dim + hidden * (num_layers - 1) + 16)
+    std = math.sqrt(3 / hidden)
+    c = dict(inputs=g.normal(0, 1, (B, input_dim)).astype(np.float16), weights=g.uniform(-std, std, n).astype(np.float16),
+             grad=g.normal(0, 1e-2, (B, 16)).astype(np.float16), input_dim=input_dim, num_layers=num_layers)
+    got = _mlp_run(ours(), c, hidden, act)
+    out, fb = oracle.ffmlp_forward(c["inputs"], c["weights"], input_dim, 16, hidden, num_layers, activation=act)
+    gw, bb, gi = oracle.ffmlp_backward(c["grad"], c["inputs"], c["weights"], got["fb"].astype(np.float16), input_dim, 16, hidden, num_layers,
+                                      activation=act, calc_grad_inputs=True)
+    tol = 1e-3 if act in (0, 6) else 3e-3            # __expf in the kernels vs expf in the oracle; the derivative through stored fp16 values
+    assert rel(got["out"], out.astype(np.float32)) <= tol
+    assert rel(got["out_inf"], out.astype(np.float32)) <= tol
+    assert rel(got["fb"], fb.astype(np.float32)) <= tol
+    if not (hidden == 64 and input_dim in (32, 64)):   # the tensor-core kernel keeps dL/dact in shared memory and does not write backward_buffer
+        assert rel(got["bb"], bb.astype(np.float32)) <= 2 * tol
+    assert rel(got["grad_inputs"], gi.astype(np.float32)) <= 2 * tol
+    assert rel(got["grad_weights"], gw) <= 2 * tol
+
+
+def test_ffmlp_module_generic_width_trains():
+    """The module surface for a non-field shape: FFMLP(144, 16, 16, 2) (network_tcnn.py:504-515) forward + backward through autograd."""
     from focnerf_b200.ffmlp import FFMLP
-    net = FFMLP(32, 3, 128, 2).cuda()
-    with pytest.raises(RuntimeError), torch.autocast("cuda", dtype=torch.float16):
-        net(torch.zeros(128, 32, device="cuda").half())
+    net = FFMLP(144, 16, 16, 2).cuda().train()
+    x = torch.randn(300, 144, device="cuda").half().requires_grad_()
+    with torch.autocast("cuda", dtype=torch.float16):
+        y = net(x)
+    assert y.shape == (300, 16)
+    y.float().pow(2).sum().backward()
+    assert torch.isfinite(net.weights.grad).all() and float(net.weights.grad.abs().max()) > 0 and x.grad.shape == x.shape
+    w = net.weights.detach().half().float()
+    h = torch.relu(x.detach().float() @ w[:144 * 16].view(16, 144).t()).half().float()
+    h = torch.relu(h @ w[144 * 16:144 * 16 + 256].view(16, 16).t()).half().float()
+    want = (h @ w[144 * 16 + 256:].view(16, 16).t())
+    assert float((y.detach().float() - want).abs().max()) <= 2e-3 * float(want.abs().max())
+
+
+def test_unsupported_shapes_raise():
+    """What the reference module rejects is rejected (ffmlp.py:104-107) -- and so is a hidden width its kernels do not have."""
+    from focnerf_b200.ffmlp import FFMLP
+    for args in ((32, 3, 48, 2), (20, 3, 64, 2), (32, 17, 64, 2), (32, 3, 64, 1)):
+        with pytest.raises(AssertionError):
+            FFMLP(*args)
 
 
 def test_freq_and_sh_encoders():

@@ -58,8 +58,8 @@ def _expected(world, steps, dev):
     return ps, opt
 
 
-def _run_rank(rank, world, port, result):
-    os.environ.update(MASTER_ADDR="127.0.0.1", MASTER_PORT=str(port))
+def _run_rank(rank, world, port, fused, result):
+    os.environ.update(MASTER_ADDR="127.0.0.1", MASTER_PORT=str(port), FOC_DP_FUSED=str(fused))
     torch.cuda.set_device(rank)
     dev = torch.device("cuda", rank)
     dist.init_process_group("gloo", rank=rank, world_size=world)
@@ -67,6 +67,7 @@ def _run_rank(rank, world, port, result):
     steps = 9
     ps = [torch.nn.Parameter(t.clone()) for t in _init(0, dev)]
     opt = PeerAdam(ps, table=ps[0], lr=1e-2, betas=(0.9, 0.99), eps=1e-15, growth_interval=3)
+    assert opt.fused_exchange == bool(fused)
     for it in range(steps):
         scale = float(opt.scale.item())
         g = _grads(it, rank, dev, world)
@@ -93,13 +94,14 @@ def _run_rank(rank, world, port, result):
     dist.destroy_process_group()
 
 
+@pytest.mark.parametrize("fused", [1, 0])       # 1: exchange inside the sweep (foc_adam_step_dp, two barriers); 0: foc_dp_reduce + foc_adam_step_peers
 @pytest.mark.parametrize("world", [1, 2])
-def test_peer_adam_matches_scaled_adam_on_mean_gradient(world):
+def test_peer_adam_matches_scaled_adam_on_mean_gradient(world, fused):
     if torch.cuda.device_count() < world:
         pytest.skip(f"needs {world} GPUs")
     mgr = mp.Manager()
     result = mgr.dict()
-    mp.spawn(_run_rank, args=(world, _free_port(), result), nprocs=world, join=True)
+    mp.spawn(_run_rank, args=(world, _free_port(), fused, result), nprocs=world, join=True)
     for r in range(world):
         assert all(result[r].values()), (r, dict(result[r]))
 
