@@ -410,6 +410,39 @@ def run_ours(args):
         quality = {"psnr_db": m, "psnr_sd_db": sd, "psnr_per_seed": psnrs, "seeds": list(C.QUALITY_SEEDS[:len(psnrs)]), "steps": C.PRETRAIN,
                    "eval_rays": C.EVAL_RAYS, "note": "fresh model per seed, the protocol's first PRETRAIN steps from an empty density grid, held-out rays"}
 
+    # end to end from PIXEL INDICES: a resident 8-view dataset of the same scene (nerf/provider.py --preload keeps
+    # poses and images on the GPU), the host uploads (pixel, camera) int32 pairs and reads the loss back; rays and ground truth are built on the
+    # device by csrc/rays.cu.  Same model, continuing from the steady state; timing only.
+    e2e_pixels = None
+    if world == 1 and args.steps > 0 and not args.no_pixels:
+        import numpy as np
+        import synthetic
+        from focnerf_b200 import rays as R
+        Hp = Wp = 800
+        poses = torch.from_numpy(np.asarray(synthetic.ring_poses(8, radius=2.2, seed=777), np.float32)).to(dev)
+        intr = synthetic.intrinsics(Hp, Wp)
+        imgs = torch.stack([scene.render_gt(*R.pixel_batch(poses[k:k + 1], intr, Hp, Wp)[:2]) for k in range(8)])
+        ds = R.PixelDataset(poses, intr, Hp, Wp, imgs, bg=1.0)
+        g = np.random.RandomState(99)
+        idx_pool = [(torch.from_numpy(g.randint(0, Hp * Wp, C.RAYS_PER_GPU).astype(np.int32)).pin_memory(),
+                     torch.from_numpy(g.randint(0, 8, C.RAYS_PER_GPU).astype(np.int32)).pin_memory()) for _ in range(64)]
+        st_idx = (torch.empty(C.RAYS_PER_GPU, dtype=torch.int32, device=dev), torch.empty(C.RAYS_PER_GPU, dtype=torch.int32, device=dev))
+        for i in range(48):
+            tr.fit_step_pixels(ds, *idx_pool[i % 64], st_idx)
+        torch.cuda.synchronize()
+        p0, p1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        p0.record()
+        for i in range(args.steps):
+            tr.fit_step_pixels(ds, *idx_pool[(48 + i) % 64], st_idx)
+        p1.record()
+        torch.cuda.synchronize()
+        pms = p0.elapsed_time(p1) / args.steps
+        e2e_pixels = {"value": C.RAYS_PER_GPU / (pms * 1e-3), "unit": "rays/s", "ms_per_step": pms, "h2d_bytes_per_step": C.RAYS_PER_GPU * 8, "d2h_bytes_per_step": 4,
+                      "samples_per_step": float(tr.step_counter[:, 0].float().mean().item()),
+                      "note": "Trainer.fit_step_pixels: the host uploads 4096 (pixel, camera) int32 pairs per step, foc_pixel_batch builds rays + ground truth from a "
+                              "resident 8-view 800x800 dataset of the same scene; density refresh every 16 steps inside, loss read back every step"}
+        del ds, imgs
+
     # round-1 workload for continuity (frozen analytic occupancy grid, lr 1e-2, no refresh): NOT the headline
     frozen = None
     if world == 1 and args.frozen_steps > 0:
@@ -505,7 +538,7 @@ def run_ours(args):
                 "h2d_bytes_per_step": world * C.RAYS_PER_GPU * 9 * 4, "d2h_bytes_per_step": world * 4},
         "gpu_launches": int(round(launches_per_step * args.steps)),
         "render_own_model": render_own if render is not render_own else None,
-        "multi_object": multi, "multi_object_edit8": multi8, "density_refresh": refresh, "quality": quality, "quality_dp": quality_dp, "frozen_bitfield": frozen,
+        "multi_object": multi, "multi_object_edit8": multi8, "density_refresh": refresh, "quality": quality, "quality_dp": quality_dp, "e2e_pixels": e2e_pixels, "frozen_bitfield": frozen,
         "roofline": roof,
     }
     if world == 1:
@@ -550,6 +583,7 @@ if __name__ == "__main__":
     ap.add_argument("--frozen-steps", type=int, default=64, help="timed steps of round 1's frozen-occupancy workload, for continuity (0 = skip)")
     ap.add_argument("--warmup", type=int, default=8)
     ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
+    ap.add_argument("--no-pixels", action="store_true", help="skip the pixel-index end-to-end leg")
     ap.add_argument("--no-graph", action="store_true", help="launch the step eagerly instead of replaying a CUDA graph")
     ap.add_argument("--torch-optim", action="store_true", help="torch.optim.Adam + GradScaler instead of the fused ScaledAdam")
     ap.add_argument("--no-fused", action="store_true", help="field network through the unfused operator modules")

@@ -10,7 +10,9 @@
 //                      [B, L*C] tensor the network consumes -- this removes the permute+reshape copy the reference's
 //                      Python wrapper does after the kernel (grid.py:57).
 // fp16 numerics follow the reference's c10::Half rounding sequence (see hashgrid.cuh) so encodings agree bit for bit.
+#include <cstdlib>
 #include "hashgrid.cuh"
+#include "tc_common.cuh"
 
 using namespace foc;
 
@@ -125,7 +127,8 @@ struct LevelParams {
 // formed once per dimension: (p + 1) * k = p * k + k in the wrapping 32-bit arithmetic of gridencoder.cu:50-84, so the 2^D corner
 // indices are D multiplies + D adds + (D - 1) combines each, instead of 2 D multiplies each.  Same indices, same float
 // operations in the same order, same bits out.
-template <typename T, int D, int C, bool HASHED>
+// SMEM: `tab` is a shared-memory copy of the level (k_grid_fwd_staged): plain loads instead of ld.global.nc
+template <typename T, int D, int C, bool HASHED, bool SMEM = false>
 __device__ __forceinline__ void encode_level_uniform(const float (&x)[D], const T* __restrict__ tab, const LevelParams<D>& P,
                                                      bool align_corners, uint32_t interp, float (&res)[C]) {
     constexpr uint32_t primes[7] = {1u, 2654435761u, 805459861u, 3674653429u, 2097192037u, 1434869437u, 2165219737u};
@@ -158,9 +161,14 @@ __device__ __forceinline__ void encode_level_uniform(const float (&x)[D], const 
         }
         if constexpr (sizeof(T) == 2 && C == 2) {
             if (row[1] == row[0] + 1 && (row[0] & 1u) == 0) {
-                const uint2 u = __ldg(reinterpret_cast<const uint2*>(tab + (size_t)row[0] * 2));
+                const uint2 u = SMEM ? *reinterpret_cast<const uint2*>(tab + (size_t)row[0] * 2) : __ldg(reinterpret_cast<const uint2*>(tab + (size_t)row[0] * 2));
                 const __half2 a = *reinterpret_cast<const __half2*>(&u.x), b = *reinterpret_cast<const __half2*>(&u.y);
                 rows[idx][0] = __low2float(a); rows[idx][1] = __high2float(a); rows[idx + 1][0] = __low2float(b); rows[idx + 1][1] = __high2float(b);
+                continue;
+            }
+            if constexpr (SMEM) {
+                const __half2 h0 = *reinterpret_cast<const __half2*>(tab + (size_t)row[0] * 2), h1 = *reinterpret_cast<const __half2*>(tab + (size_t)row[1] * 2);
+                rows[idx][0] = __low2float(h0); rows[idx][1] = __high2float(h0); rows[idx + 1][0] = __low2float(h1); rows[idx + 1][1] = __high2float(h1);
                 continue;
             }
         }
@@ -264,6 +272,84 @@ k_grid_fwd_tile(const float* __restrict__ inputs, const T* __restrict__ table, c
     }
 }
 
+// EXPERIMENT (BASELINE.json north_star item 2; measured and NOT the default): the tile kernel as a persistent kernel whose CTAs
+// first copy the coarsest `n_stage` levels of the fp16 table (level 0: 4 920 rows = 19.7 KB, level 1: 12 168 = 48.7 KB, level 2: 32 768 =
+// 131 KB) into shared memory with one cp.async.bulk, and gather those levels from there.  THREADS / 4 points per tile iteration.
+// Selected by FOC_GRID_FWD_STAGE=2 (two CTAs of 512 threads per SM) or =3 (one CTA of 1024 threads per SM).  Same arithmetic, same bits.
+template <int THREADS>
+__global__ void __launch_bounds__(THREADS)
+k_grid_fwd_staged(const float* __restrict__ inputs, const __half* __restrict__ table, const int32_t* __restrict__ offsets,
+                  __half* __restrict__ outputs, uint32_t B, uint32_t L, float S, uint32_t H, uint32_t gridtype, bool align_corners, uint32_t interp,
+                  const int32_t* __restrict__ n_rows, uint32_t n_stage, uint32_t stage_rows_cap) {
+    using T = __half;
+    constexpr int D = 3, C = 2, TP = THREADS / 4;
+    pdl_sync();
+    if (n_rows != nullptr) { const uint32_t v = (uint32_t)max(__ldg(n_rows), 0); B = v < B ? v : B; }
+    extern __shared__ __align__(128) uint8_t tile_raw[];
+    // rows of levels [0, n_stage) as the offsets tensor holds them; the host sized the buffer from its own restatement of the sizing rule
+    uint32_t stage_rows = (uint32_t)__ldg(offsets + n_stage);
+    if (stage_rows > stage_rows_cap) { n_stage = 0; stage_rows = 0; }                       // disagreement: gather everything from global memory
+    __half* s_tab = reinterpret_cast<__half*>(tile_raw);                                    // [stage_rows][2]
+    uint32_t* tw = reinterpret_cast<uint32_t*>(tile_raw + (size_t)stage_rows_cap * 4);      // [TP][L + 1] words
+    __shared__ LevelParams<D> s_lv[kTileMaxLevels];
+    __shared__ __align__(8) uint64_t s_bar;
+    if (threadIdx.x < L) {
+        const GridLevel lv = grid_level(offsets, threadIdx.x, S, H);
+        const GridIndexer<D> gi(gridtype, align_corners, lv.hashmap_size, lv.resolution);
+        LevelParams<D>& P = s_lv[threadIdx.x];
+        P.scale = lv.scale; P.offset = lv.offset; P.and_mask = gi.and_mask; P.hashed = gi.hashed; P.need_mod = gi.need_mod;
+        P.hashmap_size = lv.hashmap_size; P.resolution = lv.resolution;
+        #pragma unroll
+        for (int d = 0; d < D; ++d) P.st[d] = gi.st[d];
+    }
+    if (threadIdx.x == 0) { foc::tc::mbar_init(&s_bar, 1); foc::tc::fence_barrier_init(); }
+    __syncthreads();
+    if (threadIdx.x == 0 && stage_rows != 0) {
+        const uint32_t bytes = stage_rows * 4u;
+        foc::tc::mbar_expect_tx(&s_bar, bytes);
+        asm volatile("cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];"
+                     ::"r"(foc::tc::smem_u32(s_tab)), "l"(table), "r"(bytes), "r"(foc::tc::smem_u32(&s_bar)) : "memory");
+    }
+    if (stage_rows != 0) foc::tc::mbar_wait(&s_bar, 0);
+    const uint32_t lane = threadIdx.x & 31u, warp = threadIdx.x >> 5;
+    constexpr uint32_t kPtWarps = TP / 32;                              // warps side by side over the points of a tile
+    const uint32_t pt = (warp % kPtWarps) * 32u + lane;
+    for (uint32_t tile = blockIdx.x; (uint64_t)tile * TP < B; tile += gridDim.x) {
+        const uint32_t b0 = tile * TP, b = b0 + pt;
+        if (b < B) {
+            float x[D];
+            #pragma unroll
+            for (int d = 0; d < D; ++d) x[d] = __ldg(inputs + (size_t)b * D + d);
+            const bool oob = grid_oob<D>(x);
+            for (uint32_t level = warp / kPtWarps; level < L; level += 4) {
+                float res[C];
+                if (oob) { res[0] = 0.f; res[1] = 0.f; }
+                else {
+                    const LevelParams<D>& P = s_lv[level];
+                    if (level < n_stage && !P.need_mod && !P.hashed) encode_level_uniform<T, D, C, false, true>(x, s_tab + (size_t)P.offset * C, P, align_corners, interp, res);
+                    else {
+                        const T* tab = table + (size_t)P.offset * C;
+                        if (P.need_mod) {
+                            GridLevel lv; lv.scale = P.scale; lv.resolution = P.resolution; lv.hashmap_size = P.hashmap_size; lv.offset = P.offset;
+                            const GridIndexer<D> gidx(gridtype, align_corners, lv.hashmap_size, lv.resolution);
+                            float pos[D], pder[D];
+                            uint32_t pg[D];
+                            encode_level<T, D, C>(x, tab, lv, gidx, align_corners, interp, pos, pder, pg, res);
+                        } else if (P.hashed) encode_level_uniform<T, D, C, true>(x, tab, P, align_corners, interp, res);
+                        else encode_level_uniform<T, D, C, false>(x, tab, P, align_corners, interp, res);
+                    }
+                }
+                store_row<T, C>(reinterpret_cast<T*>(tw + (size_t)pt * (L + 1) + level), res);
+            }
+        }
+        __syncthreads();
+        const uint32_t npts = min((uint32_t)TP, B - b0);
+        uint32_t* dst = reinterpret_cast<uint32_t*>(outputs + (size_t)b0 * L * C);
+        for (uint32_t i = threadIdx.x; i < npts * L; i += THREADS) { const uint32_t r = i / L, c = i - r * L; dst[i] = tw[r * (L + 1) + c]; }
+        __syncthreads();
+    }
+}
+
 template <typename T, int D, int C, int LAYOUT>
 __global__ void __launch_bounds__(256)
 k_grid_fwd(const float* __restrict__ inputs, const T* __restrict__ table, const int32_t* __restrict__ offsets,
@@ -336,6 +422,36 @@ k_grid_fwd(const float* __restrict__ inputs, const T* __restrict__ table, const 
     }
 }
 
+// FOC_GRID_FWD_STAGE (read once): 0 = the tile kernel (default); 2 / 3 = k_grid_fwd_staged with that many coarse levels in shared memory
+inline int grid_fwd_stage_levels() { static const int v = [] { const char* e = getenv("FOC_GRID_FWD_STAGE"); return e ? atoi(e) : 0; }(); return v; }
+
+inline int launch_staged(const float* inputs, const __half* table, const int32_t* offsets, __half* outputs, uint32_t B, uint32_t L, float S, uint32_t H,
+                         uint32_t gridtype, bool ac, uint32_t interp, const int32_t* n_rows, uint32_t ns, cudaStream_t st) {
+    // rows of levels [0, ns): the gridencoder's sizing rule (grid.py:117-128), as the offsets tensor holds it (device memory: restated here)
+    uint32_t rows = 0;
+    for (uint32_t l = 0; l < ns; ++l) {
+        const uint32_t res = (uint32_t)ceilf(exp2f((float)l * S) * (float)H);
+        uint64_t n = (uint64_t)(res + 1) * (res + 1) * (res + 1);
+        rows += (uint32_t)((n + 7) / 8 * 8);
+    }
+    const bool big = ns >= 3;
+    const uint32_t threads = big ? 1024u : 512u, tp = threads / 4;
+    const size_t smem = (size_t)rows * 4 + (size_t)tp * (L + 1) * 4;
+    if (smem > 220 * 1024) return FOC_ERR_UNSUPPORTED;
+    static DynSmemOptIn optin_a, optin_b;
+    int dev = 0, sms = kNumSMs;
+    cudaGetDevice(&dev);
+    cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev);
+    if (big) {
+        if (int rc = optin_b.ensure(k_grid_fwd_staged<1024>, 220 * 1024)) return rc;
+        foc::launch(k_grid_fwd_staged<1024>, (uint32_t)sms, 1024, smem, st, inputs, table, offsets, outputs, B, L, S, H, gridtype, ac, interp, n_rows, ns, rows);
+    } else {
+        if (int rc = optin_a.ensure(k_grid_fwd_staged<512>, 110 * 1024)) return rc;
+        foc::launch(k_grid_fwd_staged<512>, (uint32_t)sms * 2u, 512, smem, st, inputs, table, offsets, outputs, B, L, S, H, gridtype, ac, interp, n_rows, ns, rows);
+    }
+    FOC_LAUNCH_CHECK(); return 0;
+}
+
 template <typename T, int D, int C>
 int launch_fwd(const float* inputs, const void* table, const int32_t* offsets, void* outputs, uint32_t B, uint32_t L,
                float S, uint32_t H, void* dy_dx, uint32_t gridtype, bool ac, uint32_t interp, int layout, cudaStream_t st, const int32_t* n_rows = nullptr) {
@@ -345,6 +461,10 @@ int launch_fwd(const float* inputs, const void* table, const int32_t* offsets, v
         dim3 grid(ceil_div(B, 256), L);
         foc::launch(k_grid_fwd<T, D, C, 0>, grid, 256, 0, st, inputs, (const T*)table, offsets, (T*)outputs, B, L, S, H, (T*)dy_dx, gridtype, ac, interp);
     } else if (!dy_dx && L <= (uint32_t)kTileMaxLevels && (size_t)kTilePts * (L * C * sizeof(T) + 4) <= 40 * 1024) {
+        if constexpr (sizeof(T) == 2 && D == 3 && C == 2) {
+            if (const int ns = grid_fwd_stage_levels(); ns > 0 && gridtype == 0 && (uint32_t)ns < L)
+                return launch_staged(inputs, (const __half*)table, offsets, (__half*)outputs, B, L, S, H, gridtype, ac, interp, n_rows, (uint32_t)ns, st);
+        }
         foc::launch(k_grid_fwd_tile<T, D, C>, ceil_div(B, (uint32_t)kTilePts), 256, (size_t)kTilePts * (L * C * sizeof(T) + 4), st, inputs, (const T*)table, offsets,
                     (T*)outputs, B, L, S, H, gridtype, ac, interp, n_rows);
     } else {

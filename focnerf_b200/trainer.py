@@ -417,6 +417,25 @@ class Trainer:
         loss = self.train_step(stage[0], stage[1], stage[2])
         return float(loss.item())
 
+    def train_step_pixels(self, dataset, pix_h, pose_idx_h, stage):
+        """End-to-end step from PIXEL INDICES: the host uploads (pixel, camera) int32 pairs -- 8 bytes per ray instead of 36 -- and
+        rays.PixelDataset builds rays and ground truth on the device (csrc/rays.cu), straight into the captured step's input buffers.
+        stage = (pix, pose_idx) int32 device buffers.  Returns the loss as a Python float."""
+        stage[0].copy_(pix_h, non_blocking=True)
+        stage[1].copy_(pose_idx_h, non_blocking=True)
+        n = int(pix_h.shape[0])
+        out = None
+        if self.use_graph and self._graph is not None and self.mean_count > 0 and self._graph[2][0].shape[0] == n:
+            out = tuple(self._graph[2][:3])
+        o, d, gt = dataset.batch(stage[0], stage[1], out=out)
+        return float(self.train_step(o, d, gt).item())
+
+    def fit_step_pixels(self, dataset, pix_h, pose_idx_h, stage):
+        if self.global_step % self.update_extra_interval == 0:
+            self.update_extra_state()
+        self.global_step += 1
+        return self.train_step_pixels(dataset, pix_h, pose_idx_h, stage)
+
     # ---- the reference's training loop body (nerf/utils.py:851-870, train_one_epoch) ---------------------------------------
     def fit_step(self, rays_o, rays_d, gt_rgb, bg_color=1.0):
         """One iteration of train_one_epoch: refresh the density grid when `global_step % update_extra_interval == 0`

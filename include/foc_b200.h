@@ -156,6 +156,15 @@ int foc_grad_total_variation(const float *inputs, const float *embeddings, float
                              float weight, uint32_t B, uint32_t D, uint32_t C, uint32_t L, float S, uint32_t H,
                              uint32_t gridtype, int align_corners, void *stream);
 
+/* The batch of a train step from pixel indices, one launch.  Replaces, on the device, get_rays
+ * (nerf/utils.py:56-157: ~15 torch launches) and the loader's ground-truth gather (nerf/provider.py collate `images[index, inds]` plus
+ * train_step's RGBA blend, legacy/nerf/utils.py:468-500): ray n looks at flat pixel pix[n] (NULL: n) of camera pose_idx[n] (NULL: 0);
+ * poses [n_poses,4,4] f32 row-major camera-to-world, intrinsics as the reference passes them.  images (optional, with gt): resident
+ * [n_poses, H*W, channels] f32, channels 3 or 4 (4: rgb * a + bg * (1 - a)) -> gt [N,3].  rays_o / rays_d [N,3] f32. */
+int foc_pixel_batch(const float *poses, uint32_t n_poses, float fx, float fy, float cx, float cy, uint32_t H, uint32_t W,
+                    const int32_t *pose_idx, const int32_t *pix, uint32_t N, float *rays_o, float *rays_d, const float *images,
+                    uint32_t channels, float bg, float *gt, void *stream);
+
 /* ---------------------------------------------------------------- ffmlp (ffmlp/src/ffmlp.h:7-13) */
 
 /* replaces ffmlp_forward / ffmlp_inference, ffmlp.h:8-9 (ffmlp.cu:331-407, 525-709).  tcgen05/TMEM kernel.

@@ -1,0 +1,110 @@
+"""-m gpu: device-side batch construction (csrc/rays.cu, focnerf_b200/rays.py) against the reference's own arithmetic.
+
+The expected values are the lines of nerf/utils.py:62-66,119-131 (legacy/nerf/utils.py get_rays) restated in torch on the same device:
+meshgrid + 0.5, gather, (i - cx) / fx, stack, divide by the norm, `directions @ poses[:, :3, :3].transpose(-1, -2)`.  cuBLAS does not
+fix the summation order of the 3-term dot products, so directions are compared to 1 ulp-scale tolerance (2e-7 absolute on unit
+vectors), origins and the gathered ground truth bitwise."""
+import numpy as np
+import pytest
+import torch
+
+import synthetic
+
+pytestmark = pytest.mark.gpu
+
+
+def _reference_get_rays(poses, intrinsics, H, W, inds):
+    fx, fy, cx, cy = intrinsics
+    dev, B = poses.device, poses.shape[0]
+    i, j = torch.meshgrid(torch.linspace(0, W - 1, W, device=dev), torch.linspace(0, H - 1, H, device=dev), indexing="ij")
+    i = i.t().reshape([1, H * W]).expand([B, H * W]) + 0.5
+    j = j.t().reshape([1, H * W]).expand([B, H * W]) + 0.5
+    i, j = torch.gather(i, -1, inds), torch.gather(j, -1, inds)
+    zs = torch.ones_like(i)
+    xs, ys = (i - cx) / fx * zs, (j - cy) / fy * zs
+    directions = torch.stack((xs, ys, zs), dim=-1)
+    directions = directions / torch.norm(directions, dim=-1, keepdim=True)
+    rays_d = directions @ poses[:, :3, :3].transpose(-1, -2)
+    rays_o = poses[..., :3, 3][..., None, :].expand_as(rays_d)
+    return rays_o, rays_d
+
+
+def test_pixel_batch_matches_reference_get_rays():
+    from focnerf_b200 import rays
+    H, W, B, N = 600, 800, 5, 4096
+    poses = torch.from_numpy(np.stack(synthetic.ring_poses(B, radius=2.2, seed=3)).astype(np.float32)).cuda()
+    intr = synthetic.intrinsics(H, W)
+    g = torch.Generator(device="cuda").manual_seed(1)
+    inds = torch.randint(0, H * W, (N,), device="cuda", generator=g).expand(B, N).contiguous()
+    inds[0, :4] = torch.tensor([0, W - 1, (H - 1) * W, H * W - 1], device="cuda")          # the four corners
+    want_o, want_d = _reference_get_rays(poses, intr, H, W, inds)
+    pix = inds.reshape(-1).to(torch.int32)
+    pidx = torch.arange(B, device="cuda", dtype=torch.int32).repeat_interleave(N)
+    o, d, gt = rays.pixel_batch(poses, intr, H, W, pix, pidx)
+    assert gt is None
+    assert torch.equal(o.view(B, N, 3), want_o)
+    assert float((d.view(B, N, 3) - want_d).abs().max()) <= 2e-7
+    assert float((d.norm(dim=-1) - 1).abs().max()) <= 2e-7
+    # and against the numpy-side generator the synthetic pool uses
+    o2, d2 = synthetic.get_rays(poses[2].cpu().numpy(), intr, H, W, inds[2].cpu())
+    assert float((d.view(B, N, 3)[2].cpu() - d2).abs().max()) <= 3e-7 and torch.equal(o.view(B, N, 3)[2].cpu(), o2)
+    # the module-level get_rays keeps the reference's result keys; N <= 0 = every pixel in order
+    res = rays.get_rays(poses[:2], intr, 60, 80, N=-1)
+    full_o, full_d = _reference_get_rays(poses[:2], synthetic.intrinsics(60, 80), 60, 80, torch.arange(4800, device="cuda").expand(2, 4800))
+    res = rays.get_rays(poses[:2], synthetic.intrinsics(60, 80), 60, 80, N=-1)
+    assert set(res) == {"rays_o", "rays_d"} and float((res["rays_d"] - full_d).abs().max()) <= 2e-7 and torch.equal(res["rays_o"], full_o)
+    res = rays.get_rays(poses[:2], synthetic.intrinsics(60, 80), 60, 80, N=100)
+    assert res["inds"].shape == (2, 100) and res["rays_d"].shape == (2, 100, 3)
+
+
+@pytest.mark.parametrize("channels", [3, 4])
+def test_pixel_batch_gathers_ground_truth(channels):
+    from focnerf_b200 import rays
+    H, W, B, N = 64, 48, 3, 1000
+    g = torch.Generator(device="cuda").manual_seed(2)
+    poses = torch.from_numpy(np.stack(synthetic.ring_poses(B, radius=2.0, seed=4)).astype(np.float32)).cuda()
+    images = torch.rand(B, H * W, channels, device="cuda", generator=g)
+    ds = rays.PixelDataset(poses, synthetic.intrinsics(H, W), H, W, images, bg=0.75)
+    pix = torch.randint(0, H * W, (N,), device="cuda", generator=g).to(torch.int32)
+    pidx = torch.randint(0, B, (N,), device="cuda", generator=g).to(torch.int32)
+    o, d, gt = ds.batch(pix, pidx)
+    px = images[pidx.long(), pix.long()]
+    want = px[:, :3] * px[:, 3:] + 0.75 * (1 - px[:, 3:]) if channels == 4 else px      # legacy/nerf/utils.py train_step's blend
+    assert torch.equal(gt, want)
+    assert torch.equal(o, poses[pidx.long(), :3, 3])
+
+
+def test_trainer_step_from_pixel_indices_equals_step_from_rays():
+    """Trainer.train_step_pixels (8 bytes per ray uploaded) trains exactly like train_step on the rays / colours the same indices select."""
+    import cases
+    from focnerf_b200 import rays
+    from focnerf_b200.trainer import Trainer
+    scene, cascade, grid, bits, thresh = cases.scene_bitfield(1.0)
+    H = W = 200
+    P = 4
+    poses = torch.from_numpy(np.stack(synthetic.ring_poses(P, radius=2.2, seed=9)).astype(np.float32)).cuda()
+    intr = synthetic.intrinsics(H, W)
+    imgs = []
+    for p in range(P):
+        o, d, _ = rays.pixel_batch(poses[p:p + 1], intr, H, W)
+        imgs.append(scene.render_gt(o, d))
+    ds = rays.PixelDataset(poses, intr, H, W, torch.stack(imgs), bg=1.0)
+    losses = {}
+    for mode in ("pixels", "rays"):
+        tr = Trainer(bound=1.0, density_grid=torch.from_numpy(grid), seed=0, use_graph=True)
+        stage = (torch.empty(2048, dtype=torch.int32, device="cuda"), torch.empty(2048, dtype=torch.int32, device="cuda"))
+        out = []
+        for it in range(24):
+            g = np.random.RandomState(100 + it)
+            pix_h = torch.from_numpy(g.randint(0, H * W, 2048).astype(np.int32)).pin_memory()
+            pidx_h = torch.from_numpy(g.randint(0, P, 2048).astype(np.int32)).pin_memory()
+            if mode == "pixels":
+                out.append(tr.train_step_pixels(ds, pix_h, pidx_h, stage))
+            else:
+                o, d, gt = ds.batch(pix_h.cuda(), pidx_h.cuda())
+                out.append(float(tr.train_step(o, d, gt).item()))
+            if tr.local_step % 16 == 0:
+                tr.update_mean_count()
+        losses[mode] = out
+    assert losses["pixels"] == losses["rays"]
+    assert losses["pixels"][-1] < losses["pixels"][0]
