@@ -14,7 +14,19 @@
 
 namespace foc {
 
-constexpr int kNumSMs = 148;   // B200: 2 dies x 74 SMs
+constexpr int kNumSMs = 148;   // B200: 2 dies x 74 SMs (tuning thresholds; persistent grids ask the device: num_sms())
+
+// SM count of the CURRENT device, cached per device (no process-wide assumption: a part with SMs fused off, or MIG, reports fewer)
+inline int num_sms() {
+    static int cache[64] = {};
+    int dev = 0;
+    if (cudaGetDevice(&dev) != cudaSuccess || dev < 0 || dev >= 64) return kNumSMs;
+    if (cache[dev] == 0) {
+        int v = 0;
+        cache[dev] = (cudaDeviceGetAttribute(&v, cudaDevAttrMultiProcessorCount, dev) == cudaSuccess && v > 0) ? v : kNumSMs;
+    }
+    return cache[dev];
+}
 
 // ---- programmatic dependent launch (PDL).  The train step is ~45 back-to-back launches of 5-50 us kernels; with PDL the
 // next kernel's CTAs are scheduled while the previous kernel drains and run their prologue (barrier init, TMEM allocation,

@@ -278,7 +278,7 @@ int launch_field_fwd(const uint16_t* enc, const float* dirs, const uint16_t* w_s
     FieldFwdParams p;
     p.dirs = dirs; p.sigma = sigma; p.rgb = rgb; p.B = B; p.num_tiles = B / kTile; p.n_hmm_s = hs; p.n_hmm_c = hc; p.training = TRAIN; p.n_rows = n_rows;
     const uint32_t want = ceil_div(p.num_tiles, (uint32_t)kGroups);
-    const uint32_t grid = want < (uint32_t)kNumSMs ? want : (uint32_t)kNumSMs;
+    const uint32_t sms = (uint32_t)foc::num_sms(), grid = want < sms ? want : sms;
     foc::launch(k_field_fwd<TRAIN>, grid, 128 * kGroups, L.total, st, tm_in, tm_win_s, tm_w_s, tm_win_c, tm_w_c, tm_fb_s, tm_fb_c, tm_cin, p);
     FOC_LAUNCH_CHECK(); return 0;
 }

@@ -439,9 +439,7 @@ inline int launch_staged(const float* inputs, const __half* table, const int32_t
     const size_t smem = (size_t)rows * 4 + (size_t)tp * (L + 1) * 4;
     if (smem > 220 * 1024) return FOC_ERR_UNSUPPORTED;
     static DynSmemOptIn optin_a, optin_b;
-    int dev = 0, sms = kNumSMs;
-    cudaGetDevice(&dev);
-    cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev);
+    const int sms = foc::num_sms();
     if (big) {
         if (int rc = optin_b.ensure(k_grid_fwd_staged<1024>, 220 * 1024)) return rc;
         foc::launch(k_grid_fwd_staged<1024>, (uint32_t)sms, 1024, smem, st, inputs, table, offsets, outputs, B, L, S, H, gridtype, ac, interp, n_rows, ns, rows);

@@ -390,7 +390,7 @@ k_mlp_wgrad_finish(const float* __restrict__ partials, uint32_t n_cta, uint32_t 
 }
 
 uint32_t bwd_grid(uint32_t B) {
-    const uint32_t tiles = B / kTile, cap = (uint32_t)kNumSMs * 2u;
+    const uint32_t tiles = B / kTile, cap = (uint32_t)foc::num_sms() * 2u;
     return tiles < cap ? tiles : cap;
 }
 uint32_t num_params_of(uint32_t input_dim, uint32_t num_layers) { return kHidden * (input_dim + kHidden * (num_layers - 1) + kOutPad); }

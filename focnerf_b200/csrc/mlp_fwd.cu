@@ -237,7 +237,7 @@ int launch_fwd(const uint16_t* inputs, const uint16_t* weights, uint32_t B, uint
     p.B = B; p.num_layers = num_layers; p.activation = activation; p.output_activation = output_activation;
     p.num_tiles = B / kTile;
     const uint32_t ctas_per_sm = 4;                                    // 4 x 64 TMEM columns, ~4 x 45 KB shared memory
-    const uint32_t grid = p.num_tiles < (uint32_t)kNumSMs * ctas_per_sm ? p.num_tiles : (uint32_t)kNumSMs * ctas_per_sm;
+    const uint32_t cap = (uint32_t)foc::num_sms() * ctas_per_sm, grid = p.num_tiles < cap ? p.num_tiles : cap;
     foc::launch(k_mlp_fwd<IN, ACT>, grid, 128, smem, st, tm_in, tm_win, tm_w, tm_fb, p);
     FOC_LAUNCH_CHECK(); return 0;
 }
