@@ -54,10 +54,7 @@ __device__ __forceinline__ uint4 ld_peer16(const void* p) {
 }
 // mean over the W ranks, summed in fp32 in rank order: the same bits on whichever rank owns the element (k_dp_reduce's arithmetic)
 template <int W>
-__device__ __forceinline__ void pull_table4(const PeerGrad& G, uint64_t i, float (&g)[4]) {
-    uint2 v[W];
-    #pragma unroll
-    for (int r = 0; r < W; ++r) v[r] = ld_peer8(G.g16[r] + i);
+__device__ __forceinline__ void mean_table4(const uint2 (&v)[W], float (&g)[4]) {
     g[0] = g[1] = g[2] = g[3] = 0.f;
     #pragma unroll
     for (int r = 0; r < W; ++r) {
@@ -126,19 +123,27 @@ __global__ void __launch_bounds__(kThreads) k_adam_nonfinite(const __grid_consta
     bool ok = true;
     if (T.grad_dtype == 1) {
         const __half* g = static_cast<const __half*>(T.grad);
-        uint64_t i = base + (uint64_t)threadIdx.x * 8;
+        const uint64_t i0 = base + (uint64_t)threadIdx.x * 8;
+        constexpr int kIt = kPerBlock / (kThreads * 8);
+        // all loads of the thread first (independent, in flight together), then branch-free tests: a short-circuit `&&` per word made
+        // every load wait for the previous one's verdict
+        uint4 v[kIt];
         #pragma unroll
-        for (int u = 0; u < kPerBlock / (kThreads * 8); ++u, i += (uint64_t)kThreads * 8) {
-            if (i + 8 <= end) {
-                const uint4 v = *reinterpret_cast<const uint4*>(g + i);
-                const uint32_t w[4] = {v.x, v.y, v.z, v.w};
-                #pragma unroll
-                for (int k = 0; k < 4; ++k)         // exponent field all ones <=> inf / nan, per 16-bit half
-                    ok = ok && ((w[k] & 0x7c00u) != 0x7c00u) && ((w[k] & 0x7c000000u) != 0x7c000000u);
-            } else {
-                for (uint64_t j = i; j < end && j < i + 8; ++j) ok = ok && ((__half_as_ushort(g[j]) & 0x7c00u) != 0x7c00u);
-            }
+        for (int u = 0; u < kIt; ++u) {
+            const uint64_t i = i0 + (uint64_t)u * kThreads * 8;
+            v[u] = (i + 8 <= end) ? *reinterpret_cast<const uint4*>(g + i) : make_uint4(0u, 0u, 0u, 0u);     // default policy: the sweep reads it next
         }
+        uint32_t bad = 0;
+        #pragma unroll
+        for (int u = 0; u < kIt; ++u) {
+            const uint32_t w[4] = {v[u].x, v[u].y, v[u].z, v[u].w};
+            #pragma unroll
+            for (int k = 0; k < 4; ++k)             // exponent field all ones <=> inf / nan, per 16-bit half
+                bad |= (uint32_t)((w[k] & 0x7c00u) == 0x7c00u) | (uint32_t)((w[k] & 0x7c000000u) == 0x7c000000u);
+            const uint64_t i = i0 + (uint64_t)u * kThreads * 8;
+            if (i < end && i + 8 > end) { for (uint64_t j = i; j < end; ++j) bad |= (uint32_t)((__half_as_ushort(g[j]) & 0x7c00u) == 0x7c00u); }
+        }
+        ok = bad == 0;
     } else {
         const float* g = static_cast<const float*>(T.grad);
         uint64_t i = base + (uint64_t)threadIdx.x * 4;
@@ -181,6 +186,21 @@ __global__ void __launch_bounds__(kThreads) k_adam_step(const __grid_constant__ 
     const FocAdamTensor& T = L.t[ti];
     const uint64_t base = (uint64_t)(vb - L.block_start[ti]) * kPerBlock;
     const bool skip = bad || T.grad == nullptr;
+    // PULL: every peer load of this thread's kUnroll iterations is issued before the first one is used -- NVLink latency (~2 us) is paid
+    // once per CTA, not once per iteration (a shard is at most a wave or two of CTAs, so nothing else would hide it)
+    uint2 pre[PULL > 0 ? kUnroll : 1][PULL > 0 ? PULL : 1];
+    if constexpr (PULL > 0) {
+        if (!skip && ti == PS.tensor) {
+            #pragma unroll
+            for (int u = 0; u < kUnroll; ++u) {
+                const uint64_t i = base + ((uint64_t)u * kThreads + threadIdx.x) * kVec;
+                if (i < T.n) {
+                    #pragma unroll
+                    for (int r = 0; r < PULL; ++r) pre[u][r] = ld_peer8(PG.g16[r] + i);
+                }
+            }
+        }
+    }
     #pragma unroll
     for (int u = 0; u < kUnroll; ++u) {
         const uint64_t i = base + ((uint64_t)u * kThreads + threadIdx.x) * kVec;
@@ -189,7 +209,7 @@ __global__ void __launch_bounds__(kThreads) k_adam_step(const __grid_constant__ 
         if (!skip) {
             float g[4], p[4], m[4], v[4];
             if constexpr (PULL > 0) {
-                if (ti == PS.tensor) pull_table4<PULL>(PG, i, g);     // the shard is a multiple of 8 elements: never a partial vector
+                if (ti == PS.tensor) mean_table4<PULL>(pre[u], g);    // the shard is a multiple of 8 elements: never a partial vector
                 else pull_tail4<PULL>(PG, T, i, g);
             } else load_grad4(T, i, T.n, g);
             if (full) {

@@ -71,6 +71,7 @@ class Trainer:
         if data_parallel == "peer" and not (optimizer == "fused" and fp16):
             data_parallel = "nccl"
         self.data_parallel = data_parallel
+        self._dp_group = group
         if data_parallel is not None:
             from . import dist as fdist
             fdist.broadcast_parameters(list(self.model.parameters()), group=group)
@@ -281,6 +282,13 @@ class Trainer:
         if self.grad_sync is not None:                 # data-parallel: all-reduce the (scaled) gradients over NCCL
             self.grad_sync()
         return loss
+
+    def reset_graph(self):
+        """Drop the captured step: the next train_step captures it again with buffers sized from the CURRENT mean sample count (a
+        caller that is about to time a steady state does this once, so that a slow drift since the last capture cannot trigger a
+        re-capture in the middle of its measurement)."""
+        self.flush()
+        self._graph = None
 
     def flush(self):
         """Apply the gradients a pipelined step left pending.  Called before anything reads the parameters."""
@@ -511,7 +519,13 @@ class Trainer:
         """renderer.py:533-536: mean samples of the last 16 steps (one D2H sync, every 16 steps)."""
         total = min(self.local_step, 16)
         if total > 0:
-            self.mean_count = int(self.step_counter[:total, 0].sum().item() / total)
+            mean = self.step_counter[:total, 0].sum().float() / total
+            if self.data_parallel is not None:
+                # data-parallel: every rank sizes its sample buffers (and decides about a re-capture of the step) from the SAME number, the
+                # largest rank's mean -- otherwise the ranks re-capture at different steps and each stall is paid by all of them at the barrier
+                import torch.distributed as dist
+                dist.all_reduce(mean, op=dist.ReduceOp.MAX, group=self._dp_group)
+            self.mean_count = int(mean.item())
 
     # ------------------------------------------------------------------------------------------------ inference
     @torch.no_grad()
