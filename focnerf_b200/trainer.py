@@ -581,7 +581,8 @@ class Trainer:
           raymarching.compact_alive.
         mode="single_pass" (default): the same samples and the same front-to-back recurrence, but marched for all rays at once
           into exactly-sized ray-ordered buffers (march_rays_all: one 4-byte host read per frame), one field evaluation, one
-          compositor launch with the same early termination.  Samples behind the termination point are evaluated and
+          compositor launch with the TRAINING kernel's termination rule (K7: stop once T after a sample < T_thresh; the loop's K10 tests T
+          before the sample -- at most one trailing sample per ray, <= T_thresh per pixel).  Samples behind the termination point are evaluated and
           discarded -- the tensor pipe and HBM are far from saturated, the launch/sync chain was the bound.
         mode="windowed": the loop's early termination without its host-driven iterations -- the march is recorded once, then each
           depth window (`windows` = samples per ray: the first 48, then the rest) is expanded for the rays still alive, evaluated and

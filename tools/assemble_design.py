@@ -28,3 +28,7 @@ stack (its Trainer, run_cuda, L1 wrappers) on its own CUDA extensions built for 
 
 The reference's GUI / OpenGL viewer is unavailable on this box and not part of the path.
 """)
+
+# profiles/r2_scaling.md from its template
+sc = open(os.path.join(ROOT, "profiles", "r2_scaling.md.in")).read()
+open(os.path.join(ROOT, "profiles", "r2_scaling.md"), "w").write(sc.replace("@@SCALING_TABLE@@", tabs["scaling"]))
