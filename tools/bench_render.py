@@ -10,20 +10,19 @@ ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
 for p in (ROOT, os.path.join(ROOT, "tests")):
     sys.path.insert(0, p)
 import cases  # noqa: E402
-import bench  # noqa: E402
 import synthetic  # noqa: E402
 from focnerf_b200.trainer import Trainer  # noqa: E402
 
 
 def main(steps):
     dev = torch.device("cuda", 0)
-    scene, cascade, grid, bits, thresh = cases.scene_bitfield(1.0)
-    tr = Trainer(bound=1.0, density_grid=torch.from_numpy(grid), device=dev, seed=0, use_graph=True)
-    pool_dev, _ = bench.make_pool(scene, bench.POOL, bench.RAYS_PER_GPU, 1000, dev)
+    # round-2 protocol (bench_common): the learnt-grid model after `steps` iterations of the reference's loop
+    import bench_common as C
+    scene, cascade, grid, bits, thresh = C.scene_and_grid()
+    tr = Trainer(bound=C.BOUND, device=dev, seed=0, use_graph=True, lr=C.LR, iters=C.ITERS, update_extra_interval=C.UPDATE_EXTRA_INTERVAL)
+    pool_dev, _ = C.make_pool(scene, C.POOL, C.RAYS_PER_GPU, 1000, dev, pinned=False)
     for i in range(steps):
-        tr.train_step(*pool_dev[i % bench.POOL])
-        if tr.local_step % 16 == 0:
-            tr.update_mean_count()
+        tr.fit_step(*pool_dev[i % C.POOL])
     pose = synthetic.ring_poses(8, radius=2.2, seed=123)[3]
     o, d = synthetic.get_rays(pose, synthetic.intrinsics(800, 800), 800, 800)
     o, d = o.to(dev), d.to(dev)
@@ -81,13 +80,15 @@ def multi_breakdown():
     dev = torch.device("cuda", 0)
     from focnerf_b200.multiobject import MultiObjectRenderer
     from focnerf_b200.network import NeRFNetwork
-    o, d = bench.multi_rays(device=dev)
+    import bench_common as C
+    o, d = (t.to(dev) for t in C.multi_rays())
     aabb = torch.tensor([-1.0] * 3 + [1.0] * 3, device=dev)
-    r = MultiObjectRenderer(bench.multi_objects(lambda: NeRFNetwork(bound=1.0), 4, dev), aabb, num_steps=512)
+    models = C.multi_object_tables([NeRFNetwork(bound=1.0).to(dev).eval() for _ in range(4)], lambda m: m.encoder.embeddings)
+    r = MultiObjectRenderer(models, aabb, num_steps=512)
     breakdown(lambda: r.render(o[:65536], d[:65536], chunk=16384), "multi-object, 65536 rays x 4 objects x 512 samples")
 
 
 if __name__ == "__main__":
     if os.environ.get("FOC_RENDER_BREAKDOWN") == "1":
         multi_breakdown()
-    main(int(sys.argv[1]) if len(sys.argv) > 1 else 1100)
+    main(int(sys.argv[1]) if len(sys.argv) > 1 else 1024)
