@@ -18,7 +18,7 @@ using namespace foc;
 
 namespace {
 
-constexpr int kRows = 32, kThreads = 256, kOutPad = 16, kMaxHidden = 256;
+constexpr int kRows = 32, kThreads = 256, kOutPad = 16;
 
 // ffmlp/src/utils.h:424-470 and 537-582 (through the stored POST-activation value)
 __device__ __forceinline__ float g_act(uint32_t a, float v) {

@@ -43,9 +43,6 @@ struct PeerGrad {
     const float* tail[FOC_MAX_PEERS];          // flat fp32 gradients of the replicated tensors; tensors[i].grad points into tail[rank]
     int rank;
 };
-// FOC_DP_DEBUG (measurement only; results are WRONG with it): 1 = pull every rank's gradient from this rank's own buffers,
-// 2 = push the fp16 copies to this rank only -- to attribute the sweep's time to NVLink loads / stores
-static int dp_debug() { static const int v = [] { const char* e = getenv("FOC_DP_DEBUG"); return e ? atoi(e) : 0; }(); return v; }
 // peer data: never served from a stale L1 line
 __device__ __forceinline__ uint2 ld_peer8(const void* p) {
     uint2 v; asm volatile("ld.relaxed.sys.global.v2.u32 {%0,%1}, [%2];" : "=r"(v.x), "=r"(v.y) : "l"(p) : "memory"); return v;
@@ -386,8 +383,6 @@ FOC_API int foc_adam_step_dp(const FocAdamTensor* tensors, int count, const floa
         if ((reinterpret_cast<uintptr_t>(peer_shadow16[r]) | reinterpret_cast<uintptr_t>(grads->grad16[r]) | reinterpret_cast<uintptr_t>(grads->tail[r])) & 15u) return FOC_ERR_UNSUPPORTED;
         ps.base[r] = peer_shadow16[r]; pg.g16[r] = grads->grad16[r]; pg.tail[r] = grads->tail[r];
     }
-    if (dp_debug() & 1) for (int r = 0; r < grads->world; ++r) { pg.g16[r] = grads->grad16[pg.rank]; pg.tail[r] = grads->tail[pg.rank]; }
-    if (dp_debug() & 2) for (int r = 0; r < grads->world; ++r) ps.base[r] = peer_shadow16[pg.rank];
     for (int i = 0; i < count; ++i) {                                   // every tensor but the table takes its gradient from the fp32 tails
         if (i == peer_tensor) continue;
         const float* g = static_cast<const float*>(tensors[i].grad);

@@ -49,7 +49,6 @@ def test_pixel_batch_matches_reference_get_rays():
     o2, d2 = synthetic.get_rays(poses[2].cpu().numpy(), intr, H, W, inds[2].cpu())
     assert float((d.view(B, N, 3)[2].cpu() - d2).abs().max()) <= 3e-7 and torch.equal(o.view(B, N, 3)[2].cpu(), o2)
     # the module-level get_rays keeps the reference's result keys; N <= 0 = every pixel in order
-    res = rays.get_rays(poses[:2], intr, 60, 80, N=-1)
     full_o, full_d = _reference_get_rays(poses[:2], synthetic.intrinsics(60, 80), 60, 80, torch.arange(4800, device="cuda").expand(2, 4800))
     res = rays.get_rays(poses[:2], synthetic.intrinsics(60, 80), 60, 80, N=-1)
     assert set(res) == {"rays_o", "rays_d"} and float((res["rays_d"] - full_d).abs().max()) <= 2e-7 and torch.equal(res["rays_o"], full_o)
