@@ -179,3 +179,49 @@ def test_torch_renderer_restatement_matches_the_c_oracle():
     np.testing.assert_allclose(img.numpy()[hit], oi[hit, :3], atol=2e-5, rtol=0)
     np.testing.assert_allclose(ws.numpy()[hit], ow[hit], atol=2e-5, rtol=0)
     np.testing.assert_allclose(dep.numpy()[hit], od[hit], atol=2e-5, rtol=0)
+
+
+@pytest.mark.parametrize("input_dim,hidden,num_layers", [(144, 16, 1), (48, 64, 2), (32, 128, 3), (16, 256, 2)])
+def test_oracle_mlp_general_shapes_against_numpy(input_dim, hidden, num_layers):
+    """The golden vectors only hold the field's 64-wide nets.  The oracle's code path for every other shape the reference module accepts
+    (ffmlp.py:99-123; the shapes csrc/mlp_generic.cu serves, tests/test_gpu_mlp.py checks against this oracle) is pinned here against a
+    plain numpy restatement: y = W_out relu(W_h ... relu(W_in x)), fp16 storage between layers, and the analytic gradients of that chain."""
+    import oracle
+    g = np.random.RandomState(5)
+    B = 64
+    std = np.sqrt(3 / hidden)
+    n = hidden * (input_dim + hidden * (num_layers - 1) + 16)
+    x = g.normal(0, 1, (B, input_dim)).astype(np.float16)
+    w = g.uniform(-std, std, n).astype(np.float16)
+    grad = g.normal(0, 1e-2, (B, 16)).astype(np.float16)
+    out, fb = oracle.ffmlp_forward(x, w, input_dim, 16, hidden, num_layers)
+    gw, bb, gi = oracle.ffmlp_backward(grad, x, w, fb, input_dim, 16, hidden, num_layers, calc_grad_inputs=True)
+    # numpy chain
+    mats, off = [], 0
+    for o, i in [(hidden, input_dim)] + [(hidden, hidden)] * (num_layers - 1) + [(16, hidden)]:
+        mats.append(w[off:off + o * i].astype(np.float64).reshape(o, i)); off += o * i
+    acts, h = [], x.astype(np.float64)
+    for m in mats[:-1]:
+        h = np.maximum(h @ m.T, 0).astype(np.float16).astype(np.float64)
+        acts.append(h)
+    want = (h @ mats[-1].T).astype(np.float16)
+    # the oracle rounds double -> float -> half (orc_mlp.c: (float)s, then rh()), numpy double -> half: a double rounding can differ by one
+    # fp16 ulp in rare elements, which then moves later layers by a few ulps
+    close = lambda a, b: np.allclose(a.astype(np.float64), b.astype(np.float64), rtol=4e-3, atol=1e-4)
+    assert close(out, want) and float(np.mean(out.view(np.uint16) != want.view(np.uint16))) < 0.05
+    for l in range(num_layers):
+        assert close(fb[l], acts[l])
+    acts = [fb[l].astype(np.float64) for l in range(num_layers)]        # the backward below goes through the ORACLE's stored activations
+    # backward through the stored activations
+    closeg = lambda a, b: np.allclose(a.astype(np.float64), b.astype(np.float64), rtol=4e-3, atol=2e-6)
+    d = grad.astype(np.float64)
+    gws = [None] * len(mats)
+    gws[-1] = d.T @ acts[-1]
+    for l in range(num_layers - 1, -1, -1):
+        d = ((d @ mats[l + 1]).astype(np.float16).astype(np.float64) * (acts[l] > 0)).astype(np.float16).astype(np.float64)
+        assert closeg(bb[num_layers - 1 - l], d), l
+        d = bb[num_layers - 1 - l].astype(np.float64)                  # continue from the oracle's own (double-rounded) values
+        prev = acts[l - 1] if l > 0 else x.astype(np.float64)
+        gws[l] = d.T @ prev
+    assert closeg(gi, (d @ mats[0]).astype(np.float16))
+    np.testing.assert_allclose(gw, np.concatenate([m.reshape(-1) for m in gws]), rtol=1e-10, atol=1e-12)
