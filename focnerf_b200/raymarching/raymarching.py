@@ -352,6 +352,25 @@ class WindowedMarch:
         return xyzs, dirs, deltas
 
     @torch.no_grad()
+    def window_spec(self, start, width, cap, counter, rows):
+        """window() without the host read: the samples go into buffers of `cap` rows (a multiple of 128, the caller's guess), `counter`
+        (int32 [2], device) receives the exact total and `rows` (int32 [1], device) the number of valid rows min(cap, total rounded up
+        to 128) for consumers that honour a device-side row count.  Rays whose slice would pass `cap` are dropped by the expansion and
+        skipped by composite(): the caller compares counter[0] with cap afterwards and renders again when it did not fit."""
+        b, g, ms, C, H = self.args
+        dev = self.rays_o.device
+        counter.zero_()
+        _backend.march_window_count(self.scratch, self.N, int(start), int(width), self.alive, self.wcounts, self.rays_w, counter)
+        rows.copy_(torch.clamp((counter[:1] + 127) // 128 * 128, min=128, max=int(cap)))
+        M = self.M = int(cap)
+        xyzs = torch.empty(M, 3, dtype=torch.float32, device=dev)
+        dirs = torch.empty(M, 3, dtype=torch.float32, device=dev)
+        deltas = torch.empty(M, 2, dtype=torch.float32, device=dev)
+        _backend.march_window_expand(self.rays_o, self.rays_d, b, g, ms, self.N, C, H, M, int(start), self.nears, self.rays_w, self.noises,
+                                     self.scratch, xyzs, dirs, deltas)
+        return xyzs, dirs, deltas
+
+    @torch.no_grad()
     def composite(self, sigmas, rgbs, deltas, T_thresh=1e-4):
         sigmas, rgbs = sigmas.float().contiguous(), rgbs.float().contiguous()
         _backend.composite_window(sigmas, rgbs, deltas, self.rays_w, self.M, self.N, float(T_thresh), self.rays_t, self.weights_sum,

@@ -544,7 +544,14 @@ class Trainer:
         if cap is None or total * 1.03 > cap or total * 1.5 < cap:
             self._render_cap[N] = max(16384, -(-int(total * 1.125 + 128) // 16384) * 16384)
 
-    def render_frames(self, frames, bg_color=1.0, T_thresh=1e-4, exchange=None):
+    def _render_size_windows(self, key, totals):
+        """Per-window capacities of the speculative windowed render: the totals of this frame + 12.5 % (+ 16 384 rows: the late windows
+        hold few samples and move more from frame to frame), kept while every total stays inside its band (see _render_size)."""
+        caps = self._render_cap.get(key)
+        if caps is None or any(t * 1.03 > c or (t + 16384) * 1.5 < c for t, c in zip(totals, caps)):
+            self._render_cap[key] = [max(16384, -(-int(t * 1.125 + 16384) // 16384) * 16384) for t in totals]
+
+    def render_frames(self, frames, bg_color=1.0, T_thresh=1e-4, exchange=None, mode="single_pass", windows=(32, 64, 928)):
         """A camera path: `frames` = [(rays_o, rays_d), ...] -> [(image, depth, weights_sum), ...] with NO host read between frames (the
         reference's test loop, legacy/nerf/utils.py test(), pays ~45 reads per frame).  Every frame is enqueued into buffers sized from
         the previous one; the exact totals of all frames come back in one read at the end and any frame whose samples did not fit is
@@ -552,23 +559,31 @@ class Trainer:
         outs, checks = [], []
         for o, d in frames:
             pend = []
-            out = self.render(o, d, bg_color, T_thresh, mode="single_pass", exchange=exchange, _defer=pend)
+            out = self.render(o, d, bg_color, T_thresh, mode=mode, exchange=exchange, windows=windows, _defer=pend)
             if exchange is not None:
                 out = tuple(t.clone() for t in out)
             outs.append(out)
             checks.append(pend[0] if pend else None)
         live = [i for i, c in enumerate(checks) if c is not None]
         if live:
-            totals = torch.cat([checks[i][0] for i in live]).tolist()              # the one host read
-            for i, t in zip(live, totals):
+            totals = torch.cat([checks[i][0].reshape(-1) for i in live]).tolist()  # the one host read
+            pos = 0
+            for i in live:
+                caps = checks[i][1] if isinstance(checks[i][1], list) else [checks[i][1]]
+                t = totals[pos:pos + len(caps)]
+                pos += len(caps)
                 N = frames[i][0].reshape(-1, 3).shape[0]
-                if _pad128(t) > checks[i][1]:
+                key = checks[i][2] if len(checks[i]) > 2 else N
+                if any(_pad128(a) > c for a, c in zip(t, caps)):
                     self.render_overflows += 1
-                    self._render_cap.pop(N, None)
-                    out = self.render(frames[i][0], frames[i][1], bg_color, T_thresh, mode="single_pass", exchange=exchange)
+                    self._render_cap.pop(key, None)
+                    out = self.render(frames[i][0], frames[i][1], bg_color, T_thresh, mode=mode, exchange=exchange, windows=windows)
                     outs[i] = tuple(x.clone() for x in out) if exchange is not None else out
                 elif i == live[-1]:
-                    self._render_size(N, t)
+                    if isinstance(checks[i][1], list):
+                        self._render_size_windows(key, t)
+                    else:
+                        self._render_size(N, t[0])
         return outs
 
     def render(self, rays_o, rays_d, bg_color=1.0, T_thresh=1e-4, device_compaction=True, mode="single_pass", exchange=None,
@@ -607,21 +622,64 @@ class Trainer:
             return frame[:, :3], frame[:, 3], frame[:, 4]
 
         if mode == "windowed":
+            field = self.model.forward_fused if self.fused and self.fp16 else self.model
+            widths, start = [], 0
+            for width in windows:
+                width = min(int(width), self.max_steps - start)
+                if width > 0:
+                    widths.append((start, width)); start += width
+            key = (N, tuple(widths))
+            caps = self._render_cap.get(key) if self._render_rows_ok() else None
+            if caps is not None:
+                # speculative sizing per window (see single_pass below): every window's samples go into buffers of the previous frame's
+                # size, the row counts stay on the device, and the exact totals of ALL windows are read once, after the last launch
+                from ._lib import set_valid_rows
+                wm = raymarching.WindowedMarch(rays_o, rays_d, self.bound, self.density_bitfield, self.cascade, self.grid_size, nears, fars,
+                                               self.dt_gamma, self.max_steps)
+                counters = torch.zeros(len(widths), 2, dtype=torch.int32, device=dev)
+                rows = torch.zeros(len(widths), 1, dtype=torch.int32, device=dev)
+                for wi, (st, width) in enumerate(widths):
+                    w = wm.window_spec(st, width, caps[wi], counters[wi], rows[wi])
+                    prev = set_valid_rows(rows[wi])
+                    try:
+                        with torch.autocast("cuda", dtype=torch.float16, enabled=self.fp16):
+                            sigmas, rgbs = field(w[0], w[1])
+                    finally:
+                        set_valid_rows(prev)
+                    wm.composite(sigmas, rgbs, w[2], T_thresh)
+                out = finish(wm.image, wm.depth, wm.weights_sum, False)
+                totals = counters[:, 0].contiguous()
+                if exchange is not None and exchange.world > 1:           # every rank must take the same decision
+                    import torch.distributed as dist
+                    dist.all_reduce(totals, op=dist.ReduceOp.MAX, group=exchange.arena.group)
+                if _defer is not None:
+                    _defer.append((totals, list(caps), key))
+                    return out
+                tl = totals.tolist()
+                fits = all(_pad128(t) <= c for t, c in zip(tl, caps))
+                self._render_size_windows(key, tl)
+                if fits:
+                    return out
+                self.render_overflows += 1                              # fall through: exact sizes, one read per window
             wm = raymarching.WindowedMarch(rays_o, rays_d, self.bound, self.density_bitfield, self.cascade, self.grid_size, nears, fars,
                                            self.dt_gamma, self.max_steps)
-            field = self.model.forward_fused if self.fused and self.fp16 else self.model
-            start = 0
-            for width in windows:
-                width = min(width, self.max_steps - start)
-                if width <= 0:
-                    break
-                w = wm.window(start, width)
+            tl = []
+            for st, width in widths:
+                w = wm.window(st, width)
+                tl.append(0 if w is None else w[0].shape[0])
                 if w is None:
                     break
                 with torch.autocast("cuda", dtype=torch.float16, enabled=self.fp16):
                     sigmas, rgbs = field(w[0], w[1])
                 wm.composite(sigmas, rgbs, w[2], T_thresh)
-                start += width
+            tl += [0] * (len(widths) - len(tl))
+            if self._render_rows_ok():
+                if exchange is not None and exchange.world > 1:
+                    import torch.distributed as dist
+                    tt = torch.tensor(tl, dtype=torch.int32, device=dev)
+                    dist.all_reduce(tt, op=dist.ReduceOp.MAX, group=exchange.arena.group)
+                    tl = tt.tolist()
+                self._render_size_windows(key, tl)
             return finish(wm.image, wm.depth, wm.weights_sum, False)
         if mode == "single_pass":
             field = self.model.forward_fused if self.fused and self.fp16 else self.model

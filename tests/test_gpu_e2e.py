@@ -98,6 +98,30 @@ def test_render_speculative_sizing_is_exact():
     assert same(outs[0], exact) and same(outs[1], exact2) and tr.render_overflows >= 3
 
 
+def test_render_windowed_speculative_sizing_is_exact():
+    """mode="windowed" with per-window capacities learnt from the previous frame (no host read inside the frame) gives the bits of the
+    exactly-sized windowed render, also when a window's guess was too small, and through render_frames."""
+    scene, tr = _trainer()
+    for it in range(32):
+        o, d = cases.camera_rays(4096, 700 + it)
+        o, d = torch.from_numpy(o).cuda(), torch.from_numpy(d).cuda()
+        tr.train_step(o, d, scene.render_gt(o, d))
+    o, d = cases.camera_rays(30000, 9)
+    o, d = torch.from_numpy(o).cuda(), torch.from_numpy(d).cuda()
+    wins = (16, 48, 960)
+    same = lambda a, b: all(torch.equal(torch.nan_to_num(x), torch.nan_to_num(y)) for x, y in zip(a, b))
+    exact = [t.clone() for t in tr.render(o, d, mode="windowed", windows=wins)]          # first frame: exact sizes, one read per window
+    keys = [k for k in tr._render_cap if isinstance(k, tuple)]
+    assert len(keys) == 1 and len(tr._render_cap[keys[0]]) == 3
+    assert same(tr.render(o, d, mode="windowed", windows=wins), exact) and tr.render_overflows == 0
+    tr._render_cap[keys[0]] = [16384, 16384, 16384]                                      # too small for the first windows
+    assert same(tr.render(o, d, mode="windowed", windows=wins), exact) and tr.render_overflows == 1
+    outs = tr.render_frames([(o, d), (o, d)], mode="windowed", windows=wins)
+    assert same(outs[0], exact) and same(outs[1], exact)
+    single = tr.render(o, d)                                                             # and it is the same picture as the single pass
+    assert float((torch.nan_to_num(single[0]) - torch.nan_to_num(exact[0])).abs().max()) <= 2e-3
+
+
 @pytest.mark.parametrize("windows", [(48, 976), (8, 24, 64, 928), (1024,)])
 def test_render_windowed_matches_loop(windows):
     """Depth-windowed render (recorded march, K10 recurrence per window, alive flags) reproduces the reference-style loop."""

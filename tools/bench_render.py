@@ -32,15 +32,25 @@ def main(steps):
         n_world = int(os.environ["FOC_RENDER_SHARE"])
         idx = cyclic_tile(800 * 800, 0, n_world).to(dev)
         oo, dd = o[idx].contiguous(), d[idx].contiguous()
-        for _ in range(2):
-            tr.render(oo, dd)
+        for mode in ("single_pass", "windowed"):
+            for _ in range(3):
+                tr.render(oo, dd, mode=mode, windows=(32, 64, 928))
+            torch.cuda.synchronize()
+            t = time.perf_counter()
+            tr.render_frames([(oo, dd)] * 10, mode=mode, windows=(32, 64, 928))
+            torch.cuda.synchronize()
+            print(f"1/{n_world} share ({oo.shape[0]} rays), render_frames x 10, {mode}: {(time.perf_counter() - t) / 10 * 1e3:.3f} ms/frame "
+                  f"(overflows {tr.render_overflows})", flush=True)
+    for mode in ("single_pass", "windowed"):
+        for _ in range(3):
+            tr.render(o, d, mode=mode, windows=(32, 64, 928))
         torch.cuda.synchronize()
         t = time.perf_counter()
-        for _ in range(10):
-            tr.render(oo, dd)
+        tr.render_frames([(o, d)] * 5, mode=mode, windows=(32, 64, 928))
         torch.cuda.synchronize()
-        print(f"1/{n_world} share ({oo.shape[0]} rays): {(time.perf_counter() - t) / 10 * 1e3:.3f} ms/frame (whole frame / {n_world} would be the ideal)")
-        breakdown(lambda: tr.render(oo, dd), f"1/{n_world} share of the frame, single_pass")
+        print(f"whole frame, render_frames x 5, {mode}: {(time.perf_counter() - t) / 5 * 1e3:.3f} ms/frame (overflows {tr.render_overflows})", flush=True)
+    if os.environ.get("FOC_RENDER_QUICK"):
+        return
     ref = None
     for name, kw in [("single_pass", dict(mode="single_pass")),
                      ("windowed 48+976", dict(mode="windowed", windows=(48, 976))),
