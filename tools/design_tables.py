@@ -47,6 +47,10 @@ def status():
     if ro and rr:
         rows.append(("800×800 render, configs[2], the reference arm's checkpoint in both arms", f"{f(rr['value'])} Mrays/s ({f(rr['ms_per_frame'])} ms / frame), coverage {rr.get('coverage'):.5f}",
                      f"{f(ro['value'])} Mrays/s ({f(ro['ms_per_frame'])} ms / frame), coverage {ro.get('coverage'):.5f}", f"{ro['value'] / rr['value']:.1f}×"))
+    rw = o.get("render_windowed") or {}
+    if rw and rr:
+        rows.append(("same frame in depth windows (32 / 64 / 928 samples per ray, the reference loop's exact termination rule, speculative sizing per window: `render_windowed`)",
+                     "(same reference loop)", f"{f(rw['value'])} Mrays/s ({f(rw['ms_per_frame'])} ms / frame), coverage {rw.get('coverage'):.5f}", f"{rw['value'] / rr['value']:.1f}×"))
     for key, label in (("multi_object", "4-object 640×480 composite, configs[3] (T = 512 per ray and object), full frame"), ("multi_object_edit8", "8-object composite with editable.py's offset on object 0, configs[4]")):
         mo, mr = o.get(key) or {}, r.get(key) or {}
         if mo and mr:
@@ -92,7 +96,7 @@ def kernels():
 
 def scaling():
     base = load("r2_scale_n1.json") or load("r2_bench.json")     # the N = 1 run of the same lease when there is one
-    print("| N | train rays/s (ms / step) | efficiency | e2e rays/s | render Mrays/s (ms / frame) | render speed-up | K = 4 composite Mrays/s (ms) | K = 8 edit (ms) | train 32 768 rays / GPU (ms / step) | dp_parity |\n|" + "---|" * 10)
+    print("| N | train rays/s (ms / step) | efficiency | e2e rays/s | render Mrays/s (ms / frame) | render speed-up | render, depth windows (ms / frame) | K = 4 composite Mrays/s (ms) | K = 8 edit (ms) | train 32 768 rays / GPU (ms / step) | dp_parity |\n|" + "---|" * 11)
     for n in (1, 2, 4, 8):
         d = base if n == 1 else load(f"r2_scale_n{n}.json")
         if not d:
@@ -100,7 +104,7 @@ def scaling():
         rd, m4, m8, big = d.get("render") or d.get("render_own_model") or {}, d.get("multi_object") or {}, d.get("multi_object_edit8") or {}, d.get("train_262k") or {}
         rb = base.get("render") or base.get("render_own_model") or {}
         print(f"| {n} | {f(d['value'] / 1e6)} M ({f(d['ms_per_step'], 4)}) | {100 * d['value'] / (n * base['value']):.1f} % | {f(d['e2e']['value'] / 1e6)} M | "
-              f"{f(rd.get('value'), 1)} ({f(rd.get('ms_per_frame'))}) | {(rd.get('value', 0) / rb['value'] if rb else 0):.2f}× | {f(m4.get('value'))} ({f(m4.get('ms_per_frame'), 1)}) | {f(m8.get('ms_per_frame'), 1)} | "
+              f"{f(rd.get('value'), 1)} ({f(rd.get('ms_per_frame'))}) | {(rd.get('value', 0) / rb['value'] if rb else 0):.2f}× | {f((d.get('render_windowed') or {}).get('ms_per_frame'))} | {f(m4.get('value'))} ({f(m4.get('ms_per_frame'), 1)}) | {f(m8.get('ms_per_frame'), 1)} | "
               f"{f((big.get('value') or 0) / 1e6)} M ({f(big.get('ms_per_step'))}) | {d.get('dp_parity')} |")
     for n in (2, 4, 8):
         d = load(f"r2_scale_n{n}.json")
