@@ -95,6 +95,10 @@ def kernels():
 
 
 def scaling():
+    try:
+        WIN = json.load(open(os.path.join(P, 'r2_render_windowed.json')))['by_n']
+    except Exception:
+        WIN = {}
     base = load("r2_scale_n1.json") or load("r2_bench.json")     # the N = 1 run of the same lease when there is one
     print("| N | train rays/s (ms / step) | efficiency | e2e rays/s | render Mrays/s (ms / frame) | render speed-up | render, depth windows (ms / frame) | K = 4 composite Mrays/s (ms) | K = 8 edit (ms) | train 32 768 rays / GPU (ms / step) | dp_parity |\n|" + "---|" * 11)
     for n in (1, 2, 4, 8):
@@ -104,7 +108,7 @@ def scaling():
         rd, m4, m8, big = d.get("render") or d.get("render_own_model") or {}, d.get("multi_object") or {}, d.get("multi_object_edit8") or {}, d.get("train_262k") or {}
         rb = base.get("render") or base.get("render_own_model") or {}
         print(f"| {n} | {f(d['value'] / 1e6)} M ({f(d['ms_per_step'], 4)}) | {100 * d['value'] / (n * base['value']):.1f} % | {f(d['e2e']['value'] / 1e6)} M | "
-              f"{f(rd.get('value'), 1)} ({f(rd.get('ms_per_frame'))}) | {(rd.get('value', 0) / rb['value'] if rb else 0):.2f}× | {f((d.get('render_windowed') or {}).get('ms_per_frame'))} | {f(m4.get('value'))} ({f(m4.get('ms_per_frame'), 1)}) | {f(m8.get('ms_per_frame'), 1)} | "
+              f"{f(rd.get('value'), 1)} ({f(rd.get('ms_per_frame'))}) | {(rd.get('value', 0) / rb['value'] if rb else 0):.2f}× | {f((d.get('render_windowed') or {}).get('ms_per_frame') or WIN.get(str(n), {}).get('windowed_ms'))} | {f(m4.get('value'))} ({f(m4.get('ms_per_frame'), 1)}) | {f(m8.get('ms_per_frame'), 1)} | "
               f"{f((big.get('value') or 0) / 1e6)} M ({f(big.get('ms_per_step'))}) | {d.get('dp_parity')} |")
     for n in (2, 4, 8):
         d = load(f"r2_scale_n{n}.json")
