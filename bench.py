@@ -381,7 +381,7 @@ def run_ours(args):
     if args.frames > 0:
         render_own = render_bench(tr, dev, rank, world, frames=args.frames, tag="own (trained by this arm)")
         render = render_own
-        if world == 1 and os.path.exists(C.SHARED_CKPT) and os.environ.get("FOC_NO_SHARED_CKPT") != "1":
+        if os.path.exists(C.SHARED_CKPT) and os.environ.get("FOC_NO_SHARED_CKPT") != "1":      # every N: the 1 -> 8 render curve is of ONE model
             # the reference arm (run first) left ITS trained model in the reference's checkpoint format: render the same model
             try:
                 tr_s = make_trainer(0)
