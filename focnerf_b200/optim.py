@@ -184,6 +184,15 @@ class FocDpReduce(ctypes.Structure):
                 ("reduced_tail", ctypes.c_void_p), ("inf_flag", ctypes.c_void_p), ("shard_blocks", ctypes.c_uint32)]
 
 
+def shard_range(n, world, rank, block=4096):
+    """Rank `rank`'s slice of an n-element table sharded over `world` ranks: equal slices whose length is a multiple of `block` (the
+    sweep's elements per CTA), the last ranks' slices shorter or empty.  -> (slice length of a full shard, start, length)."""
+    per = -(-n // world)
+    per = -(-per // block) * block
+    start = min(rank * per, n)
+    return per, start, min(start + per, n) - start
+
+
 class FocDpGrads(ctypes.Structure):
     """include/foc_b200.h: struct FocDpGrads"""
     _fields_ = [("world", ctypes.c_int32), ("rank", ctypes.c_int32), ("grad16", ctypes.c_void_p * 8), ("tail", ctypes.c_void_p * 8)]
@@ -216,10 +225,7 @@ class PeerAdam(ScaledAdam):
         n = table.numel()
         if n % 8:
             raise RuntimeError("PeerAdam: the sharded table must hold a multiple of 8 values")
-        per = -(-n // self.world)
-        per = -(-per // self.BLOCK) * self.BLOCK
-        self.shard_start = min(self.rank * per, n)
-        self.shard_n = min(self.shard_start + per, n) - self.shard_start
+        per, self.shard_start, self.shard_n = shard_range(n, self.world, self.rank, self.BLOCK)
         self.shard_len = per
         self.tail = [p for p in self.params if p is not table]
         self.tail_off, off = [], 0

@@ -74,3 +74,17 @@ def test_generic_ffmlp_module_accepts_the_reference_shapes():
         m = FFMLP(*args)
         i, o, h, l = args
         assert m.weights.numel() == h * (i + h * (l - 1) + 16)
+
+
+def test_dp_shard_ranges_tile_the_table():
+    """optim.shard_range (PeerAdam): the ranks' slices are disjoint, ordered, cover the table exactly and start on 4096-element blocks."""
+    from focnerf_b200.optim import shard_range
+    for n in (8, 4096, 12239728, 12239728 + 8, 50000 * 2):
+        for world in (1, 2, 3, 4, 8):
+            pos = 0
+            for r in range(world):
+                per, start, length = shard_range(n, world, r)
+                assert per % 4096 == 0 and start == min(r * per, n) and start % 4096 == 0 or start == n
+                assert start == pos and length >= 0
+                pos += length
+            assert pos == n
